@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py — the post-mount HBM probe on N B200s, one JSON line.
+
+Workload (BASELINE.json configs[1], "AddGPU of 1 B200 ... then the post-mount HBM probe"):
+one STEP is one probe pass over a pair of N-byte device buffers (N = 8 GiB, >> 126 MB L2):
+
+    hbm_write_pattern(A)      N   algorithmic bytes
+    hbm_read_verify(A)        N
+    hbm_copy(A -> B)          2N
+                              4N  per step
+
+`value`   = 4N * K * world / (device time of K steps, max over ranks)      [GB/s], buffers resident in HBM,
+            launched through the C ABI's device-pointer entry points on torch's current stream.
+`e2e`     = the same 4N per call, divided by the WALL time of the reference-facing one-shot call
+            gmp_probe_hbm() (device select, cudaMalloc of both buffers, the passes, a pinned-host DMA round trip
+            of `dma` bytes each way, verdict read-back, cudaFree) — host buffers and copies inside the timed region.
+`roofline`= the copy kernel (largest share of the step) against MEASURED_PEAKS.json's hbm_gbs.
+`cpu_baseline` = the oracle's CPU port of the same three passes on the host cores (bounded sample).
+`--impl reference` times that CPU port alone (the reference itself has no device-memory code).
+
+Multi-GPU: the probe shards by device with no data-path collective (weak scaling); torch.distributed is used
+only for the barrier and the max-over-ranks of the device time.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GIB = 1 << 30
+METRIC = "probe HBM GB/s per job (write+read-verify+copy pass, algorithmic bytes)"
+SEED = 0x9E3779B97F4A7C15
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, torch copy_ read+write)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(prefix="gmp_clocks_", suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu_index), f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        try:
+            rows = [r.strip().split(", ") for r in open(self.path) if r.strip()]
+            os.unlink(self.path)
+        except Exception:
+            return out
+        sm, mx, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                power.append(float(r[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, r[5:9]):
+                if v.strip().lower() == "active":
+                    reasons.add(name)
+        if sm:
+            # "under load" = samples in the upper half of the power range seen
+            lo, hi = min(power), max(power)
+            load = [s for s, p in zip(sm, power) if p >= lo + 0.5 * (hi - lo)] or sm
+            out.update(sm_mhz=statistics.median(load), sm_max_mhz=max(mx), reasons=sorted(reasons),
+                       samples=len(sm), power_w_max=hi)
+        return out
+
+
+def host_cores() -> int:
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_port_run(sample_bytes: int, threads: int, min_seconds: float, max_reps: int):
+    """The oracle's CPU port of one step (fill, verify, copy) on `threads` host threads."""
+    from oracle import gmo_ctypes as gmo  # the checker doubles as the timed CPU baseline, nothing else
+
+    total_s, reps, per = 0.0, 0, [0.0, 0.0, 0.0]
+    while reps < max_reps and (reps == 0 or total_s < min_seconds):
+        secs, (bad, _first, x, s) = gmo.cpu_probe(sample_bytes, threads, SEED + reps)
+        assert bad == 0 and (x, s) == gmo.pattern_checksum(sample_bytes, 0, SEED + reps)
+        total_s += sum(secs)
+        per = [a + b for a, b in zip(per, secs)]
+        reps += 1
+    gbs = 4.0 * sample_bytes * reps / total_s / 1e9
+    return gbs, total_s / reps, reps, [p / reps for p in per]
+
+
+def run_reference(args, rank: int, world: int):
+    if rank != 0:
+        return
+    threads = min(256, host_cores())
+    sample = args.cpu_sample_gib * GIB
+    # each "step" is one bounded sample of the workload
+    for _ in range(min(args.warmup, 1)):
+        cpu_port_run(sample, threads, 0.0, 1)
+    t0 = time.perf_counter()
+    per_step = []
+    for _ in range(args.steps):
+        gbs, sec, _reps, _ = cpu_port_run(sample, threads, 0.0, 1)
+        per_step.append(sec)
+    wall = time.perf_counter() - t0
+    value = 4.0 * sample * args.steps / sum(per_step) / 1e9
+    line = {
+        "impl": "reference",
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * sum(per_step) / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": f"CPU port of the probe step (fill+verify+copy) on host DRAM, "
+                               f"{args.cpu_sample_gib} GiB per buffer sample of the {args.gib} GiB workload",
+                   "bytes_per_buffer": sample, "algorithmic_bytes_per_step": 4 * sample},
+        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": threads, "kind": "port",
+                         "sample": f"{args.cpu_sample_gib} GiB per buffer x {args.steps} steps; the reference has no "
+                                   f"device-memory path, so this is oracle/gmo_pattern.c on pthreads"},
+        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "wall_s": wall,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--gib", type=float, default=8.0, help="bytes per buffer in GiB (BASELINE: 8)")
+    ap.add_argument("--dma-mib", type=int, default=64, help="pinned host<->device round trip inside the e2e call")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 -> min(steps, 10)")
+    ap.add_argument("--cpu-sample-gib", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-clocks", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    from gpumounter_b200 import probe
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: gpumounter_b200 has no CPU fallback "
+                         "(use --impl reference for the CPU port)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    nbytes = int(args.gib * GIB) & ~15
+    a = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    b = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    acc = torch.zeros(4, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream()
+    s = stream.cuda_stream
+    pa, pb, pacc = a.data_ptr(), b.data_ptr(), acc.data_ptr()
+    launches = 0
+
+    def step(i, ev=None):
+        nonlocal launches
+        seed = SEED + i
+        if ev:
+            ev[0].record(stream)
+        probe.hbm_write_pattern(pa, nbytes, probe.PAT_SPLITMIX, seed, s)
+        if ev:
+            ev[1].record(stream)
+        probe.hbm_read_verify_async(pa, nbytes, probe.PAT_SPLITMIX, seed, pacc, s)
+        if ev:
+            ev[2].record(stream)
+        probe.hbm_copy(pb, pa, nbytes, s)
+        if ev:
+            ev[3].record(stream)
+        launches += 3
+
+    for i in range(args.warmup):
+        step(i)
+    r = probe.hbm_verify_fetch(pacc, s)
+    assert r.ok, "warm-up verify failed"
+
+    K = args.steps
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank)
+    if not args.no_clocks and rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    launches = 0
+    barrier()
+    torch.cuda.synchronize()
+    t_start.record(stream)
+    for i in range(K):
+        step(args.warmup + i, evs[i])
+    t_end.record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    dev_ms = t_start.elapsed_time(t_end)
+    timed_launches = launches
+    clocks = sampler.stop() if (not args.no_clocks and rank == 0) else None
+
+    # the last step's verdicts: A verified in-step; verify the copy now (outside the timed region)
+    r = probe.hbm_verify_fetch(pacc, s)
+    last_seed = SEED + args.warmup + K - 1
+    rb = probe.hbm_read_verify(pb, nbytes, probe.PAT_SPLITMIX, last_seed, s)
+    assert r.ok and rb.ok and (r.xor64, r.sum64) == (rb.xor64, rb.sum64), "probe verification failed"
+
+    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    max_ms = float(t.item())
+    step_bytes = 4 * nbytes
+    value = step_bytes * K * world / (max_ms * 1e-3) / 1e9
+
+    k_ms = {"write": [], "verify": [], "copy": []}
+    for e in evs:
+        k_ms["write"].append(e[0].elapsed_time(e[1]))
+        k_ms["verify"].append(e[1].elapsed_time(e[2]))
+        k_ms["copy"].append(e[2].elapsed_time(e[3]))
+    avg = {k: sum(v) / len(v) for k, v in k_ms.items()}
+    algo = {"write": nbytes, "verify": nbytes, "copy": 2 * nbytes}
+    gbs = {k: algo[k] / (avg[k] * 1e-3) / 1e9 for k in avg}
+    peak, peak_src = load_peaks()
+
+    # ---- e2e: the reference-facing one-shot call, wall clock, host buffers + copies inside ----
+    e2e_steps = args.e2e_steps or min(K, 10)
+    dma = args.dma_mib << 20
+    del b  # the one-shot call allocates its own pair; keep A so that the device is not empty
+    torch.cuda.empty_cache()
+
+    my_uuid = probe.enumerate_cuda()[local_rank].uuid
+
+    def one_shot():
+        return probe.probe_hbm(my_uuid, nbytes=nbytes, iters=1, seed=SEED, dma_bytes=dma,
+                               flags=probe.HBM_F_KEEP_DEVICE)
+
+    for _ in range(2):
+        one_shot()
+    barrier()
+    torch.cuda.synchronize()
+    w0 = time.perf_counter()
+    last = None
+    for _ in range(e2e_steps):
+        last = one_shot()
+    torch.cuda.synchronize()
+    w1 = time.perf_counter()
+    barrier()
+    e2e_s = torch.tensor([w1 - w0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = step_bytes * e2e_steps * world / float(e2e_s.item()) / 1e9
+    e2e = {
+        "value": e2e_value, "unit": "GB/s",
+        "h2d_bytes_per_step": int(last.h2d_bytes), "d2h_bytes_per_step": int(last.d2h_bytes),
+        "ms_per_call": 1e3 * float(e2e_s.item()) / e2e_steps, "calls": e2e_steps,
+        "call": "gmp_probe_hbm(uuid, {bytes, iters=1, dma_bytes}) one-shot, context warm",
+        "phases_ms_last_call": {k[3:]: getattr(last, k) / 1e6 for k in
+                                ("ns_select_device", "ns_context", "ns_alloc", "ns_first_kernel", "ns_kernels",
+                                 "ns_dma", "ns_teardown", "ns_total")},
+        "in_call_gbs": {"write": last.write_gbs_best, "verify": last.read_gbs_best, "copy": last.copy_gbs_best,
+                        "h2d": last.h2d_gbs, "d2h": last.d2h_gbs},
+    }
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "ms_per_step": max_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "post-mount HBM probe step: write_pattern(A)+read_verify(A)+copy(A->B), "
+                               "BASELINE configs[1]", "bytes_per_buffer": nbytes, "buffers": 2,
+                   "algorithmic_bytes_per_step": step_bytes, "pattern": "splitmix",
+                   "l2": "inputs larger than L2 (2 x %.1f GiB vs 126 MB), no flush needed" % (nbytes / GIB),
+                   "parallelism": f"{world} independent per-GPU probes, no collective"},
+        "gpu_launches": timed_launches,
+        "kernels": {k: {"avg_ms": avg[k], "gbs": gbs[k], "frac_of_peak": gbs[k] / peak,
+                        "share_of_step": avg[k] / sum(avg.values())} for k in avg},
+        "roofline": {"bound": "hbm", "kernel": "k_hbm_copy", "achieved": gbs["copy"], "peak": peak, "unit": "GB/s",
+                     "frac": gbs["copy"] / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": 2 * nbytes},
+        "e2e": e2e,
+        "clocks": clocks,
+    }
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            line["roofline"]["traffic"] = json.load(f).get("k_hbm_copy_dram_bytes_per_launch")
+    except Exception:
+        pass
+
+    if world == 1 and not args.no_cpu_baseline:
+        threads = min(256, host_cores())
+        sample = args.cpu_sample_gib * GIB
+        cgbs, sec, reps, per = cpu_port_run(sample, threads, 8.0, 6)
+        line["cpu_baseline"] = {
+            "value": cgbs, "unit": "GB/s", "cores": threads, "kind": "port",
+            "sample": f"oracle/gmo_pattern.c fill+verify+copy of {args.cpu_sample_gib} GiB per buffer on host DRAM, "
+                      f"{reps} reps, {sec:.2f} s per rep (the reference has no device-memory code to time)",
+            "seconds_per_pass": {"fill": per[0], "verify": per[1], "copy": per[2]},
+        }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,486 @@
+// Error plumbing, CUDA device selection by UUID, and the one-shot HBM probe
+// (gmp_probe_hbm) that the worker calls after a mount
+// (hook point: ref pkg/server/gpu-mount/server.go:97-98).
+
+#include "gmp_internal.h"
+
+#include <algorithm>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+namespace gmp {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void clear_error() { g_err[0] = '\0'; }
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error("%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    switch (e) {
+        case cudaErrorNoDevice:
+        case cudaErrorInsufficientDriver:
+        case cudaErrorStubLibrary:
+        case cudaErrorSystemDriverMismatch:
+        case cudaErrorSystemNotReady:
+        case cudaErrorInitializationError:
+        case cudaErrorCompatNotSupportedOnDevice:
+            (void)cudaGetLastError();
+            return GMP_ERR_UNAVAILABLE;
+        case cudaErrorMemoryAllocation:
+            (void)cudaGetLastError();
+            return GMP_ERR_NOMEM;
+        case cudaErrorInvalidDevice:
+            (void)cudaGetLastError();
+            return GMP_ERR_NO_DEVICE;
+        default:
+            return GMP_ERR_CUDA;
+    }
+}
+
+void format_uuid(const unsigned char b[16], char out[GMP_UUID_LEN]) {
+    // NVML prints the 16 raw bytes as GPU-8-4-4-4-12 lowercase hex.
+    snprintf(out, GMP_UUID_LEN,
+             "GPU-%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", b[0], b[1], b[2], b[3],
+             b[4], b[5], b[6], b[7], b[8], b[9], b[10], b[11], b[12], b[13], b[14], b[15]);
+}
+
+static int device_uuid(int ordinal, char out[GMP_UUID_LEN], char pci[GMP_PCI_LEN]) {
+    cudaDeviceProp prop;
+    GMP_CUDA(cudaGetDeviceProperties(&prop, ordinal));
+    format_uuid(reinterpret_cast<const unsigned char*>(prop.uuid.bytes), out);
+    if (pci != nullptr) {
+        // same layout NVML uses for pci.busId: domain(8 hex):bus:device.function
+        snprintf(pci, GMP_PCI_LEN, "%08X:%02X:%02X.0", (unsigned)prop.pciDomainID, (unsigned)prop.pciBusID,
+                 (unsigned)prop.pciDeviceID);
+    }
+    return GMP_OK;
+}
+
+int find_cuda_device(const char* uuid, int* ordinal, int* device_count) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    if (device_count) *device_count = n;
+    if (n == 0) {
+        set_error("CUDA sees no device");
+        return GMP_ERR_UNAVAILABLE;
+    }
+    if (uuid == nullptr || uuid[0] == '\0') {
+        *ordinal = 0;
+        return GMP_OK;
+    }
+    for (int i = 0; i < n; ++i) {
+        char u[GMP_UUID_LEN];
+        int rc = device_uuid(i, u, nullptr);
+        if (rc != GMP_OK) return rc;
+        if (strcmp(u, uuid) == 0) {
+            *ordinal = i;
+            return GMP_OK;
+        }
+    }
+    set_error("no CUDA-visible device has UUID %s (%d visible)", uuid, n);
+    return GMP_ERR_NO_DEVICE;
+}
+
+}  // namespace gmp
+
+using namespace gmp;
+
+extern "C" int gmp_abi_version(void) { return GMP_ABI_VERSION; }
+
+extern "C" const char* gmp_last_error(void) { return g_err; }
+
+extern "C" const char* gmp_strerror(int code) {
+    switch (code) {
+        case GMP_OK: return "ok";
+        case GMP_ERR_INVALID: return "invalid argument";
+        case GMP_ERR_UNAVAILABLE: return "CUDA driver or GPU unavailable";
+        case GMP_ERR_NO_DEVICE: return "no such device";
+        case GMP_ERR_CUDA: return "CUDA call failed";
+        case GMP_ERR_NVML: return "NVML call failed";
+        case GMP_ERR_NVML_NOT_FOUND: return "could not load NVML library";
+        case GMP_ERR_VERIFY: return "pattern verification failed";
+        case GMP_ERR_NOMEM: return "out of memory";
+        case GMP_ERR_SYS: return "system call failed";
+        case GMP_ERR_BUFFER_TOO_SMALL: return "buffer too small";
+        case GMP_ERR_DEVICE_SET: return "device set mismatch";
+        case GMP_ERR_P2P_MATRIX: return "P2P matrix mismatch between CUDA and NVML";
+        case GMP_ERR_CGROUP_DRIVER: return "unsupported cgroup driver";
+        case GMP_ERR_NAME: return "invalid character in cgroup name component";
+        case GMP_ERR_EMPTY_CGROUP: return "cgroup has no process";
+        case GMP_ERR_TARGET: return "Target must be specified";
+        case GMP_ERR_BUSY: return "GPU busy";
+        case GMP_ERR_NODE_CTL: return "/dev/nvidiactl missing or not openable";
+        case GMP_ERR_NODE_UVM: return "/dev/nvidia-uvm missing or not openable";
+        case GMP_ERR_NODE_GPU: return "GPU device node missing";
+        case GMP_ERR_NODE_DENIED: return "GPU device node not openable (device cgroup)";
+        case GMP_ERR_DRIVER_LIB: return "libcuda.so.1 not found";
+        default: return "unknown error";
+    }
+}
+
+extern "C" int gmp_enumerate_cuda(gmp_device* out, int cap, int* n) {
+    clear_error();
+    if (out == nullptr || n == nullptr || cap < 0) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    *n = 0;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    if (count > cap) {
+        *n = count;
+        set_error("%d CUDA devices, capacity %d", count, cap);
+        return GMP_ERR_BUFFER_TOO_SMALL;
+    }
+    for (int i = 0; i < count; ++i) {
+        memset(&out[i], 0, sizeof(out[i]));
+        int rc = device_uuid(i, out[i].uuid, out[i].pci_bus_id);
+        if (rc != GMP_OK) return rc;
+        out[i].minor = UINT32_MAX;
+        out[i].nvml_index = -1;
+        out[i].cuda_ordinal = i;
+    }
+    *n = count;
+    return GMP_OK;
+}
+
+extern "C" int gmp_device_sets_equal(const gmp_device* a, int na, const gmp_device* b, int nb) {
+    clear_error();
+    if ((na > 0 && a == nullptr) || (nb > 0 && b == nullptr) || na < 0 || nb < 0) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    if (na != nb) {
+        set_error("device counts differ: %d vs %d", na, nb);
+        return GMP_ERR_DEVICE_SET;
+    }
+    std::vector<char> used((size_t)nb, 0);
+    for (int i = 0; i < na; ++i) {
+        int hit = -1;
+        for (int j = 0; j < nb; ++j) {
+            if (!used[j] && strncmp(a[i].uuid, b[j].uuid, GMP_UUID_LEN) == 0) {
+                hit = j;
+                break;
+            }
+        }
+        if (hit < 0) {
+            set_error("UUID %s present on one side only", a[i].uuid);
+            return GMP_ERR_DEVICE_SET;
+        }
+        if (a[i].minor != UINT32_MAX && b[hit].minor != UINT32_MAX && a[i].minor != b[hit].minor) {
+            set_error("UUID %s: minor %u vs %u", a[i].uuid, a[i].minor, b[hit].minor);
+            return GMP_ERR_DEVICE_SET;
+        }
+        used[hit] = 1;
+    }
+    return GMP_OK;
+}
+
+// ---- one-shot HBM probe ---------------------------------------------------------------
+namespace {
+
+struct Series {
+    std::vector<double> gbs;
+    void add(double bytes, float ms) {
+        if (ms > 0.f) gbs.push_back(bytes / (ms * 1e-3) / 1e9);
+    }
+    double best() const { return gbs.empty() ? 0.0 : *std::max_element(gbs.begin(), gbs.end()); }
+    double median() const {
+        if (gbs.empty()) return 0.0;
+        std::vector<double> v(gbs);
+        std::sort(v.begin(), v.end());
+        const size_t n = v.size();
+        return (n & 1) ? v[n / 2] : 0.5 * (v[n / 2 - 1] + v[n / 2]);
+    }
+};
+
+// Everything the probe owns on the device; released in one place on every path.
+struct ProbeResources {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    void* a = nullptr;
+    void* b = nullptr;
+    unsigned long long* acc = nullptr;
+    void* pinned = nullptr;
+    void release() {
+        if (pinned) cudaFreeHost(pinned);
+        if (acc) cudaFree(acc);
+        if (b) cudaFree(b);
+        if (a) cudaFree(a);
+        for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
+        if (stream) cudaStreamDestroy(stream);
+        pinned = a = b = nullptr;
+        acc = nullptr;
+        ev[0] = ev[1] = nullptr;
+        stream = nullptr;
+    }
+};
+
+int timed(ProbeResources& r, cudaError_t (*fn)(void*), void* ctx, float* ms) {
+    GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
+    GMP_CUDA(fn(ctx));
+    GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+    GMP_CUDA(cudaEventSynchronize(r.ev[1]));
+    GMP_CUDA(cudaEventElapsedTime(ms, r.ev[0], r.ev[1]));
+    return GMP_OK;
+}
+
+struct PassCtx {
+    ProbeResources* r;
+    void* buf;
+    void* src;
+    size_t bytes;
+    int pattern;
+    uint64_t seed;
+};
+
+cudaError_t do_write(void* p) {
+    auto* c = static_cast<PassCtx*>(p);
+    return launch_write(c->buf, c->bytes, c->pattern, c->seed, c->r->stream);
+}
+cudaError_t do_verify(void* p) {
+    auto* c = static_cast<PassCtx*>(p);
+    return launch_verify(c->buf, c->bytes, c->pattern, c->seed, c->r->acc, c->r->stream);
+}
+cudaError_t do_copy(void* p) {
+    auto* c = static_cast<PassCtx*>(p);
+    return launch_copy(c->buf, c->src, c->bytes, c->r->stream);
+}
+
+int fetch_acc(ProbeResources& r, gmp_verify_result* v) {
+    unsigned long long raw[4];
+    GMP_CUDA(cudaMemcpyAsync(raw, r.acc, sizeof(raw), cudaMemcpyDeviceToHost, r.stream));
+    GMP_CUDA(cudaStreamSynchronize(r.stream));
+    decode_acc(raw, v);
+    return GMP_OK;
+}
+
+void note_verify(gmp_hbm_result* out, const gmp_verify_result& v, int pattern) {
+    out->xor64 = v.xor64;
+    out->sum64 = v.sum64;
+    if (v.mismatch_lanes != 0) {
+        if (out->mismatch_lanes == 0) {
+            out->first_bad_lane = v.first_bad_lane;
+            out->first_bad_pattern = pattern;
+        }
+        out->mismatch_lanes += v.mismatch_lanes;
+    }
+}
+
+int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeResources& r) {
+    uint64_t t0 = now_ns();
+    GMP_CUDA(cudaSetDevice(ordinal));
+    GMP_CUDA(cudaFree(0));  // forces primary-context creation so it is timed on its own
+    out->ns_context = now_ns() - t0;
+
+    int sms = 0;
+    GMP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ordinal));
+    out->sm_count = (uint32_t)sms;
+
+    t0 = now_ns();
+    GMP_CUDA(cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking));
+    GMP_CUDA(cudaEventCreate(&r.ev[0]));
+    GMP_CUDA(cudaEventCreate(&r.ev[1]));
+    GMP_CUDA(cudaMalloc(&r.a, o.bytes));
+    const bool want_copy = !(o.flags & GMP_HBM_F_SKIP_COPY);
+    if (want_copy) GMP_CUDA(cudaMalloc(&r.b, o.bytes));
+    GMP_CUDA(cudaMalloc(&r.acc, 4 * sizeof(unsigned long long)));
+    out->ns_alloc = now_ns() - t0;
+    out->d2h_bytes = 0;
+    out->h2d_bytes = 0;
+
+    Series wr, rd, cp;
+    const uint64_t tk0 = now_ns();
+    bool first = true;
+    int last_pattern = GMP_PAT_SPLITMIX;
+    uint64_t last_seed = o.seed;
+    for (int pat = 0; pat < GMP_PAT_COUNT; ++pat) {
+        if (!(o.pattern_mask & (1u << pat))) continue;
+        for (uint32_t it = 0; it < o.iters; ++it) {
+            uint64_t seed = o.seed + it;
+            if (pat == GMP_PAT_ADDRESS) seed = reinterpret_cast<uint64_t>(r.a);
+            PassCtx c{&r, r.a, nullptr, (size_t)o.bytes, pat, seed};
+            const uint64_t tf = now_ns();
+            float ms = 0.f;
+            int rc = timed(r, do_write, &c, &ms);
+            if (rc != GMP_OK) return rc;
+            wr.add((double)o.bytes, ms);
+            rc = timed(r, do_verify, &c, &ms);
+            if (rc != GMP_OK) return rc;
+            rd.add((double)o.bytes, ms);
+            gmp_verify_result v;
+            rc = fetch_acc(r, &v);
+            if (rc != GMP_OK) return rc;
+            out->d2h_bytes += 32;
+            note_verify(out, v, pat);
+            if (first) {
+                out->ns_first_kernel = now_ns() - tf;
+                first = false;
+            }
+            last_pattern = pat;
+            last_seed = seed;
+        }
+        out->patterns_run |= 1u << pat;
+    }
+    if (want_copy) {
+        // buffer A still holds (last_pattern, last_seed); copy it and verify the copy
+        const uint32_t reps = o.iters;
+        for (uint32_t it = 0; it < reps; ++it) {
+            PassCtx c{&r, r.b, r.a, (size_t)o.bytes, last_pattern, last_seed};
+            float ms = 0.f;
+            int rc = timed(r, do_copy, &c, &ms);
+            if (rc != GMP_OK) return rc;
+            cp.add(2.0 * (double)o.bytes, ms);
+        }
+        PassCtx c{&r, r.b, nullptr, (size_t)o.bytes, last_pattern, last_seed};
+        float ms = 0.f;
+        int rc = timed(r, do_verify, &c, &ms);
+        if (rc != GMP_OK) return rc;
+        rd.add((double)o.bytes, ms);
+        gmp_verify_result v;
+        rc = fetch_acc(r, &v);
+        if (rc != GMP_OK) return rc;
+        out->d2h_bytes += 32;
+        note_verify(out, v, last_pattern);
+    }
+    out->ns_kernels = now_ns() - tk0;
+    out->write_gbs_best = wr.best();
+    out->write_gbs_median = wr.median();
+    out->read_gbs_best = rd.best();
+    out->read_gbs_median = rd.median();
+    out->copy_gbs_best = cp.best();
+    out->copy_gbs_median = cp.median();
+
+    // host <-> device DMA round trip through pinned memory: proves the PCIe/BAR
+    // mappings of the freshly mounted device work, both directions.
+    if (o.dma_bytes != 0) {
+        const uint64_t td = now_ns();
+        const size_t nb = (size_t)std::min<uint64_t>(o.dma_bytes, o.bytes) & ~(size_t)15;
+        if (nb != 0) {
+            GMP_CUDA(cudaHostAlloc(&r.pinned, nb, cudaHostAllocDefault));
+            uint64_t* h = static_cast<uint64_t*>(r.pinned);
+            const uint64_t lanes = nb / 16;
+            const uint64_t s_up = o.seed ^ 0x5851F42D4C957F2Dull, s_down = o.seed ^ 0x14057B7EF767814Full;
+            for (uint64_t L = 0; L < lanes; ++L) host_lane_words(GMP_PAT_SPLITMIX, s_up, L, h[2 * L], h[2 * L + 1]);
+            float ms = 0.f;
+            GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
+            GMP_CUDA(cudaMemcpyAsync(r.a, r.pinned, nb, cudaMemcpyHostToDevice, r.stream));
+            GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+            GMP_CUDA(cudaEventSynchronize(r.ev[1]));
+            GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
+            out->h2d_gbs = ms > 0.f ? (double)nb / (ms * 1e-3) / 1e9 : 0.0;
+            out->h2d_bytes += nb;
+            GMP_CUDA(launch_verify(r.a, nb, GMP_PAT_SPLITMIX, s_up, r.acc, r.stream));
+            gmp_verify_result v;
+            int rc = fetch_acc(r, &v);
+            if (rc != GMP_OK) return rc;
+            out->d2h_bytes += 32;
+            note_verify(out, v, GMP_PAT_SPLITMIX);
+            GMP_CUDA(launch_write(r.a, nb, GMP_PAT_SPLITMIX, s_down, r.stream));
+            GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
+            GMP_CUDA(cudaMemcpyAsync(r.pinned, r.a, nb, cudaMemcpyDeviceToHost, r.stream));
+            GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+            GMP_CUDA(cudaEventSynchronize(r.ev[1]));
+            GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
+            out->d2h_gbs = ms > 0.f ? (double)nb / (ms * 1e-3) / 1e9 : 0.0;
+            out->d2h_bytes += nb;
+            uint64_t bad = 0, first_bad = ~0ull;
+            for (uint64_t L = 0; L < lanes; ++L) {
+                uint64_t e0, e1;
+                host_lane_words(GMP_PAT_SPLITMIX, s_down, L, e0, e1);
+                if (h[2 * L] != e0 || h[2 * L + 1] != e1) {
+                    if (bad == 0) first_bad = L;
+                    ++bad;
+                }
+            }
+            if (bad != 0) {
+                gmp_verify_result hv{bad, first_bad, 0, 0};
+                const uint64_t kx = out->xor64, ks = out->sum64;
+                note_verify(out, hv, GMP_PAT_SPLITMIX);
+                out->xor64 = kx;
+                out->sum64 = ks;
+            }
+        }
+        out->ns_dma = now_ns() - td;
+    }
+    return GMP_OK;
+}
+
+}  // namespace
+
+extern "C" int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out) {
+    clear_error();
+    if (out == nullptr) {
+        set_error("out is NULL");
+        return GMP_ERR_INVALID;
+    }
+    memset(out, 0, sizeof(*out));
+    out->first_bad_lane = ~0ull;
+    out->first_bad_pattern = -1;
+    out->cuda_ordinal = -1;
+
+    gmp_hbm_opts o;
+    memset(&o, 0, sizeof(o));
+    if (opts != nullptr) o = *opts;
+    if (o.bytes == 0) o.bytes = GMP_HBM_DEFAULT_BYTES;
+    if (o.iters == 0) o.iters = 3;
+    if (o.pattern_mask == 0) o.pattern_mask = 1u << GMP_PAT_SPLITMIX;
+    if (o.seed == 0) o.seed = kGamma;
+    if (o.dma_bytes == UINT64_MAX) o.dma_bytes = GMP_HBM_DEFAULT_DMA_BYTES;
+    if (o.pattern_mask >> GMP_PAT_COUNT) {
+        set_error("pattern_mask 0x%x names unknown patterns", o.pattern_mask);
+        return out->status = GMP_ERR_INVALID;
+    }
+    out->bytes = o.bytes;
+    out->iters = o.iters;
+
+    const uint64_t t_begin = now_ns();
+    int ordinal = -1;
+    int rc = find_cuda_device(uuid, &ordinal, nullptr);
+    out->ns_select_device = now_ns() - t_begin;
+    if (rc != GMP_OK) return out->status = rc;
+    out->cuda_ordinal = ordinal;
+    {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, ordinal) == cudaSuccess)
+            format_uuid(reinterpret_cast<const unsigned char*>(prop.uuid.bytes), out->uuid);
+    }
+
+    int prev = -1;
+    (void)cudaGetDevice(&prev);
+    ProbeResources res;
+    rc = run_probe(ordinal, o, out, res);
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));
+
+    const uint64_t tt = now_ns();
+    if (rc != GMP_OK && rc != GMP_ERR_UNAVAILABLE) (void)cudaGetLastError();
+    res.release();
+    if (!(o.flags & GMP_HBM_F_KEEP_DEVICE)) {
+        // leave no context, allocation or mapping behind on the probed device
+        (void)cudaDeviceReset();
+    }
+    if (prev >= 0 && prev != ordinal) (void)cudaSetDevice(prev);
+    out->ns_teardown = now_ns() - tt;
+    out->ns_total = now_ns() - t_begin;
+    memcpy(g_err, keep, sizeof(keep));
+
+    if (rc == GMP_OK && out->mismatch_lanes != 0) {
+        set_error("%llu mismatching 16-byte lanes, first at lane %llu (pattern %d)",
+                  (unsigned long long)out->mismatch_lanes, (unsigned long long)out->first_bad_lane,
+                  out->first_bad_pattern);
+        rc = GMP_ERR_VERIFY;
+    }
+    return out->status = rc;
+}

@@ -1,0 +1,553 @@
+// HBM probe kernels for NVIDIA B200 (sm_100a): pattern write, read-verify, copy.
+//
+// All three are pure streaming kernels bound by HBM3e bandwidth (0 reuse, a few
+// integer ops per 16 bytes), so the design rules are the memory ones:
+//   * every global access is a 16-byte vector (one warp instruction = 512
+//     contiguous bytes = four full 128-byte lines);
+//   * each thread keeps UNROLL independent 16-byte requests in flight before it
+//     touches any of them (memory-level parallelism hides the ~600-cycle DRAM
+//     latency);
+//   * a CTA walks contiguous THREADS*UNROLL*16-byte tiles (4-16 KiB), and the
+//     grid is persistent: (SM count) x (CTAs per SM) CTAs stride over the tiles,
+//     so the launch is exactly one wave on all 148 SMs;
+//   * streaming cache hints keep the 126 MB L2 from being polluted by data that
+//     is never re-read;
+//   * the verify kernel folds mismatch count, first bad lane and two checksums
+//     in registers, reduces with warp shuffles and shared memory, and issues four
+//     atomics per CTA (<= a few thousand per launch).
+//
+// Algorithmic bytes per launch (used for every GB/s figure): write = N,
+// verify = N, copy = 2N for an N-byte buffer.
+//
+// There is no reference counterpart (the reference has no device code); the CPU
+// statement of the same arithmetic used by the tests is oracle/gmo_pattern.c.
+
+#include "gmp_internal.h"
+
+#include <atomic>
+#include <stdlib.h>
+#include <string_view>
+
+namespace gmp {
+
+// ---- cache-hinted 16-byte accesses --------------------------------------------
+enum { HINT_DEFAULT = 0, HINT_STREAM = 1, HINT_NOALLOC = 2 };
+
+template <int HINT>
+__device__ __forceinline__ void st16(uint4* p, const uint4& v) {
+    if (HINT == HINT_STREAM) {
+        __stcs(p, v);  // st.global.cs: evict-first, the line is never read again by this kernel
+    } else if (HINT == HINT_NOALLOC) {
+        asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y),
+                     "r"(v.z), "r"(v.w)
+                     : "memory");
+    } else {
+        *p = v;
+    }
+}
+
+// Loads are deliberately NOT volatile: the scheduler must be free to hoist all
+// UNROLL loads of a tile above the first use (front-batched LDG.128s).
+template <int HINT>
+__device__ __forceinline__ uint4 ld16(const uint4* p) {
+    if (HINT == HINT_STREAM) {
+        return __ldcs(p);  // ld.global.cs
+    } else if (HINT == HINT_NOALLOC) {
+        uint4 v;
+        asm("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+            : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+            : "l"(p));
+        return v;
+    } else {
+        return *p;
+    }
+}
+
+__device__ __forceinline__ uint4 pack(uint64_t w0, uint64_t w1) {
+    return make_uint4((uint32_t)w0, (uint32_t)(w0 >> 32), (uint32_t)w1, (uint32_t)(w1 >> 32));
+}
+
+// ---- write --------------------------------------------------------------------
+template <int PAT, int THREADS, int UNROLL, int HINT>
+__global__ void __launch_bounds__(THREADS) k_hbm_write_pattern(uint4* __restrict__ dst, uint64_t nlanes,
+                                                               uint32_t tail_bytes, uint64_t seed) {
+    constexpr uint64_t kTile = (uint64_t)THREADS * UNROLL;
+    const uint64_t ntiles = (nlanes + kTile - 1) / kTile;
+    for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const uint64_t base = t * kTile + threadIdx.x;
+        if (base + (uint64_t)(UNROLL - 1) * THREADS < nlanes) {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const uint64_t L = base + (uint64_t)j * THREADS;
+                uint64_t w0, w1;
+                lane_words<PAT>(seed, L, w0, w1);
+                st16<HINT>(dst + L, pack(w0, w1));
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const uint64_t L = base + (uint64_t)j * THREADS;
+                if (L < nlanes) {
+                    uint64_t w0, w1;
+                    lane_words<PAT>(seed, L, w0, w1);
+                    st16<HINT>(dst + L, pack(w0, w1));
+                }
+            }
+        }
+    }
+    // ragged last lane: its leading tail_bytes bytes, written by one thread
+    if (tail_bytes != 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+        uint64_t w0, w1;
+        lane_words<PAT>(seed, nlanes, w0, w1);
+        unsigned char* p = reinterpret_cast<unsigned char*>(dst + nlanes);
+        for (uint32_t b = 0; b < tail_bytes; ++b) {
+            const uint64_t w = (b < 8) ? w0 : w1;
+            p[b] = (unsigned char)(w >> (8 * (b & 7)));
+        }
+    }
+}
+
+// ---- read + verify --------------------------------------------------------------
+// acc[0] += mismatching lanes; acc[1] = max(UINT64_MAX - bad lane) (0 = none);
+// acc[2] ^= words; acc[3] += words.  All four combine commutatively, so the
+// result is independent of CTA scheduling and bit-exact against the oracle.
+__device__ __forceinline__ uint64_t shfl_xor64(uint64_t v, int m) {
+    uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, m);
+    uint32_t hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), m);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+template <int THREADS>
+__device__ __forceinline__ void block_fold_and_publish(uint64_t bad, uint64_t inv_first, uint64_t x, uint64_t s,
+                                                       unsigned long long* __restrict__ acc) {
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+        bad += shfl_xor64(bad, m);
+        const uint64_t o = shfl_xor64(inv_first, m);
+        inv_first = o > inv_first ? o : inv_first;
+        x ^= shfl_xor64(x, m);
+        s += shfl_xor64(s, m);
+    }
+    constexpr int kWarps = THREADS / 32;
+    __shared__ uint64_t sh[4][kWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        sh[0][warp] = bad;
+        sh[1][warp] = inv_first;
+        sh[2][warp] = x;
+        sh[3][warp] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        bad = lane < kWarps ? sh[0][lane] : 0;
+        inv_first = lane < kWarps ? sh[1][lane] : 0;
+        x = lane < kWarps ? sh[2][lane] : 0;
+        s = lane < kWarps ? sh[3][lane] : 0;
+#pragma unroll
+        for (int m = 16; m > 0; m >>= 1) {
+            bad += shfl_xor64(bad, m);
+            const uint64_t o = shfl_xor64(inv_first, m);
+            inv_first = o > inv_first ? o : inv_first;
+            x ^= shfl_xor64(x, m);
+            s += shfl_xor64(s, m);
+        }
+        if (lane == 0) {
+            if (bad) atomicAdd(acc + 0, (unsigned long long)bad);
+            if (inv_first) atomicMax(acc + 1, (unsigned long long)inv_first);
+            atomicXor(acc + 2, (unsigned long long)x);
+            atomicAdd(acc + 3, (unsigned long long)s);
+        }
+    }
+}
+
+template <int PAT>
+__device__ __forceinline__ void check_lane(const uint4& v, uint64_t seed, uint64_t L, uint64_t& bad,
+                                           uint64_t& inv_first, uint64_t& x, uint64_t& s) {
+    uint64_t e0, e1;
+    lane_words<PAT>(seed, L, e0, e1);
+    const uint64_t g0 = ((uint64_t)v.y << 32) | v.x;
+    const uint64_t g1 = ((uint64_t)v.w << 32) | v.z;
+    x ^= g0 ^ g1;
+    s += g0 + g1;
+    if ((g0 ^ e0) | (g1 ^ e1)) {
+        bad += 1;
+        const uint64_t inv = ~0ull - L;
+        inv_first = inv > inv_first ? inv : inv_first;
+    }
+}
+
+template <int PAT, int THREADS, int UNROLL, int HINT>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS) k_hbm_read_verify(const uint4* __restrict__ src, uint64_t nlanes,
+                                                             uint32_t tail_bytes, uint64_t seed,
+                                                             unsigned long long* __restrict__ acc) {
+    constexpr uint64_t kTile = (uint64_t)THREADS * UNROLL;
+    const uint64_t ntiles = (nlanes + kTile - 1) / kTile;
+    uint64_t bad = 0, inv_first = 0, x = 0, s = 0;
+    for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const uint64_t base = t * kTile + threadIdx.x;
+        if (base + (uint64_t)(UNROLL - 1) * THREADS < nlanes) {
+            uint4 v[UNROLL];
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) v[j] = ld16<HINT>(src + base + (uint64_t)j * THREADS);
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j)
+                check_lane<PAT>(v[j], seed, base + (uint64_t)j * THREADS, bad, inv_first, x, s);
+        } else {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const uint64_t L = base + (uint64_t)j * THREADS;
+                if (L < nlanes) {
+                    const uint4 v = ld16<HINT>(src + L);
+                    check_lane<PAT>(v, seed, L, bad, inv_first, x, s);
+                }
+            }
+        }
+    }
+    if (tail_bytes != 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+        // ragged last lane: compare its leading bytes, checksum them zero-padded
+        uint64_t e0, e1;
+        lane_words<PAT>(seed, nlanes, e0, e1);
+        const unsigned char* p = reinterpret_cast<const unsigned char*>(src + nlanes);
+        uint64_t g0 = 0, g1 = 0;
+        for (uint32_t b = 0; b < tail_bytes; ++b) {
+            const uint64_t byte = p[b];
+            if (b < 8)
+                g0 |= byte << (8 * b);
+            else
+                g1 |= byte << (8 * (b - 8));
+        }
+        const uint64_t m0 = tail_bytes >= 8 ? ~0ull : ((1ull << (8 * tail_bytes)) - 1);
+        const uint64_t m1 = tail_bytes <= 8 ? 0ull : ((1ull << (8 * (tail_bytes - 8))) - 1);
+        x ^= g0 ^ g1;
+        s += g0 + g1;
+        if (((g0 ^ e0) & m0) | ((g1 ^ e1) & m1)) {
+            bad += 1;
+            const uint64_t inv = ~0ull - nlanes;
+            inv_first = inv > inv_first ? inv : inv_first;
+        }
+    }
+    block_fold_and_publish<THREADS>(bad, inv_first, x, s, acc);
+}
+
+// ---- copy -----------------------------------------------------------------------
+template <int THREADS, int UNROLL, int HINT>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS) k_hbm_copy(uint4* __restrict__ dst, const uint4* __restrict__ src,
+                                                      uint64_t nlanes, uint32_t tail_bytes) {
+    constexpr uint64_t kTile = (uint64_t)THREADS * UNROLL;
+    const uint64_t ntiles = (nlanes + kTile - 1) / kTile;
+    for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const uint64_t base = t * kTile + threadIdx.x;
+        if (base + (uint64_t)(UNROLL - 1) * THREADS < nlanes) {
+            uint4 v[UNROLL];
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) v[j] = ld16<HINT>(src + base + (uint64_t)j * THREADS);
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) st16<HINT>(dst + base + (uint64_t)j * THREADS, v[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const uint64_t L = base + (uint64_t)j * THREADS;
+                if (L < nlanes) st16<HINT>(dst + L, ld16<HINT>(src + L));
+            }
+        }
+    }
+    if (tail_bytes != 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+        const unsigned char* sp = reinterpret_cast<const unsigned char*>(src + nlanes);
+        unsigned char* dp = reinterpret_cast<unsigned char*>(dst + nlanes);
+        for (uint32_t b = 0; b < tail_bytes; ++b) dp[b] = sp[b];
+    }
+}
+
+__global__ void k_hbm_corrupt(unsigned char* p, size_t off, unsigned char mask) { p[off] ^= mask; }
+
+// ---- launch geometry --------------------------------------------------------------
+Tunables& tunables() {
+    static Tunables t = {/*write_ctas_per_sm*/ 8, /*read*/ 4, /*copy*/ 4, /*write_variant*/ 1, /*read_variant*/ 1,
+                         /*copy_variant*/ 1};
+    return t;
+}
+
+cudaError_t current_device_info(DeviceInfo* info) {
+    static std::atomic<int> sm_cache[GMP_MAX_DEVICES * 4];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    int sms = 0;
+    const bool cacheable = dev >= 0 && dev < GMP_MAX_DEVICES * 4;
+    if (cacheable) sms = sm_cache[dev].load(std::memory_order_relaxed);
+    if (sms == 0) {
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        if (cacheable) sm_cache[dev].store(sms, std::memory_order_relaxed);
+    }
+    info->ordinal = dev;
+    info->sm_count = sms;
+    return cudaSuccess;
+}
+
+static unsigned grid_for(uint64_t nlanes, uint64_t tile, int sm_count, int ctas_per_sm) {
+    uint64_t ntiles = (nlanes + tile - 1) / tile;
+    if (ntiles == 0) ntiles = 1;  // still one CTA for the ragged tail
+    uint64_t g = (uint64_t)sm_count * (uint64_t)(ctas_per_sm > 0 ? ctas_per_sm : 1);
+    return (unsigned)(ntiles < g ? ntiles : g);
+}
+
+// Variant table: (THREADS, UNROLL, HINT).  Variant 1 is the default picked by the
+// sweep recorded in profiles/; the others stay selectable through gmp_tune() so
+// that the sweep can be re-run on new silicon.
+#define GMP_VARIANTS(X) \
+    X(0, 256, 4, HINT_DEFAULT) \
+    X(1, 256, 4, HINT_STREAM)  \
+    X(2, 256, 8, HINT_STREAM)  \
+    X(3, 512, 4, HINT_STREAM)  \
+    X(4, 256, 4, HINT_NOALLOC) \
+    X(5, 256, 8, HINT_NOALLOC) \
+    X(6, 512, 2, HINT_STREAM)  \
+    X(7, 128, 8, HINT_STREAM)
+
+template <int PAT>
+static cudaError_t launch_write_pat(uint4* dst, uint64_t nlanes, uint32_t tail, uint64_t seed, int sm_count,
+                                    cudaStream_t s) {
+    const Tunables& tn = tunables();
+    switch (tn.write_variant) {
+#define X(ID, T, U, H)                                                                           \
+    case ID:                                                                                     \
+        k_hbm_write_pattern<PAT, T, U, H>                                                        \
+            <<<grid_for(nlanes, (uint64_t)T * U, sm_count, tn.write_ctas_per_sm), T, 0, s>>>(dst, nlanes, tail, seed); \
+        break;
+        GMP_VARIANTS(X)
+#undef X
+        default:
+            return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+template <int PAT>
+static cudaError_t launch_verify_pat(const uint4* src, uint64_t nlanes, uint32_t tail, uint64_t seed,
+                                     unsigned long long* acc, int sm_count, cudaStream_t s) {
+    const Tunables& tn = tunables();
+    switch (tn.read_variant) {
+#define X(ID, T, U, H)                                                                          \
+    case ID:                                                                                    \
+        k_hbm_read_verify<PAT, T, U, H>                                                         \
+            <<<grid_for(nlanes, (uint64_t)T * U, sm_count, tn.read_ctas_per_sm), T, 0, s>>>(src, nlanes, tail, seed, acc); \
+        break;
+        GMP_VARIANTS(X)
+#undef X
+        default:
+            return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+#define GMP_PATTERN_SWITCH(pattern, CALL)        \
+    switch (pattern) {                           \
+        case GMP_PAT_SPLITMIX:                   \
+            return CALL(GMP_PAT_SPLITMIX);       \
+        case GMP_PAT_ZERO:                       \
+            return CALL(GMP_PAT_ZERO);           \
+        case GMP_PAT_ONES:                       \
+            return CALL(GMP_PAT_ONES);           \
+        case GMP_PAT_CHECKER:                    \
+            return CALL(GMP_PAT_CHECKER);        \
+        case GMP_PAT_ADDRESS:                    \
+            return CALL(GMP_PAT_ADDRESS);        \
+        default:                                 \
+            return cudaErrorInvalidValue;        \
+    }
+
+cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, cudaStream_t s) {
+    if (bytes == 0) return cudaSuccess;
+    DeviceInfo di;
+    cudaError_t e = current_device_info(&di);
+    if (e != cudaSuccess) return e;
+    const uint64_t nlanes = bytes / 16;
+    const uint32_t tail = (uint32_t)(bytes % 16);
+#define CALL(P) launch_write_pat<P>(static_cast<uint4*>(dptr), nlanes, tail, seed, di.sm_count, s)
+    GMP_PATTERN_SWITCH(pattern, CALL)
+#undef CALL
+}
+
+cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed, unsigned long long* d_acc,
+                          cudaStream_t s) {
+    if (pattern < 0 || pattern >= GMP_PAT_COUNT) return cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(d_acc, 0, 4 * sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return e;
+    if (bytes == 0) return cudaSuccess;
+    DeviceInfo di;
+    e = current_device_info(&di);
+    if (e != cudaSuccess) return e;
+    const uint64_t nlanes = bytes / 16;
+    const uint32_t tail = (uint32_t)(bytes % 16);
+#define CALL(P) launch_verify_pat<P>(static_cast<const uint4*>(dptr), nlanes, tail, seed, d_acc, di.sm_count, s)
+    GMP_PATTERN_SWITCH(pattern, CALL)
+#undef CALL
+}
+
+cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s) {
+    if (bytes == 0) return cudaSuccess;
+    DeviceInfo di;
+    cudaError_t e = current_device_info(&di);
+    if (e != cudaSuccess) return e;
+    const uint64_t nlanes = bytes / 16;
+    const uint32_t tail = (uint32_t)(bytes % 16);
+    const Tunables& tn = tunables();
+    switch (tn.copy_variant) {
+#define X(ID, T, U, H)                                                                      \
+    case ID:                                                                                \
+        k_hbm_copy<T, U, H><<<grid_for(nlanes, (uint64_t)T * U, di.sm_count, tn.copy_ctas_per_sm), T, 0, s>>>( \
+            static_cast<uint4*>(dst), static_cast<const uint4*>(src), nlanes, tail);         \
+        break;
+        GMP_VARIANTS(X)
+#undef X
+        default:
+            return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+void decode_acc(const unsigned long long raw[4], gmp_verify_result* out) {
+    out->mismatch_lanes = raw[0];
+    out->first_bad_lane = raw[1] ? (~0ull - raw[1]) : ~0ull;
+    out->xor64 = raw[2];
+    out->sum64 = raw[3];
+}
+
+void host_lane_words(int pattern, uint64_t seed, uint64_t L, uint64_t& w0, uint64_t& w1) {
+    switch (pattern) {
+        case GMP_PAT_SPLITMIX: lane_words<GMP_PAT_SPLITMIX>(seed, L, w0, w1); break;
+        case GMP_PAT_ZERO: lane_words<GMP_PAT_ZERO>(seed, L, w0, w1); break;
+        case GMP_PAT_ONES: lane_words<GMP_PAT_ONES>(seed, L, w0, w1); break;
+        case GMP_PAT_CHECKER: lane_words<GMP_PAT_CHECKER>(seed, L, w0, w1); break;
+        default: lane_words<GMP_PAT_ADDRESS>(seed, L, w0, w1); break;
+    }
+}
+
+}  // namespace gmp
+
+// ---- C ABI: section 3 of gpumounter_probe.h ----------------------------------------
+using namespace gmp;
+
+static int check_buffer(const void* p, size_t bytes, int pattern) {
+    if (pattern < 0 || pattern >= GMP_PAT_COUNT) {
+        set_error("unknown pattern %d", pattern);
+        return GMP_ERR_INVALID;
+    }
+    if (bytes != 0 && p == nullptr) {
+        set_error("NULL device pointer with bytes=%zu", bytes);
+        return GMP_ERR_INVALID;
+    }
+    if ((reinterpret_cast<uintptr_t>(p) & 15u) != 0) {
+        set_error("device pointer %p is not 16-byte aligned", p);
+        return GMP_ERR_INVALID;
+    }
+    return GMP_OK;
+}
+
+extern "C" int gmp_hbm_write_pattern(void* dptr, size_t bytes, int pattern, uint64_t seed, void* stream) {
+    clear_error();
+    int rc = check_buffer(dptr, bytes, pattern);
+    if (rc != GMP_OK) return rc;
+    GMP_CUDA(launch_write(dptr, bytes, pattern, seed, static_cast<cudaStream_t>(stream)));
+    return GMP_OK;
+}
+
+extern "C" int gmp_hbm_read_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed, gmp_verify_result* out,
+                                   void* stream) {
+    clear_error();
+    if (out == nullptr) {
+        set_error("out is NULL");
+        return GMP_ERR_INVALID;
+    }
+    int rc = check_buffer(dptr, bytes, pattern);
+    if (rc != GMP_OK) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // scratch: the 32-byte device accumulator the kernel reduces into
+    unsigned long long* d_acc = nullptr;
+    GMP_CUDA(cudaMalloc(&d_acc, 4 * sizeof(unsigned long long)));
+    unsigned long long raw[4] = {0, 0, 0, 0};
+    cudaError_t e = launch_verify(dptr, bytes, pattern, seed, d_acc, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(raw, d_acc, sizeof(raw), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaError_t ef = cudaFree(d_acc);
+    if (e != cudaSuccess) return cuda_fail(e, "gmp_hbm_read_verify");
+    if (ef != cudaSuccess) return cuda_fail(ef, "cudaFree(accumulator)");
+    decode_acc(raw, out);
+    return GMP_OK;
+}
+
+extern "C" int gmp_hbm_copy(void* dst, const void* src, size_t bytes, void* stream) {
+    clear_error();
+    int rc = check_buffer(dst, bytes, 0);
+    if (rc == GMP_OK) rc = check_buffer(src, bytes, 0);
+    if (rc != GMP_OK) return rc;
+    GMP_CUDA(launch_copy(dst, src, bytes, static_cast<cudaStream_t>(stream)));
+    return GMP_OK;
+}
+
+extern "C" int gmp_hbm_corrupt(void* dptr, size_t bytes, size_t byte_offset, uint8_t mask, void* stream) {
+    clear_error();
+    if (dptr == nullptr || byte_offset >= bytes) {
+        set_error("corrupt: offset %zu outside buffer of %zu bytes", byte_offset, bytes);
+        return GMP_ERR_INVALID;
+    }
+    k_hbm_corrupt<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned char*>(dptr), byte_offset, mask);
+    GMP_CUDA(cudaGetLastError());
+    return GMP_OK;
+}
+
+extern "C" int gmp_hbm_read_verify_async(const void* dptr, size_t bytes, int pattern, uint64_t seed, void* d_acc,
+                                         void* stream) {
+    clear_error();
+    if (d_acc == nullptr || (reinterpret_cast<uintptr_t>(d_acc) & 7u) != 0) {
+        set_error("d_acc must be 32 bytes of 8-byte-aligned device memory");
+        return GMP_ERR_INVALID;
+    }
+    int rc = check_buffer(dptr, bytes, pattern);
+    if (rc != GMP_OK) return rc;
+    GMP_CUDA(launch_verify(dptr, bytes, pattern, seed, static_cast<unsigned long long*>(d_acc),
+                           static_cast<cudaStream_t>(stream)));
+    return GMP_OK;
+}
+
+extern "C" int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, void* stream) {
+    clear_error();
+    if (d_acc == nullptr || out == nullptr) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    unsigned long long raw[4];
+    GMP_CUDA(cudaMemcpyAsync(raw, d_acc, sizeof(raw), cudaMemcpyDeviceToHost, s));
+    GMP_CUDA(cudaStreamSynchronize(s));
+    decode_acc(raw, out);
+    return GMP_OK;
+}
+
+extern "C" int gmp_tune(const char* knob, int value) {
+    clear_error();
+    if (knob == nullptr) return GMP_ERR_INVALID;
+    Tunables& t = tunables();
+    int* slot = nullptr;
+    int limit = 64;
+    const std::string_view k(knob);
+    if (k == "write_ctas_per_sm") slot = &t.write_ctas_per_sm;
+    else if (k == "read_ctas_per_sm") slot = &t.read_ctas_per_sm;
+    else if (k == "copy_ctas_per_sm") slot = &t.copy_ctas_per_sm;
+    else if (k == "write_variant") { slot = &t.write_variant; limit = 7; }
+    else if (k == "read_variant") { slot = &t.read_variant; limit = 7; }
+    else if (k == "copy_variant") { slot = &t.copy_variant; limit = 7; }
+    if (slot == nullptr) {
+        set_error("unknown knob '%s'", knob);
+        return GMP_ERR_INVALID;
+    }
+    if (value >= 0) {
+        if (value > limit || (limit == 64 && value == 0)) {
+            set_error("knob '%s': value %d out of range", knob, value);
+            return GMP_ERR_INVALID;
+        }
+        *slot = value;
+    }
+    return *slot;
+}

@@ -1,0 +1,245 @@
+// NVML enumeration, per-GPU process list and P2P status through a dlopen'ed
+// libnvidia-ml.so.1.  B200-era replacement for the reference's cgo binding
+// (ref: pkg/util/gpu/collector/nvml/{bindings.go,nvml.go,nvml_dl.go}) and its
+// callers GetGPUInfo (ref: pkg/util/gpu/collector/collector.go:40-79) and
+// GetRunningProcess (ref: pkg/device/nvidia.go:58-87).
+
+#include "gmp_nvml.h"
+
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+namespace gmp {
+void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+void clear_error();
+
+int NvmlSession::open() {
+    if (handle_ != nullptr) return GMP_OK;
+    const char* name = getenv("GPUMOUNTER_NVML_LIB");
+    if (name == nullptr || name[0] == '\0') name = "libnvidia-ml.so.1";  // ref: nvml_dl.go:30
+    void* h = dlopen(name, RTLD_LAZY | RTLD_LOCAL);
+    if (h == nullptr) {
+        set_error("could not load NVML library (%s)", dlerror());  // ref: bindings.go:53-55
+        return GMP_ERR_NVML_NOT_FOUND;
+    }
+    struct Sym {
+        void** slot;
+        const char* name;
+        bool required;
+    };
+    const Sym syms[] = {
+        {(void**)&Init, "nvmlInit_v2", true},
+        {(void**)&Shutdown, "nvmlShutdown", true},
+        {(void**)&ErrorString, "nvmlErrorString", true},
+        {(void**)&DeviceGetCount, "nvmlDeviceGetCount_v2", true},
+        {(void**)&DeviceGetHandleByIndex, "nvmlDeviceGetHandleByIndex_v2", true},
+        {(void**)&DeviceGetHandleByUUID, "nvmlDeviceGetHandleByUUID", true},
+        {(void**)&DeviceGetMinorNumber, "nvmlDeviceGetMinorNumber", true},
+        {(void**)&DeviceGetUUID, "nvmlDeviceGetUUID", true},
+        {(void**)&DeviceGetPciInfo, "nvmlDeviceGetPciInfo_v3", false},
+        {(void**)&DeviceGetP2PStatus, "nvmlDeviceGetP2PStatus", false},
+        {(void**)&DeviceGetNvLinkState, "nvmlDeviceGetNvLinkState", false},
+        {(void**)&DeviceGetComputeRunningProcesses, "nvmlDeviceGetComputeRunningProcesses_v3", false},
+        {(void**)&DeviceGetGraphicsRunningProcesses, "nvmlDeviceGetGraphicsRunningProcesses_v3", false},
+        {(void**)&SystemGetDriverVersion, "nvmlSystemGetDriverVersion", false},
+        {(void**)&SystemGetNVMLVersion, "nvmlSystemGetNVMLVersion", false},
+    };
+    for (const Sym& s : syms) {
+        *s.slot = dlsym(h, s.name);
+        if (*s.slot == nullptr && s.required) {
+            set_error("could not load NVML library (%s lacks %s)", name, s.name);
+            dlclose(h);
+            return GMP_ERR_NVML_NOT_FOUND;
+        }
+    }
+    nvmlReturn_t r = Init();
+    if (r != NVML_SUCCESS) {
+        handle_ = h;
+        int rc = fail(r, "nvmlInit_v2");
+        handle_ = nullptr;
+        dlclose(h);
+        return rc;
+    }
+    handle_ = h;
+    return GMP_OK;
+}
+
+void NvmlSession::close() {
+    if (handle_ == nullptr) return;
+    if (Shutdown) (void)Shutdown();
+    dlclose(handle_);
+    handle_ = nullptr;
+}
+
+int NvmlSession::fail(nvmlReturn_t r, const char* what) const {
+    const char* s = ErrorString ? ErrorString(r) : "unknown";
+    set_error("nvml: %s (%s)", s, what);  // ref: bindings.go:47-48
+    return GMP_ERR_NVML;
+}
+
+}  // namespace gmp
+
+using namespace gmp;
+
+#define GMP_NVML(sess, call, what)                       \
+    do {                                                 \
+        nvmlReturn_t r__ = (call);                       \
+        if (r__ != NVML_SUCCESS) return (sess).fail(r__, what); \
+    } while (0)
+
+extern "C" int gmp_enumerate_nvml(gmp_device* out, int cap, int* n) {
+    clear_error();
+    if (out == nullptr || n == nullptr || cap < 0) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    *n = 0;
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    unsigned int count = 0;
+    GMP_NVML(nv, nv.DeviceGetCount(&count), "nvmlDeviceGetCount_v2");
+    if ((int)count > cap) {
+        *n = (int)count;
+        set_error("%u NVML devices, capacity %d", count, cap);
+        return GMP_ERR_BUFFER_TOO_SMALL;
+    }
+    // index order, minor then UUID, exactly as ref: collector.go:56-77
+    for (unsigned int i = 0; i < count; ++i) {
+        nvmlDevice_t dev;
+        GMP_NVML(nv, nv.DeviceGetHandleByIndex(i, &dev), "nvmlDeviceGetHandleByIndex_v2");
+        gmp_device& d = out[i];
+        memset(&d, 0, sizeof(d));
+        unsigned int minor = 0;
+        GMP_NVML(nv, nv.DeviceGetMinorNumber(dev, &minor), "nvmlDeviceGetMinorNumber");
+        GMP_NVML(nv, nv.DeviceGetUUID(dev, d.uuid, GMP_UUID_LEN), "nvmlDeviceGetUUID");
+        d.minor = minor;
+        d.nvml_index = (int32_t)i;
+        d.cuda_ordinal = -1;
+        if (nv.DeviceGetPciInfo) {
+            nvmlPciInfo_t pci;
+            memset(&pci, 0, sizeof(pci));
+            if (nv.DeviceGetPciInfo(dev, &pci) == NVML_SUCCESS) snprintf(d.pci_bus_id, GMP_PCI_LEN, "%s", pci.busId);
+        }
+    }
+    *n = (int)count;
+    return GMP_OK;
+}
+
+extern "C" int gmp_nvml_versions(char* driver, size_t driver_cap, char* nvml, size_t nvml_cap) {
+    clear_error();
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    if (driver != nullptr && driver_cap > 0) {
+        driver[0] = '\0';
+        if (nv.SystemGetDriverVersion)
+            GMP_NVML(nv, nv.SystemGetDriverVersion(driver, (unsigned)driver_cap), "nvmlSystemGetDriverVersion");
+    }
+    if (nvml != nullptr && nvml_cap > 0) {
+        nvml[0] = '\0';
+        if (nv.SystemGetNVMLVersion)
+            GMP_NVML(nv, nv.SystemGetNVMLVersion(nvml, (unsigned)nvml_cap), "nvmlSystemGetNVMLVersion");
+    }
+    return GMP_OK;
+}
+
+extern "C" int gmp_gpu_running_processes(const char* uuid, gmp_process_info* out, int cap, int* n) {
+    clear_error();
+    if (uuid == nullptr || n == nullptr || cap < 0 || (cap > 0 && out == nullptr)) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    *n = 0;
+    NvmlSession nv;  // init -> by-UUID -> graphics + compute -> shutdown, ref: nvidia.go:58-87
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    nvmlDevice_t dev;
+    GMP_NVML(nv, nv.DeviceGetHandleByUUID(uuid, &dev), "nvmlDeviceGetHandleByUUID");
+    if (!nv.DeviceGetGraphicsRunningProcesses || !nv.DeviceGetComputeRunningProcesses) {
+        set_error("nvml: running-process queries not exported by this NVML");
+        return GMP_ERR_NVML;
+    }
+    // The reference sizes both queries at 1024 entries (ref: nvidia.go:74,80).
+    std::vector<nvmlProcessInfo_t> procs(1024);
+    int total = 0;
+    for (int pass = 0; pass < 2; ++pass) {  // graphics first, then compute (ref: nvidia.go:74-86)
+        unsigned int count = (unsigned)procs.size();
+        nvmlReturn_t r = pass == 0 ? nv.DeviceGetGraphicsRunningProcesses(dev, &count, procs.data())
+                                   : nv.DeviceGetComputeRunningProcesses(dev, &count, procs.data());
+        if (r != NVML_SUCCESS)
+            return nv.fail(r, pass == 0 ? "nvmlDeviceGetGraphicsRunningProcesses" : "nvmlDeviceGetComputeRunningProcesses");
+        for (unsigned int i = 0; i < count; ++i) {
+            if (total < cap) {
+                out[total].pid = procs[i].pid;
+                out[total].used_gpu_memory = procs[i].usedGpuMemory;
+            }
+            ++total;
+        }
+    }
+    *n = total;
+    if (total > cap) {
+        set_error("%d GPU processes, capacity %d", total, cap);
+        return GMP_ERR_BUFFER_TOO_SMALL;
+    }
+    return GMP_OK;
+}
+
+extern "C" int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_index, int32_t* status) {
+    clear_error();
+    if (uuids == nullptr || status == nullptr || n <= 0 || n > GMP_MAX_DEVICES) {
+        set_error("bad argument (n=%d)", n);
+        return GMP_ERR_INVALID;
+    }
+    if (caps_index < 0 || caps_index > (int)NVML_P2P_CAPS_INDEX_PCI) {
+        set_error("unknown P2P caps index %d", caps_index);
+        return GMP_ERR_INVALID;
+    }
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    if (!nv.DeviceGetP2PStatus) {
+        set_error("nvml: nvmlDeviceGetP2PStatus not exported by this NVML");
+        return GMP_ERR_NVML;
+    }
+    nvmlDevice_t dev[GMP_MAX_DEVICES];
+    for (int i = 0; i < n; ++i) GMP_NVML(nv, nv.DeviceGetHandleByUUID(uuids[i], &dev[i]), "nvmlDeviceGetHandleByUUID");
+    for (int i = 0; i < n; ++i) {
+        for (int j = 0; j < n; ++j) {
+            if (i == j) {
+                status[i * n + j] = NVML_P2P_STATUS_OK;
+                continue;
+            }
+            nvmlGpuP2PStatus_t st = NVML_P2P_STATUS_UNKNOWN;
+            GMP_NVML(nv, nv.DeviceGetP2PStatus(dev[i], dev[j], (nvmlGpuP2PCapsIndex_t)caps_index, &st),
+                     "nvmlDeviceGetP2PStatus");
+            status[i * n + j] = (int32_t)st;
+        }
+    }
+    return GMP_OK;
+}
+
+extern "C" int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* max_links) {
+    clear_error();
+    if (uuid == nullptr || active_links == nullptr) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    *active_links = 0;
+    if (max_links) *max_links = NVML_NVLINK_MAX_LINKS;
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    nvmlDevice_t dev;
+    GMP_NVML(nv, nv.DeviceGetHandleByUUID(uuid, &dev), "nvmlDeviceGetHandleByUUID");
+    if (!nv.DeviceGetNvLinkState) return GMP_OK;
+    for (unsigned int l = 0; l < NVML_NVLINK_MAX_LINKS; ++l) {
+        nvmlEnableState_t st = NVML_FEATURE_DISABLED;
+        if (nv.DeviceGetNvLinkState(dev, l, &st) == NVML_SUCCESS && st == NVML_FEATURE_ENABLED) ++*active_links;
+    }
+    return GMP_OK;
+}

@@ -1,0 +1,241 @@
+"""The post-mount probe: ctypes mirror of sections 2-5 of include/gpumounter_probe.h.
+
+No reference counterpart (the reference never touches the device it mounts); the hook
+point is right after the mount loop, ref: pkg/server/gpu-mount/server.go:97-98.
+"""
+
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+from . import _lib
+from ._lib import ProbeError, check, lib
+
+GMP_UUID_LEN = 96
+GMP_PCI_LEN = 32
+GMP_MAX_DEVICES = 16
+
+PAT_SPLITMIX, PAT_ZERO, PAT_ONES, PAT_CHECKER, PAT_ADDRESS = range(5)
+PAT_COUNT = 5
+PATTERN_NAMES = ("splitmix", "zero", "ones", "checker", "address")
+
+HBM_F_SKIP_COPY = 1 << 0
+HBM_F_KEEP_DEVICE = 1 << 1
+UINT64_MAX = (1 << 64) - 1
+
+
+class gmp_device(ctypes.Structure):
+    _fields_ = [
+        ("uuid", ctypes.c_char * GMP_UUID_LEN),
+        ("minor", ctypes.c_uint32),
+        ("pci_bus_id", ctypes.c_char * GMP_PCI_LEN),
+        ("nvml_index", ctypes.c_int32),
+        ("cuda_ordinal", ctypes.c_int32),
+    ]
+
+
+class gmp_verify_result(ctypes.Structure):
+    _fields_ = [
+        ("mismatch_lanes", ctypes.c_uint64),
+        ("first_bad_lane", ctypes.c_uint64),
+        ("xor64", ctypes.c_uint64),
+        ("sum64", ctypes.c_uint64),
+    ]
+
+
+class gmp_hbm_opts(ctypes.Structure):
+    _fields_ = [
+        ("bytes", ctypes.c_uint64),
+        ("iters", ctypes.c_uint32),
+        ("pattern_mask", ctypes.c_uint32),
+        ("seed", ctypes.c_uint64),
+        ("dma_bytes", ctypes.c_uint64),
+        ("flags", ctypes.c_uint32),
+        ("reserved", ctypes.c_uint32),
+    ]
+
+
+class gmp_hbm_result(ctypes.Structure):
+    _fields_ = [
+        ("uuid", ctypes.c_char * GMP_UUID_LEN),
+        ("cuda_ordinal", ctypes.c_int32),
+        ("status", ctypes.c_int32),
+        ("bytes", ctypes.c_uint64),
+        ("iters", ctypes.c_uint32),
+        ("patterns_run", ctypes.c_uint32),
+        ("write_gbs_best", ctypes.c_double),
+        ("write_gbs_median", ctypes.c_double),
+        ("read_gbs_best", ctypes.c_double),
+        ("read_gbs_median", ctypes.c_double),
+        ("copy_gbs_best", ctypes.c_double),
+        ("copy_gbs_median", ctypes.c_double),
+        ("h2d_gbs", ctypes.c_double),
+        ("d2h_gbs", ctypes.c_double),
+        ("mismatch_lanes", ctypes.c_uint64),
+        ("first_bad_lane", ctypes.c_uint64),
+        ("first_bad_pattern", ctypes.c_int32),
+        ("sm_count", ctypes.c_uint32),
+        ("xor64", ctypes.c_uint64),
+        ("sum64", ctypes.c_uint64),
+        ("h2d_bytes", ctypes.c_uint64),
+        ("d2h_bytes", ctypes.c_uint64),
+        ("ns_select_device", ctypes.c_uint64),
+        ("ns_context", ctypes.c_uint64),
+        ("ns_alloc", ctypes.c_uint64),
+        ("ns_first_kernel", ctypes.c_uint64),
+        ("ns_kernels", ctypes.c_uint64),
+        ("ns_dma", ctypes.c_uint64),
+        ("ns_teardown", ctypes.c_uint64),
+        ("ns_total", ctypes.c_uint64),
+    ]
+
+    def as_dict(self) -> dict:
+        d = {}
+        for name, _ in self._fields_:
+            v = getattr(self, name)
+            d[name] = v.decode() if isinstance(v, bytes) else v
+        return d
+
+
+@dataclass
+class Device:
+    uuid: str
+    minor: Optional[int]
+    pci_bus_id: str
+    nvml_index: int
+    cuda_ordinal: int
+
+
+@dataclass
+class VerifyResult:
+    mismatch_lanes: int
+    first_bad_lane: int
+    xor64: int
+    sum64: int
+
+    @property
+    def ok(self) -> bool:
+        return self.mismatch_lanes == 0
+
+
+def _devices(arr, n) -> List[Device]:
+    out = []
+    for i in range(n):
+        d = arr[i]
+        out.append(
+            Device(
+                uuid=d.uuid.decode(),
+                minor=None if d.minor == 0xFFFFFFFF else int(d.minor),
+                pci_bus_id=d.pci_bus_id.decode(),
+                nvml_index=int(d.nvml_index),
+                cuda_ordinal=int(d.cuda_ordinal),
+            )
+        )
+    return out
+
+
+def _to_c_devices(devs: Sequence[Device]):
+    arr = (gmp_device * max(1, len(devs)))()
+    for i, d in enumerate(devs):
+        arr[i].uuid = d.uuid.encode()
+        arr[i].minor = 0xFFFFFFFF if d.minor is None else d.minor
+        arr[i].pci_bus_id = d.pci_bus_id.encode()
+        arr[i].nvml_index = d.nvml_index
+        arr[i].cuda_ordinal = d.cuda_ordinal
+    return arr
+
+
+def abi_version() -> int:
+    return lib().gmp_abi_version()
+
+
+def enumerate_nvml() -> List[Device]:
+    """NVML enumeration in index order (ref: pkg/util/gpu/collector/collector.go:40-79)."""
+    arr = (gmp_device * GMP_MAX_DEVICES)()
+    n = ctypes.c_int(0)
+    check(lib().gmp_enumerate_nvml(arr, GMP_MAX_DEVICES, ctypes.byref(n)), "gmp_enumerate_nvml")
+    return _devices(arr, n.value)
+
+
+def enumerate_cuda() -> List[Device]:
+    arr = (gmp_device * GMP_MAX_DEVICES)()
+    n = ctypes.c_int(0)
+    check(lib().gmp_enumerate_cuda(arr, GMP_MAX_DEVICES, ctypes.byref(n)), "gmp_enumerate_cuda")
+    return _devices(arr, n.value)
+
+
+def device_sets_equal(a: Sequence[Device], b: Sequence[Device]) -> bool:
+    rc = lib().gmp_device_sets_equal(_to_c_devices(a), len(a), _to_c_devices(b), len(b))
+    if rc == _lib.GMP_ERR_DEVICE_SET:
+        return False
+    check(rc, "gmp_device_sets_equal")
+    return True
+
+
+def _ptr(p) -> ctypes.c_void_p:
+    return ctypes.c_void_p(int(p))
+
+
+def hbm_write_pattern(dptr: int, nbytes: int, pattern: int = PAT_SPLITMIX, seed: int = 0, stream: int = 0) -> None:
+    f = lib().gmp_hbm_write_pattern
+    f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64, ctypes.c_void_p]
+    check(f(_ptr(dptr), nbytes, pattern, seed & UINT64_MAX, _ptr(stream)), "gmp_hbm_write_pattern")
+
+
+def hbm_read_verify(dptr: int, nbytes: int, pattern: int = PAT_SPLITMIX, seed: int = 0, stream: int = 0) -> VerifyResult:
+    f = lib().gmp_hbm_read_verify
+    f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64,
+                  ctypes.POINTER(gmp_verify_result), ctypes.c_void_p]
+    r = gmp_verify_result()
+    check(f(_ptr(dptr), nbytes, pattern, seed & UINT64_MAX, ctypes.byref(r), _ptr(stream)), "gmp_hbm_read_verify")
+    return VerifyResult(r.mismatch_lanes, r.first_bad_lane, r.xor64, r.sum64)
+
+
+def hbm_read_verify_async(dptr: int, nbytes: int, pattern: int, seed: int, d_acc: int, stream: int = 0) -> None:
+    f = lib().gmp_hbm_read_verify_async
+    f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
+    check(f(_ptr(dptr), nbytes, pattern, seed & UINT64_MAX, _ptr(d_acc), _ptr(stream)), "gmp_hbm_read_verify_async")
+
+
+def hbm_verify_fetch(d_acc: int, stream: int = 0) -> VerifyResult:
+    f = lib().gmp_hbm_verify_fetch
+    f.argtypes = [ctypes.c_void_p, ctypes.POINTER(gmp_verify_result), ctypes.c_void_p]
+    r = gmp_verify_result()
+    check(f(_ptr(d_acc), ctypes.byref(r), _ptr(stream)), "gmp_hbm_verify_fetch")
+    return VerifyResult(r.mismatch_lanes, r.first_bad_lane, r.xor64, r.sum64)
+
+
+def hbm_copy(dst: int, src: int, nbytes: int, stream: int = 0) -> None:
+    f = lib().gmp_hbm_copy
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    check(f(_ptr(dst), _ptr(src), nbytes, _ptr(stream)), "gmp_hbm_copy")
+
+
+def hbm_corrupt(dptr: int, nbytes: int, byte_offset: int, mask: int, stream: int = 0) -> None:
+    f = lib().gmp_hbm_corrupt
+    f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_uint8, ctypes.c_void_p]
+    check(f(_ptr(dptr), nbytes, byte_offset, mask, _ptr(stream)), "gmp_hbm_corrupt")
+
+
+def tune(knob: str, value: int = -1) -> int:
+    f = lib().gmp_tune
+    f.argtypes = [ctypes.c_char_p, ctypes.c_int]
+    return check(f(knob.encode(), value), "gmp_tune")
+
+
+def probe_hbm(uuid: Optional[str] = None, *, nbytes: int = 0, iters: int = 0, pattern_mask: int = 0, seed: int = 0,
+              dma_bytes: int = UINT64_MAX, flags: int = 0, raise_on_error: bool = True) -> gmp_hbm_result:
+    """One-shot probe of one mounted GPU (see gmp_probe_hbm in the header)."""
+    f = lib().gmp_probe_hbm
+    f.argtypes = [ctypes.c_char_p, ctypes.POINTER(gmp_hbm_opts), ctypes.POINTER(gmp_hbm_result)]
+    o = gmp_hbm_opts(nbytes, iters, pattern_mask, seed & UINT64_MAX, dma_bytes, flags, 0)
+    r = gmp_hbm_result()
+    rc = f(uuid.encode() if uuid else None, ctypes.byref(o), ctypes.byref(r))
+    if raise_on_error:
+        check(rc, "gmp_probe_hbm")
+    return r
+
+
+__all__ = [n for n in dir() if not n.startswith("_")] + ["ProbeError"]

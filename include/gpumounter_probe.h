@@ -1,0 +1,281 @@
+/*
+ * gpumounter_probe.h — C ABI of libgpumounter_probe.so
+ *
+ * The post-mount GPU probe and the native node-local mount path for GPUMounter,
+ * built for NVIDIA B200 (sm_100a).  Everything behind this header is C++/CUDA;
+ * nothing in the signatures is a C++ or torch type, so the library binds from
+ * Go (cgo), Python (ctypes) or C alike.  INTEGRATION.md shows the cgo stub and
+ * the hook in the worker.
+ *
+ * "ref:" citations are paths inside the GPUMounter reference tree
+ * (jason-gideon/GPUMounter) naming the interface an entry point replaces or
+ * extends.  The reference has no GPU compute path; the probe entry points
+ * (sections 3-5) are additive and hang off the worker's AddGPU handler right
+ * after its mount loop (ref: pkg/server/gpu-mount/server.go:80-98).
+ *
+ * Conventions (same shape as the reference's cgo->NVML seam,
+ * ref: pkg/util/gpu/collector/nvml/bindings.go:19-57, nvml.go:17-119):
+ *   - every function returns GMP_OK (0) or a negative GMP_ERR_* code; nothing
+ *     throws or aborts across the ABI; gmp_strerror() names a code and
+ *     gmp_last_error() gives this thread's detail string;
+ *   - all buffers are caller-owned and fixed-size; the library never hands out
+ *     memory the caller has to free;
+ *   - the library loads on a box with no NVIDIA driver (CUDA runtime is linked
+ *     statically and opens libcuda.so.1 lazily; NVML is dlopen'ed at call time,
+ *     ref: pkg/util/gpu/collector/nvml/nvml_dl.go:29-36).  On such a box every
+ *     GPU entry point returns GMP_ERR_UNAVAILABLE — there is NO CPU fallback.
+ *   - thread-safe for calls on distinct devices; calls that name the same
+ *     device serialise on the device like any CUDA work.
+ */
+#ifndef GPUMOUNTER_PROBE_H_
+#define GPUMOUNTER_PROBE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GMP_ABI_VERSION 1
+
+/* The library is built with -fvisibility=hidden; only GMP_API symbols are exported. */
+#if defined(__GNUC__)
+#define GMP_API __attribute__((visibility("default")))
+#else
+#define GMP_API
+#endif
+
+/* ------------------------------------------------------------------------- */
+/* 1. Status codes                                                            */
+/* ------------------------------------------------------------------------- */
+enum {
+    GMP_OK                   = 0,
+    GMP_ERR_INVALID          = -1,  /* bad argument (NULL, misaligned, unknown pattern, size over a stated limit) */
+    GMP_ERR_UNAVAILABLE      = -2,  /* no CUDA driver / no usable GPU on this box */
+    GMP_ERR_NO_DEVICE        = -3,  /* UUID / ordinal does not name a visible device */
+    GMP_ERR_CUDA             = -4,  /* a CUDA call failed; see gmp_last_error() */
+    GMP_ERR_NVML             = -5,  /* an NVML call failed; message is "nvml: <nvmlErrorString>" (ref: bindings.go:43-49) */
+    GMP_ERR_NVML_NOT_FOUND   = -6,  /* "could not load NVML library" (ref: bindings.go:51-57) */
+    GMP_ERR_VERIFY           = -7,  /* the probe ran but read back data that differs from the pattern */
+    GMP_ERR_NOMEM            = -8,  /* device or host allocation failed */
+    GMP_ERR_SYS              = -9,  /* a system call failed (errno in gmp_last_error()) */
+    GMP_ERR_BUFFER_TOO_SMALL = -10, /* caller buffer/capacity too small; required size is reported where possible */
+    GMP_ERR_DEVICE_SET       = -11, /* CUDA-visible (UUID) set differs from the expected / NVML set */
+    GMP_ERR_P2P_MATRIX       = -12, /* cudaDeviceCanAccessPeer matrix differs from NVML's P2P status matrix */
+    GMP_ERR_CGROUP_DRIVER    = -13, /* "unsupported cgroup driver: <x>" (ref: pkg/util/cgroup/cgroup.go:78-84) */
+    GMP_ERR_NAME             = -14, /* invalid character in a cgroup name component (ref: cgroup.go:37-39, a Go panic there) */
+    GMP_ERR_EMPTY_CGROUP     = -15, /* cgroup.procs has no complete line (ref: util.go:50 indexes pids[0] and panics) */
+    GMP_ERR_TARGET           = -16, /* "Target must be specified" (ref: pkg/util/namespace/namespace.go:71-73) */
+    GMP_ERR_BUSY             = -17, /* GPU has processes of the pod and force is off (ref: util.go:106-109) */
+    GMP_ERR_NODE_CTL         = -18, /* /dev/nvidiactl missing or not openable from the probing context */
+    GMP_ERR_NODE_UVM         = -19, /* /dev/nvidia-uvm missing or not openable */
+    GMP_ERR_NODE_GPU         = -20, /* /dev/nvidiaN missing */
+    GMP_ERR_NODE_DENIED      = -21, /* /dev/nvidiaN exists but open() is refused (device cgroup) */
+    GMP_ERR_DRIVER_LIB       = -22  /* libcuda.so.1 not resolvable from the probing context */
+};
+
+GMP_API int         gmp_abi_version(void);
+GMP_API const char* gmp_strerror(int code);
+/* Detail text of the last failure on the calling thread (never NULL). */
+GMP_API const char* gmp_last_error(void);
+
+/* ------------------------------------------------------------------------- */
+/* 2. Device enumeration                                                      */
+/* ------------------------------------------------------------------------- */
+#define GMP_UUID_LEN    96  /* = NVML_DEVICE_UUID_V2_BUFFER_SIZE, ref: bindings.go:38 */
+#define GMP_PCI_LEN     32
+#define GMP_MAX_DEVICES 16
+
+typedef struct gmp_device {
+    char     uuid[GMP_UUID_LEN];    /* exactly the string nvmlDeviceGetUUID returns, "GPU-xxxxxxxx-xxxx-..." */
+    uint32_t minor;                 /* /dev/nvidia<minor>; UINT32_MAX when not known (CUDA-side enumeration) */
+    char     pci_bus_id[GMP_PCI_LEN];
+    int32_t  nvml_index;            /* -1 when not known */
+    int32_t  cuda_ordinal;          /* -1 when not known */
+} gmp_device;
+
+/*
+ * NVML enumeration in NVML index order: for i in [0,count) handle-by-index ->
+ * minor number -> UUID.  Replaces GPUCollector.GetGPUInfo
+ * (ref: pkg/util/gpu/collector/collector.go:40-79) and the cgo wrappers it
+ * calls (ref: pkg/util/gpu/collector/nvml/nvml.go:17-31,83-110).  The NVML
+ * library name is "libnvidia-ml.so.1" (ref: nvml_dl.go:30) unless the
+ * environment variable GPUMOUNTER_NVML_LIB names another file (used by the
+ * tests to load a fake).  NVML is initialised and shut down inside the call,
+ * as the reference does (ref: collector.go:43-47).
+ */
+GMP_API int gmp_enumerate_nvml(gmp_device* out, int cap, int* n);
+
+/* The devices CUDA sees in this process, ordinal order, UUID in NVML's format. */
+GMP_API int gmp_enumerate_cuda(gmp_device* out, int cap, int* n);
+
+/*
+ * (UUID, minor) set equality between two enumerations, never by index
+ * (CUDA ordinals and NVML indices differ).  minor is compared only where both
+ * sides know it.  GMP_OK or GMP_ERR_DEVICE_SET.
+ */
+GMP_API int gmp_device_sets_equal(const gmp_device* a, int na, const gmp_device* b, int nb);
+
+/* Driver and NVML version strings (ref: pkg/util/gpu/collector/nvml/nvml.go:83-100; 80-byte buffers there). */
+GMP_API int gmp_nvml_versions(char* driver, size_t driver_cap, char* nvml, size_t nvml_cap);
+
+typedef struct gmp_process_info {
+    uint32_t pid;              /* host PID (the worker runs with hostPID) */
+    uint32_t reserved;
+    uint64_t used_gpu_memory;  /* ref: nvml.go:12-15 ProcessInfo{Pid, UsedGPUMemory} */
+} gmp_process_info;
+
+/*
+ * Processes running on one GPU: NVML init -> handle by UUID -> graphics
+ * processes, then compute processes, appended in that order -> shutdown.
+ * Replaces NvidiaGPU.GetRunningProcess (ref: pkg/device/nvidia.go:58-87) and
+ * the two cgo wrappers (ref: nvml.go:33-73).  *n receives the total found;
+ * GMP_ERR_BUFFER_TOO_SMALL when it exceeds cap.
+ */
+GMP_API int gmp_gpu_running_processes(const char* uuid, gmp_process_info* out, int cap, int* n);
+
+/*
+ * NVML's view of peer-to-peer capability between the n GPUs named by UUID:
+ * status[i*n+j] = nvmlDeviceGetP2PStatus(i, j, caps_index) for i != j, 0 (OK)
+ * on the diagonal.  caps_index: 0 READ, 1 WRITE, 2 NVLINK, 3 ATOMICS, 4 PCI;
+ * status 0 = NVML_P2P_STATUS_OK.  No reference counterpart (its vendored
+ * nvml.h declares the call, ref: lib/nvml.h:2663, but nothing uses it).
+ */
+GMP_API int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_index, int32_t* status);
+
+/* Number of NVLink links NVML reports enabled on the GPU (18 on an HGX B200). */
+GMP_API int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* max_links);
+
+/* ------------------------------------------------------------------------- */
+/* 3. HBM probe kernels on caller-owned DEVICE memory (current CUDA device)   */
+/* ------------------------------------------------------------------------- */
+/*
+ * No reference counterpart: the reference never touches device memory
+ * (SURVEY.md 2.3).  These are the sm_100a kernels of the post-mount probe.
+ *
+ * Pattern "v1", defined on 16-byte lanes L = 0,1,2,... of the buffer, two
+ * little-endian u64 words per lane (w0 at byte 16L, w1 at byte 16L+8):
+ *   GMP_PAT_SPLITMIX : w0 = the L-th output of the canonical SplitMix64 stream
+ *                      seeded with `seed` = mix(seed + (L+1)*0x9E3779B97F4A7C15);
+ *                      w1 = ~rotl64(w0,32) ^ L
+ *   GMP_PAT_ZERO     : w0 = w1 = 0
+ *   GMP_PAT_ONES     : w0 = w1 = ~0
+ *   GMP_PAT_CHECKER  : even L: 0xAAAA...AA, odd L: 0x5555...55; inverted when seed&1
+ *   GMP_PAT_ADDRESS  : w0 = seed + 16L, w1 = seed + 16L + 8 (address-in-address;
+ *                      pass the buffer's device address as seed)
+ * A buffer whose size is not a multiple of 16 ends in a ragged lane holding
+ * the leading bytes of that lane's pattern.  The base pointer must be 16-byte
+ * aligned; bytes == 0 is a successful no-op.
+ *
+ * `stream` is a cudaStream_t passed as void* (NULL = the legacy default
+ * stream).  write/copy are asynchronous on that stream; read_verify returns
+ * after its result has reached the host struct.
+ */
+enum {
+    GMP_PAT_SPLITMIX = 0,
+    GMP_PAT_ZERO     = 1,
+    GMP_PAT_ONES     = 2,
+    GMP_PAT_CHECKER  = 3,
+    GMP_PAT_ADDRESS  = 4,
+    GMP_PAT_COUNT    = 5
+};
+
+typedef struct gmp_verify_result {
+    uint64_t mismatch_lanes;  /* 16-byte lanes (ragged last lane included) with any differing byte */
+    uint64_t first_bad_lane;  /* smallest such lane index; UINT64_MAX when none */
+    uint64_t xor64;           /* XOR of all little-endian u64 words READ (last word zero-padded) */
+    uint64_t sum64;           /* their sum modulo 2^64 */
+} gmp_verify_result;
+
+GMP_API int gmp_hbm_write_pattern(void* dptr, size_t bytes, int pattern, uint64_t seed, void* stream);
+GMP_API int gmp_hbm_read_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed,
+                        gmp_verify_result* out, void* stream);
+GMP_API int gmp_hbm_copy(void* dst, const void* src, size_t bytes, void* stream);
+/*
+ * The same verify pass without the host round trip: `d_acc` is 32 bytes of
+ * 8-byte-aligned DEVICE memory owned by the caller, cleared and then reduced
+ * into on `stream`; gmp_hbm_verify_fetch() copies it back, waits for the
+ * stream and decodes it.  Lets a caller queue write/verify/copy passes back to
+ * back and read the verdicts once.
+ */
+GMP_API int gmp_hbm_read_verify_async(const void* dptr, size_t bytes, int pattern, uint64_t seed,
+                              void* d_acc, void* stream);
+GMP_API int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, void* stream);
+/* Fault injection for tests: XOR one byte of device memory with `mask`. */
+GMP_API int gmp_hbm_corrupt(void* dptr, size_t bytes, size_t byte_offset, uint8_t mask, void* stream);
+/*
+ * Benchmarking knob, process-wide, not for production callers: selects the
+ * launch geometry of the three kernels.  Knobs: "write_ctas_per_sm",
+ * "read_ctas_per_sm", "copy_ctas_per_sm", "write_variant", "read_variant",
+ * "copy_variant".  value < 0 only queries.  Returns the value in force
+ * (>= 0) or GMP_ERR_INVALID.
+ */
+GMP_API int gmp_tune(const char* knob, int value);
+
+/* ------------------------------------------------------------------------- */
+/* 4. One-shot HBM probe of one mounted GPU                                   */
+/* ------------------------------------------------------------------------- */
+/*
+ * Called by the worker after util.MountGPU succeeded for the device
+ * (ref: pkg/server/gpu-mount/server.go:80-98; the *NvidiaGPU it holds carries
+ * the UUID, ref: pkg/device/nvidia.go:10-17).  Selects the device by UUID,
+ * allocates two `bytes`-sized buffers, and per selected pattern runs
+ * write -> read-verify (iters times), then one copy pass + verify of the
+ * copy, then an optional host<->device DMA round trip, and frees everything.
+ * Bandwidths use algorithmic bytes: write = bytes, verify = bytes,
+ * copy = 2*bytes.
+ */
+#define GMP_HBM_DEFAULT_BYTES      (8ull << 30)
+#define GMP_HBM_DEFAULT_DMA_BYTES  (64ull << 20)
+
+typedef struct gmp_hbm_opts {
+    uint64_t bytes;         /* per buffer; 0 -> GMP_HBM_DEFAULT_BYTES */
+    uint32_t iters;         /* timed write+verify repetitions per pattern; 0 -> 3 */
+    uint32_t pattern_mask;  /* bit k selects GMP_PAT_k; 0 -> SPLITMIX only */
+    uint64_t seed;          /* 0 -> 0x9E3779B97F4A7C15; iteration i uses seed + i */
+    uint64_t dma_bytes;     /* pinned host<->device round trip; 0 -> skip; UINT64_MAX -> default */
+    uint32_t flags;         /* GMP_HBM_F_* */
+    uint32_t reserved;
+} gmp_hbm_opts;
+
+enum {
+    GMP_HBM_F_SKIP_COPY   = 1u << 0,
+    GMP_HBM_F_KEEP_DEVICE = 1u << 1   /* do not cudaDeviceReset() at the end (in-process callers that share the context) */
+};
+
+typedef struct gmp_hbm_result {
+    char     uuid[GMP_UUID_LEN];
+    int32_t  cuda_ordinal;
+    int32_t  status;             /* same value the call returned */
+    uint64_t bytes;              /* per buffer, as probed */
+    uint32_t iters;
+    uint32_t patterns_run;       /* mask */
+    double   write_gbs_best,  write_gbs_median;
+    double   read_gbs_best,   read_gbs_median;
+    double   copy_gbs_best,   copy_gbs_median;
+    double   h2d_gbs, d2h_gbs;   /* DMA round trip; 0 when skipped */
+    uint64_t mismatch_lanes;     /* summed over every verify pass, DMA included */
+    uint64_t first_bad_lane;     /* of the first failing pass; UINT64_MAX when none */
+    int32_t  first_bad_pattern;  /* -1 when none */
+    uint32_t sm_count;
+    uint64_t xor64, sum64;       /* of the last SPLITMIX verify pass (or last pass run) */
+    uint64_t h2d_bytes, d2h_bytes; /* bytes actually moved over PCIe by the call */
+    /* phase wall times, ns, CLOCK_MONOTONIC */
+    uint64_t ns_select_device;   /* cudaGetDeviceCount + UUID match + cudaSetDevice */
+    uint64_t ns_context;         /* primary-context creation (cudaFree(0)) */
+    uint64_t ns_alloc;
+    uint64_t ns_first_kernel;    /* first write+verify pass, launch to verified result */
+    uint64_t ns_kernels;         /* all timed passes */
+    uint64_t ns_dma;
+    uint64_t ns_teardown;
+    uint64_t ns_total;
+} gmp_hbm_result;
+
+/* uuid == NULL or "" probes CUDA ordinal 0. */
+GMP_API int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUMOUNTER_PROBE_H_ */
