@@ -30,36 +30,69 @@
 
 namespace gmp {
 
-// ---- cache-hinted 16-byte accesses --------------------------------------------
-enum { HINT_DEFAULT = 0, HINT_STREAM = 1, HINT_NOALLOC = 2 };
+// ---- cache-hinted vector accesses ------------------------------------------------
+// A "chunk" is VEC adjacent 16-byte lanes moved by ONE instruction: VEC=1 is the
+// classic 128-bit LDG/STG, VEC=2 is Blackwell's 256-bit LDG.E.256 / STG.E.256
+// (sm_100+, needs 32-byte alignment), which halves the LSU instruction count.
+enum { HINT_DEFAULT = 0, HINT_STREAM = 1, HINT_NOALLOC = 2, HINT_L2EF = 3 };
 
-template <int HINT>
-__device__ __forceinline__ void st16(uint4* p, const uint4& v) {
-    if (HINT == HINT_STREAM) {
-        __stcs(p, v);  // st.global.cs: evict-first, the line is never read again by this kernel
-    } else if (HINT == HINT_NOALLOC) {
-        asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y),
-                     "r"(v.z), "r"(v.w)
-                     : "memory");
+// Loads are deliberately NOT volatile: the scheduler must be free to hoist all
+// UNROLL loads of a tile above the first use (front-batched LDGs = memory-level
+// parallelism).  Stores are volatile + "memory" so they are never elided.
+#define GMP_LD128(QUAL)                                                                       \
+    asm("ld.global" QUAL ".v4.u32 {%0, %1, %2, %3}, [%4];"                                    \
+        : "=r"(v[0].x), "=r"(v[0].y), "=r"(v[0].z), "=r"(v[0].w)                             \
+        : "l"(p))
+#define GMP_ST128(QUAL)                                                                       \
+    asm volatile("st.global" QUAL ".v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v[0].x),   \
+                 "r"(v[0].y), "r"(v[0].z), "r"(v[0].w)                                        \
+                 : "memory")
+#define GMP_LD256(QUAL)                                                                       \
+    do {                                                                                      \
+        uint64_t a__, b__, c__, d__;                                                          \
+        asm("ld.global" QUAL ".v4.u64 {%0, %1, %2, %3}, [%4];"                                \
+            : "=l"(a__), "=l"(b__), "=l"(c__), "=l"(d__)                                      \
+            : "l"(p));                                                                        \
+        v[0] = make_uint4((uint32_t)a__, (uint32_t)(a__ >> 32), (uint32_t)b__, (uint32_t)(b__ >> 32)); \
+        v[1] = make_uint4((uint32_t)c__, (uint32_t)(c__ >> 32), (uint32_t)d__, (uint32_t)(d__ >> 32)); \
+    } while (0)
+#define GMP_ST256(QUAL)                                                                       \
+    do {                                                                                      \
+        const uint64_t a__ = ((uint64_t)v[0].y << 32) | v[0].x, b__ = ((uint64_t)v[0].w << 32) | v[0].z; \
+        const uint64_t c__ = ((uint64_t)v[1].y << 32) | v[1].x, d__ = ((uint64_t)v[1].w << 32) | v[1].z; \
+        asm volatile("st.global" QUAL ".v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(p), "l"(a__), "l"(b__), \
+                     "l"(c__), "l"(d__)                                                       \
+                     : "memory");                                                             \
+    } while (0)
+
+template <int VEC, int HINT>
+__device__ __forceinline__ void ld_chunk(const uint4* p, uint4 (&v)[VEC]) {
+    static_assert(VEC == 1 || VEC == 2, "chunk is 16 or 32 bytes");
+    if (VEC == 1) {
+        if (HINT == HINT_STREAM) GMP_LD128(".cs");
+        else if (HINT == HINT_NOALLOC) GMP_LD128(".nc.L1::no_allocate");
+        else if (HINT == HINT_L2EF) GMP_LD128(".cs");  // L2::evict_first exists for 256-bit accesses only
+        else GMP_LD128("");
     } else {
-        *p = v;
+        if (HINT == HINT_STREAM) GMP_LD256(".cs");
+        else if (HINT == HINT_NOALLOC) GMP_LD256(".nc.L1::no_allocate");
+        else if (HINT == HINT_L2EF) GMP_LD256(".L2::evict_first");
+        else GMP_LD256("");
     }
 }
 
-// Loads are deliberately NOT volatile: the scheduler must be free to hoist all
-// UNROLL loads of a tile above the first use (front-batched LDG.128s).
-template <int HINT>
-__device__ __forceinline__ uint4 ld16(const uint4* p) {
-    if (HINT == HINT_STREAM) {
-        return __ldcs(p);  // ld.global.cs
-    } else if (HINT == HINT_NOALLOC) {
-        uint4 v;
-        asm("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-            : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-            : "l"(p));
-        return v;
+template <int VEC, int HINT>
+__device__ __forceinline__ void st_chunk(uint4* p, const uint4 (&v)[VEC]) {
+    if (VEC == 1) {
+        if (HINT == HINT_STREAM) GMP_ST128(".cs");
+        else if (HINT == HINT_NOALLOC) GMP_ST128(".L1::no_allocate");
+        else if (HINT == HINT_L2EF) GMP_ST128(".cs");
+        else GMP_ST128("");
     } else {
-        return *p;
+        if (HINT == HINT_STREAM) GMP_ST256(".cs");
+        else if (HINT == HINT_NOALLOC) GMP_ST256(".L1::no_allocate");
+        else if (HINT == HINT_L2EF) GMP_ST256(".L2::evict_first");
+        else GMP_ST256("");
     }
 }
 
@@ -67,44 +100,63 @@ __device__ __forceinline__ uint4 pack(uint64_t w0, uint64_t w1) {
     return make_uint4((uint32_t)w0, (uint32_t)(w0 >> 32), (uint32_t)w1, (uint32_t)(w1 >> 32));
 }
 
+template <int PAT>
+__device__ __forceinline__ void write_tail(uint4* dst, uint64_t nlanes, uint32_t tail_bytes, uint64_t seed) {
+    // ragged last lane: its leading tail_bytes bytes, written by one thread
+    uint64_t w0, w1;
+    lane_words<PAT>(seed, nlanes, w0, w1);
+    unsigned char* p = reinterpret_cast<unsigned char*>(dst + nlanes);
+    for (uint32_t b = 0; b < tail_bytes; ++b) {
+        const uint64_t w = (b < 8) ? w0 : w1;
+        p[b] = (unsigned char)(w >> (8 * (b & 7)));
+    }
+}
+
+// Tile walk shared by the three kernels.  A tile is THREADS*UNROLL chunks; thread t
+// owns chunks t, t+THREADS, ... of the tile, so every warp instruction touches
+// 32*VEC*16 contiguous bytes.  Lanes past the last full chunk row are handled one
+// 16-byte lane at a time by the slow path.
+#define GMP_TILE_PROLOGUE                                                          \
+    constexpr uint64_t kTileLanes = (uint64_t)THREADS * UNROLL * VEC;              \
+    const uint64_t ntiles = (nlanes + kTileLanes - 1) / kTileLanes;
+
 // ---- write --------------------------------------------------------------------
-template <int PAT, int THREADS, int UNROLL, int HINT>
-__global__ void __launch_bounds__(THREADS) k_hbm_write_pattern(uint4* __restrict__ dst, uint64_t nlanes,
-                                                               uint32_t tail_bytes, uint64_t seed) {
-    constexpr uint64_t kTile = (uint64_t)THREADS * UNROLL;
-    const uint64_t ntiles = (nlanes + kTile - 1) / kTile;
+template <int PAT, int THREADS, int UNROLL, int VEC, int HINT>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+    k_hbm_write_pattern(uint4* __restrict__ dst, uint64_t nlanes, uint32_t tail_bytes, uint64_t seed) {
+    GMP_TILE_PROLOGUE
     for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const uint64_t base = t * kTile + threadIdx.x;
-        if (base + (uint64_t)(UNROLL - 1) * THREADS < nlanes) {
+        const uint64_t base = t * kTileLanes + (uint64_t)threadIdx.x * VEC;
+        if ((t + 1) * kTileLanes <= nlanes) {
 #pragma unroll
             for (int j = 0; j < UNROLL; ++j) {
-                const uint64_t L = base + (uint64_t)j * THREADS;
-                uint64_t w0, w1;
-                lane_words<PAT>(seed, L, w0, w1);
-                st16<HINT>(dst + L, pack(w0, w1));
+                const uint64_t L = base + (uint64_t)j * THREADS * VEC;
+                uint4 v[VEC];
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    uint64_t w0, w1;
+                    lane_words<PAT>(seed, L + k, w0, w1);
+                    v[k] = pack(w0, w1);
+                }
+                st_chunk<VEC, HINT>(dst + L, v);
             }
         } else {
 #pragma unroll
             for (int j = 0; j < UNROLL; ++j) {
-                const uint64_t L = base + (uint64_t)j * THREADS;
-                if (L < nlanes) {
-                    uint64_t w0, w1;
-                    lane_words<PAT>(seed, L, w0, w1);
-                    st16<HINT>(dst + L, pack(w0, w1));
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    const uint64_t L = base + (uint64_t)j * THREADS * VEC + k;
+                    if (L < nlanes) {
+                        uint64_t w0, w1;
+                        lane_words<PAT>(seed, L, w0, w1);
+                        uint4 v[1] = {pack(w0, w1)};
+                        st_chunk<1, HINT>(dst + L, v);
+                    }
                 }
             }
         }
     }
-    // ragged last lane: its leading tail_bytes bytes, written by one thread
-    if (tail_bytes != 0 && blockIdx.x == 0 && threadIdx.x == 0) {
-        uint64_t w0, w1;
-        lane_words<PAT>(seed, nlanes, w0, w1);
-        unsigned char* p = reinterpret_cast<unsigned char*>(dst + nlanes);
-        for (uint32_t b = 0; b < tail_bytes; ++b) {
-            const uint64_t w = (b < 8) ? w0 : w1;
-            p[b] = (unsigned char)(w >> (8 * (b & 7)));
-        }
-    }
+    if (tail_bytes != 0 && blockIdx.x == 0 && threadIdx.x == 0) write_tail<PAT>(dst, nlanes, tail_bytes, seed);
 }
 
 // ---- read + verify --------------------------------------------------------------
@@ -160,6 +212,8 @@ __device__ __forceinline__ void block_fold_and_publish(uint64_t bad, uint64_t in
     }
 }
 
+// Slow, exact accounting of one lane (used for ragged edges and after a tile has
+// been found dirty).
 template <int PAT>
 __device__ __forceinline__ void check_lane(const uint4& v, uint64_t seed, uint64_t L, uint64_t& bad,
                                            uint64_t& inv_first, uint64_t& x, uint64_t& s) {
@@ -176,29 +230,73 @@ __device__ __forceinline__ void check_lane(const uint4& v, uint64_t seed, uint64
     }
 }
 
-template <int PAT, int THREADS, int UNROLL, int HINT>
-__global__ void __launch_bounds__(THREADS, 1024 / THREADS) k_hbm_read_verify(const uint4* __restrict__ src, uint64_t nlanes,
-                                                             uint32_t tail_bytes, uint64_t seed,
-                                                             unsigned long long* __restrict__ acc) {
-    constexpr uint64_t kTile = (uint64_t)THREADS * UNROLL;
-    const uint64_t ntiles = (nlanes + kTile - 1) / kTile;
+// Fast path of one lane: checksums, and OR the lane's difference bits into `dirty`.
+// No per-lane predicate or counter: a clean buffer (the overwhelmingly common case)
+// pays four LOP3s here instead of a compare + predicated count + first-lane select;
+// a tile whose `dirty` ends up non-zero is re-walked by count_bad_lane().
+template <int PAT>
+__device__ __forceinline__ void fold_lane(const uint4& v, uint64_t seed, uint64_t L, uint32_t& dirty, uint64_t& x,
+                                          uint64_t& s) {
+    uint64_t e0, e1;
+    lane_words<PAT>(seed, L, e0, e1);
+    const uint64_t g0 = ((uint64_t)v.y << 32) | v.x;
+    const uint64_t g1 = ((uint64_t)v.w << 32) | v.z;
+    x ^= g0 ^ g1;
+    s += g0 + g1;
+    const uint64_t d = (g0 ^ e0) | (g1 ^ e1);
+    dirty |= (uint32_t)d | (uint32_t)(d >> 32);
+}
+
+template <int PAT>
+__device__ __noinline__ void count_bad_lane(const uint4 v, uint64_t seed, uint64_t L, uint64_t* bad,
+                                            uint64_t* inv_first) {
+    uint64_t e0, e1;
+    lane_words<PAT>(seed, L, e0, e1);
+    const uint64_t g0 = ((uint64_t)v.y << 32) | v.x;
+    const uint64_t g1 = ((uint64_t)v.w << 32) | v.z;
+    if ((g0 ^ e0) | (g1 ^ e1)) {
+        *bad += 1;
+        const uint64_t inv = ~0ull - L;
+        *inv_first = inv > *inv_first ? inv : *inv_first;
+    }
+}
+
+template <int PAT, int THREADS, int UNROLL, int VEC, int HINT>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+    k_hbm_read_verify(const uint4* __restrict__ src, uint64_t nlanes, uint32_t tail_bytes, uint64_t seed,
+                      unsigned long long* __restrict__ acc) {
+    GMP_TILE_PROLOGUE
     uint64_t bad = 0, inv_first = 0, x = 0, s = 0;
     for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const uint64_t base = t * kTile + threadIdx.x;
-        if (base + (uint64_t)(UNROLL - 1) * THREADS < nlanes) {
-            uint4 v[UNROLL];
+        const uint64_t base = t * kTileLanes + (uint64_t)threadIdx.x * VEC;
+        if ((t + 1) * kTileLanes <= nlanes) {
+            uint4 v[UNROLL][VEC];
 #pragma unroll
-            for (int j = 0; j < UNROLL; ++j) v[j] = ld16<HINT>(src + base + (uint64_t)j * THREADS);
+            for (int j = 0; j < UNROLL; ++j) ld_chunk<VEC, HINT>(src + base + (uint64_t)j * THREADS * VEC, v[j]);
+            uint32_t dirty = 0;
 #pragma unroll
             for (int j = 0; j < UNROLL; ++j)
-                check_lane<PAT>(v[j], seed, base + (uint64_t)j * THREADS, bad, inv_first, x, s);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k)
+                    fold_lane<PAT>(v[j][k], seed, base + (uint64_t)j * THREADS * VEC + k, dirty, x, s);
+            if (dirty != 0) {  // rare: some lane of this thread's tile differs, account for it exactly
+#pragma unroll
+                for (int j = 0; j < UNROLL; ++j)
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k)
+                        count_bad_lane<PAT>(v[j][k], seed, base + (uint64_t)j * THREADS * VEC + k, &bad, &inv_first);
+            }
         } else {
 #pragma unroll
             for (int j = 0; j < UNROLL; ++j) {
-                const uint64_t L = base + (uint64_t)j * THREADS;
-                if (L < nlanes) {
-                    const uint4 v = ld16<HINT>(src + L);
-                    check_lane<PAT>(v, seed, L, bad, inv_first, x, s);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    const uint64_t L = base + (uint64_t)j * THREADS * VEC + k;
+                    if (L < nlanes) {
+                        uint4 v[1];
+                        ld_chunk<1, HINT>(src + L, v);
+                        check_lane<PAT>(v[0], seed, L, bad, inv_first, x, s);
+                    }
                 }
             }
         }
@@ -230,24 +328,30 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS) k_hbm_read_verify(con
 }
 
 // ---- copy -----------------------------------------------------------------------
-template <int THREADS, int UNROLL, int HINT>
-__global__ void __launch_bounds__(THREADS, 1024 / THREADS) k_hbm_copy(uint4* __restrict__ dst, const uint4* __restrict__ src,
-                                                      uint64_t nlanes, uint32_t tail_bytes) {
-    constexpr uint64_t kTile = (uint64_t)THREADS * UNROLL;
-    const uint64_t ntiles = (nlanes + kTile - 1) / kTile;
+template <int THREADS, int UNROLL, int VEC, int HINT>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+    k_hbm_copy(uint4* __restrict__ dst, const uint4* __restrict__ src, uint64_t nlanes, uint32_t tail_bytes) {
+    GMP_TILE_PROLOGUE
     for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const uint64_t base = t * kTile + threadIdx.x;
-        if (base + (uint64_t)(UNROLL - 1) * THREADS < nlanes) {
-            uint4 v[UNROLL];
+        const uint64_t base = t * kTileLanes + (uint64_t)threadIdx.x * VEC;
+        if ((t + 1) * kTileLanes <= nlanes) {
+            uint4 v[UNROLL][VEC];
 #pragma unroll
-            for (int j = 0; j < UNROLL; ++j) v[j] = ld16<HINT>(src + base + (uint64_t)j * THREADS);
+            for (int j = 0; j < UNROLL; ++j) ld_chunk<VEC, HINT>(src + base + (uint64_t)j * THREADS * VEC, v[j]);
 #pragma unroll
-            for (int j = 0; j < UNROLL; ++j) st16<HINT>(dst + base + (uint64_t)j * THREADS, v[j]);
+            for (int j = 0; j < UNROLL; ++j) st_chunk<VEC, HINT>(dst + base + (uint64_t)j * THREADS * VEC, v[j]);
         } else {
 #pragma unroll
             for (int j = 0; j < UNROLL; ++j) {
-                const uint64_t L = base + (uint64_t)j * THREADS;
-                if (L < nlanes) st16<HINT>(dst + L, ld16<HINT>(src + L));
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) {
+                    const uint64_t L = base + (uint64_t)j * THREADS * VEC + k;
+                    if (L < nlanes) {
+                        uint4 v[1];
+                        ld_chunk<1, HINT>(src + L, v);
+                        st_chunk<1, HINT>(dst + L, v);
+                    }
+                }
             }
         }
     }
@@ -262,8 +366,11 @@ __global__ void k_hbm_corrupt(unsigned char* p, size_t off, unsigned char mask) 
 
 // ---- launch geometry --------------------------------------------------------------
 Tunables& tunables() {
-    static Tunables t = {/*write_ctas_per_sm*/ 8, /*read*/ 4, /*copy*/ 4, /*write_variant*/ 1, /*read_variant*/ 1,
-                         /*copy_variant*/ 1};
+    // Picked by tools/sweep_hbm.py on a B200 (profiles/r01_sweep.md): many small CTAs (several waves, so the
+    // hardware balances the ~10% speed spread between SMs) for the store-heavy kernels, exactly one resident
+    // wave for the register-accumulating verify kernel.
+    static Tunables t = {/*write_ctas_per_sm*/ 24, /*read*/ 4, /*copy*/ 32,
+                         /*write_variant*/ 12, /*read_variant*/ 10, /*copy_variant*/ 11};
     return t;
 }
 
@@ -285,35 +392,84 @@ cudaError_t current_device_info(DeviceInfo* info) {
     return cudaSuccess;
 }
 
-static unsigned grid_for(uint64_t nlanes, uint64_t tile, int sm_count, int ctas_per_sm) {
+// CTAs of `kernel` that fit on one SM at once (occupancy API, cached per instantiation).
+template <auto Kernel, int THREADS>
+static int resident_ctas_per_sm() {
+    static std::atomic<int> cache{0};
+    int v = cache.load(std::memory_order_relaxed);
+    if (v == 0) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, Kernel, THREADS, 0) != cudaSuccess || v < 1) {
+            (void)cudaGetLastError();
+            v = 1;
+        }
+        cache.store(v, std::memory_order_relaxed);
+    }
+    return v;
+}
+
+// ctas_per_sm == 0 means "exactly one resident wave" (persistent kernel); > 0 is an
+// explicit multiple of the SM count (several waves of smaller CTAs).
+static unsigned grid_for(uint64_t nlanes, uint64_t tile, int sm_count, int ctas_per_sm, int resident) {
     uint64_t ntiles = (nlanes + tile - 1) / tile;
     if (ntiles == 0) ntiles = 1;  // still one CTA for the ragged tail
-    uint64_t g = (uint64_t)sm_count * (uint64_t)(ctas_per_sm > 0 ? ctas_per_sm : 1);
+    const uint64_t per_sm = ctas_per_sm > 0 ? (uint64_t)ctas_per_sm : (uint64_t)resident;
+    const uint64_t g = (uint64_t)sm_count * per_sm;
     return (unsigned)(ntiles < g ? ntiles : g);
 }
 
-// Variant table: (THREADS, UNROLL, HINT).  Variant 1 is the default picked by the
-// sweep recorded in profiles/; the others stay selectable through gmp_tune() so
-// that the sweep can be re-run on new silicon.
-#define GMP_VARIANTS(X) \
-    X(0, 256, 4, HINT_DEFAULT) \
-    X(1, 256, 4, HINT_STREAM)  \
-    X(2, 256, 8, HINT_STREAM)  \
-    X(3, 512, 4, HINT_STREAM)  \
-    X(4, 256, 4, HINT_NOALLOC) \
-    X(5, 256, 8, HINT_NOALLOC) \
-    X(6, 512, 2, HINT_STREAM)  \
-    X(7, 128, 8, HINT_STREAM)
+// Variant table: (THREADS, UNROLL, VEC, HINT).  The defaults in tunables() were picked
+// by tools/sweep_hbm.py on a B200 (profiles/); the others stay selectable through
+// gmp_tune() so that the sweep can be re-run on new silicon.  VEC=2 variants need
+// 32-byte-aligned pointers; the launchers fall back to kFallbackVariant otherwise.
+#define GMP_VARIANTS(X)            \
+    X(0, 256, 4, 1, HINT_DEFAULT)  \
+    X(1, 256, 4, 1, HINT_STREAM)   \
+    X(2, 256, 8, 1, HINT_STREAM)   \
+    X(3, 512, 4, 1, HINT_STREAM)   \
+    X(4, 256, 4, 1, HINT_NOALLOC)  \
+    X(5, 512, 2, 1, HINT_STREAM)   \
+    X(6, 128, 8, 1, HINT_STREAM)   \
+    X(7, 256, 2, 2, HINT_STREAM)   \
+    X(8, 256, 4, 2, HINT_STREAM)   \
+    X(9, 512, 2, 2, HINT_STREAM)   \
+    X(10, 256, 2, 2, HINT_DEFAULT) \
+    X(11, 1024, 1, 2, HINT_STREAM) \
+    X(12, 1024, 2, 1, HINT_STREAM) \
+    X(13, 256, 1, 2, HINT_STREAM)  \
+    X(14, 512, 1, 2, HINT_STREAM)  \
+    X(15, 256, 4, 2, HINT_L2EF)
+constexpr int kVariantCount = 16;
+constexpr int kFallbackVariant = 1;
+
+static bool variant_is_wide(int id) {
+    switch (id) {
+#define X(ID, T, U, V, H) \
+    case ID:              \
+        return V == 2;
+        GMP_VARIANTS(X)
+#undef X
+        default:
+            return false;
+    }
+}
+
+static int pick_variant(int wanted, const void* p0, const void* p1) {
+    const uintptr_t bits = reinterpret_cast<uintptr_t>(p0) | reinterpret_cast<uintptr_t>(p1);
+    if (variant_is_wide(wanted) && (bits & 31u) != 0) return kFallbackVariant;
+    return wanted;
+}
 
 template <int PAT>
 static cudaError_t launch_write_pat(uint4* dst, uint64_t nlanes, uint32_t tail, uint64_t seed, int sm_count,
                                     cudaStream_t s) {
     const Tunables& tn = tunables();
-    switch (tn.write_variant) {
-#define X(ID, T, U, H)                                                                           \
-    case ID:                                                                                     \
-        k_hbm_write_pattern<PAT, T, U, H>                                                        \
-            <<<grid_for(nlanes, (uint64_t)T * U, sm_count, tn.write_ctas_per_sm), T, 0, s>>>(dst, nlanes, tail, seed); \
+    switch (pick_variant(tn.write_variant, dst, nullptr)) {
+#define X(ID, T, U, V, H)                                                                            \
+    case ID:                                                                                         \
+        k_hbm_write_pattern<PAT, T, U, V, H>                                                         \
+            <<<grid_for(nlanes, (uint64_t)T * U * V, sm_count, tn.write_ctas_per_sm,                 \
+                        resident_ctas_per_sm<k_hbm_write_pattern<PAT, T, U, V, H>, T>()),            \
+               T, 0, s>>>(dst, nlanes, tail, seed);                                                  \
         break;
         GMP_VARIANTS(X)
 #undef X
@@ -327,11 +483,13 @@ template <int PAT>
 static cudaError_t launch_verify_pat(const uint4* src, uint64_t nlanes, uint32_t tail, uint64_t seed,
                                      unsigned long long* acc, int sm_count, cudaStream_t s) {
     const Tunables& tn = tunables();
-    switch (tn.read_variant) {
-#define X(ID, T, U, H)                                                                          \
-    case ID:                                                                                    \
-        k_hbm_read_verify<PAT, T, U, H>                                                         \
-            <<<grid_for(nlanes, (uint64_t)T * U, sm_count, tn.read_ctas_per_sm), T, 0, s>>>(src, nlanes, tail, seed, acc); \
+    switch (pick_variant(tn.read_variant, src, nullptr)) {
+#define X(ID, T, U, V, H)                                                                           \
+    case ID:                                                                                        \
+        k_hbm_read_verify<PAT, T, U, V, H>                                                          \
+            <<<grid_for(nlanes, (uint64_t)T * U * V, sm_count, tn.read_ctas_per_sm,                 \
+                        resident_ctas_per_sm<k_hbm_read_verify<PAT, T, U, V, H>, T>()),             \
+               T, 0, s>>>(src, nlanes, tail, seed, acc);                                            \
         break;
         GMP_VARIANTS(X)
 #undef X
@@ -393,11 +551,12 @@ cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
     const Tunables& tn = tunables();
-    switch (tn.copy_variant) {
-#define X(ID, T, U, H)                                                                      \
-    case ID:                                                                                \
-        k_hbm_copy<T, U, H><<<grid_for(nlanes, (uint64_t)T * U, di.sm_count, tn.copy_ctas_per_sm), T, 0, s>>>( \
-            static_cast<uint4*>(dst), static_cast<const uint4*>(src), nlanes, tail);         \
+    switch (pick_variant(tn.copy_variant, dst, src)) {
+#define X(ID, T, U, V, H)                                                                          \
+    case ID:                                                                                       \
+        k_hbm_copy<T, U, V, H><<<grid_for(nlanes, (uint64_t)T * U * V, di.sm_count, tn.copy_ctas_per_sm,       \
+                                          resident_ctas_per_sm<k_hbm_copy<T, U, V, H>, T>()),     \
+                                 T, 0, s>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(src), nlanes, tail); \
         break;
         GMP_VARIANTS(X)
 #undef X
@@ -535,15 +694,15 @@ extern "C" int gmp_tune(const char* knob, int value) {
     if (k == "write_ctas_per_sm") slot = &t.write_ctas_per_sm;
     else if (k == "read_ctas_per_sm") slot = &t.read_ctas_per_sm;
     else if (k == "copy_ctas_per_sm") slot = &t.copy_ctas_per_sm;
-    else if (k == "write_variant") { slot = &t.write_variant; limit = 7; }
-    else if (k == "read_variant") { slot = &t.read_variant; limit = 7; }
-    else if (k == "copy_variant") { slot = &t.copy_variant; limit = 7; }
+    else if (k == "write_variant") { slot = &t.write_variant; limit = kVariantCount - 1; }
+    else if (k == "read_variant") { slot = &t.read_variant; limit = kVariantCount - 1; }
+    else if (k == "copy_variant") { slot = &t.copy_variant; limit = kVariantCount - 1; }
     if (slot == nullptr) {
         set_error("unknown knob '%s'", knob);
         return GMP_ERR_INVALID;
     }
     if (value >= 0) {
-        if (value > limit || (limit == 64 && value == 0)) {
+        if (value > limit) {
             set_error("knob '%s': value %d out of range", knob, value);
             return GMP_ERR_INVALID;
         }

@@ -208,8 +208,10 @@ GMP_API int gmp_hbm_corrupt(void* dptr, size_t bytes, size_t byte_offset, uint8_
  * Benchmarking knob, process-wide, not for production callers: selects the
  * launch geometry of the three kernels.  Knobs: "write_ctas_per_sm",
  * "read_ctas_per_sm", "copy_ctas_per_sm", "write_variant", "read_variant",
- * "copy_variant".  value < 0 only queries.  Returns the value in force
- * (>= 0) or GMP_ERR_INVALID.
+ * "copy_variant".  A *_ctas_per_sm of 0 means one resident wave (persistent
+ * grid sized by the occupancy API); N > 0 launches N x (SM count) CTAs.
+ * value < 0 only queries.  Returns the value in force (>= 0) or
+ * GMP_ERR_INVALID.
  */
 GMP_API int gmp_tune(const char* knob, int value);
 
