@@ -1,0 +1,1087 @@
+// Native node-local mount path: section 6 of include/gpumounter_probe.h.
+//
+// Behavioural contract = the reference's Go packages (cited per function); mechanism =
+// direct system calls.  The reference spends two to three fork/exec chains per GPU
+// (sh -> echo; nsenter -> sh -> mknod) and needs sh/mknod/rm/kill inside the target image
+// (ref: docs/guide/FAQ.md:3-4).  Here: open/write for the device-cgroup line and one forked
+// child per call that setns()es into the target's mount namespace and issues mknod(2) /
+// unlink(2) itself.  A child is still needed because setns(CLONE_NEWNS) is refused for a
+// multithreaded caller (the worker is one), but it never exec()s anything.
+
+#include <errno.h>
+#include <fcntl.h>
+#include <sched.h>
+#include <signal.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+#include <sys/sysmacros.h>
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "gpumounter_probe.h"
+
+namespace gmp {
+void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+void clear_error();
+}  // namespace gmp
+
+namespace {
+
+using gmp::clear_error;
+using gmp::set_error;
+
+constexpr const char* kDevicesRoot = "/sys/fs/cgroup/devices";  // ref: cgroup.go:116
+constexpr const char* kDevPrefix = "/dev/nvidia";               // ref: nvidia.go:40
+constexpr const char* kCgroupPermission = "rw";                 // ref: nvidia.go:38
+constexpr mode_t kDeviceFileMode = 0666;                        // ref: nvidia.go:39 "666"
+constexpr const char* kFreeState = "GPU_FREE_STATE";            // ref: nvidia.go:21
+constexpr const char* kAllocatedState = "GPU_ALLOCATED_STATE";  // ref: nvidia.go:22
+constexpr const char* kGpuPoolNamespace = "gpu-pool";           // ref: types.go:18
+constexpr const char* kNvidiaResourceName = "nvidia.com/gpu";   // ref: types.go:10
+
+// Copies into a caller buffer; GMP_ERR_BUFFER_TOO_SMALL when it does not fit.
+int emit(const std::string& s, char* out, size_t cap) {
+    if (out == nullptr || cap < s.size() + 1) {
+        set_error("output buffer of %zu bytes too small for %zu", cap, s.size() + 1);
+        return GMP_ERR_BUFFER_TOO_SMALL;
+    }
+    memcpy(out, s.c_str(), s.size() + 1);
+    return GMP_OK;
+}
+
+template <size_t N>
+void put(char (&dst)[N], const std::string& s) {
+    const size_t n = std::min(s.size(), N - 1);
+    memcpy(dst, s.data(), n);
+    dst[n] = '\0';
+}
+
+const char* or_default(const char* v, const char* d) { return (v != nullptr && v[0] != '\0') ? v : d; }
+
+std::string devices_root(const gmp_mount_env* env) { return or_default(env ? env->devices_root : nullptr, kDevicesRoot); }
+std::string dev_prefix(const gmp_mount_env* env) { return or_default(env ? env->dev_prefix : nullptr, kDevPrefix); }
+std::string proc_root(const gmp_mount_env* env) { return or_default(env ? env->proc_root : nullptr, "/proc"); }
+
+// The node path of a GPU: the record's DeviceFilePath when the default prefix is in force
+// (that is what the reference passes to mknod/rm, ref: namespace.go:168,180), else prefix+minor.
+std::string device_node_path(const gmp_mount_env* env, const gmp_gpu* gpu) {
+    if (env == nullptr || env->dev_prefix == nullptr || env->dev_prefix[0] == '\0') return gpu->device_file_path;
+    return dev_prefix(env) + std::to_string(gpu->minor_number);
+}
+
+// ---- resource.Quantity, value only (k8s.io/apimachinery v0.18.6, go.mod:12) -----------------
+// Exact value in nano units held in 128 bits: enough for Ei-scale memory and nano-CPU.
+using i128 = __int128;
+
+bool parse_quantity(const char* text, i128* nano) {
+    if (text == nullptr) return false;
+    std::string s(text);
+    size_t i = 0;
+    bool neg = false;
+    if (i < s.size() && (s[i] == '+' || s[i] == '-')) neg = s[i++] == '-';
+    i128 mant = 0;
+    int ndigits = 0, nfrac = 0;
+    for (; i < s.size() && isdigit((unsigned char)s[i]); ++i, ++ndigits) mant = mant * 10 + (s[i] - '0');
+    if (i < s.size() && s[i] == '.') {
+        for (++i; i < s.size() && isdigit((unsigned char)s[i]); ++i, ++ndigits, ++nfrac) mant = mant * 10 + (s[i] - '0');
+    }
+    if (ndigits == 0) return false;
+    const std::string suffix = s.substr(i);
+    int pow10 = -nfrac, pow2 = 0;
+    static const struct { const char* sfx; int p10; int p2; } table[] = {
+        {"", 0, 0},   {"n", -9, 0}, {"u", -6, 0}, {"m", -3, 0}, {"k", 3, 0},   {"M", 6, 0},   {"G", 9, 0},
+        {"T", 12, 0}, {"P", 15, 0}, {"E", 18, 0}, {"Ki", 0, 10}, {"Mi", 0, 20}, {"Gi", 0, 30}, {"Ti", 0, 40},
+        {"Pi", 0, 50}, {"Ei", 0, 60}};
+    bool known = false;
+    for (const auto& t : table) {
+        if (suffix == t.sfx) {
+            pow10 += t.p10;
+            pow2 = t.p2;
+            known = true;
+            break;
+        }
+    }
+    if (!known) {  // decimal exponent form: e3, E-2
+        if (suffix.size() < 2 || (suffix[0] != 'e' && suffix[0] != 'E')) return false;
+        size_t j = 1;
+        if (suffix[j] == '+' || suffix[j] == '-') ++j;
+        if (j >= suffix.size()) return false;
+        for (size_t k = j; k < suffix.size(); ++k)
+            if (!isdigit((unsigned char)suffix[k])) return false;
+        const long e = strtol(suffix.c_str() + 1, nullptr, 10);
+        if (e > 30 || e < -30) return false;
+        pow10 += (int)e;
+    }
+    i128 v = mant << pow2;
+    for (pow10 += 9; pow10 > 0; --pow10) v *= 10;
+    for (; pow10 < 0; ++pow10) v = (v + 9) / 10;  // anything finer than nano rounds up, as ParseQuantity does
+    *nano = neg ? -v : v;
+    return true;
+}
+
+// ---- QoS (ref: cgroup.go:177-237) -------------------------------------------------------------
+struct ResourceTotals {
+    bool present[2] = {false, false};  // [cpu, memory]
+    i128 value[2] = {0, 0};
+    int count() const { return (int)present[0] + (int)present[1]; }
+    void add(int k, i128 q) {
+        value[k] = present[k] ? value[k] + q : q;
+        present[k] = true;
+    }
+};
+
+int pod_qos(const gmp_pod* pod, int* qos) {
+    ResourceTotals requests, limits;
+    bool guaranteed = true;
+    for (int c = 0; c < pod->n_containers; ++c) {
+        const gmp_container_resources& r = pod->containers[c];
+        const char* req[2] = {r.cpu_request, r.memory_request};
+        const char* lim[2] = {r.cpu_limit, r.memory_limit};
+        bool limit_found[2] = {false, false};
+        for (int k = 0; k < 2; ++k) {
+            i128 q;
+            if (req[k] != nullptr) {
+                if (!parse_quantity(req[k], &q)) {
+                    set_error("unparsable quantity '%s'", req[k]);
+                    return GMP_ERR_INVALID;
+                }
+                if (q > 0) requests.add(k, q);  // ref: cgroup.go:188-196
+            }
+            if (lim[k] != nullptr) {
+                if (!parse_quantity(lim[k], &q)) {
+                    set_error("unparsable quantity '%s'", lim[k]);
+                    return GMP_ERR_INVALID;
+                }
+                if (q > 0) {  // ref: cgroup.go:204-213
+                    limit_found[k] = true;
+                    limits.add(k, q);
+                }
+            }
+        }
+        if (!(limit_found[0] && limit_found[1])) guaranteed = false;  // ref: cgroup.go:216-218
+    }
+    if (requests.count() == 0 && limits.count() == 0) {
+        *qos = GMP_QOS_BESTEFFORT;
+        return GMP_OK;
+    }
+    if (guaranteed) {
+        for (int k = 0; k < 2; ++k)
+            if (requests.present[k] && !(limits.present[k] && limits.value[k] == requests.value[k])) guaranteed = false;
+    }
+    *qos = (guaranteed && requests.count() == limits.count()) ? GMP_QOS_GUARANTEED : GMP_QOS_BURSTABLE;
+    return GMP_OK;
+}
+
+// ---- cgroup names ----------------------------------------------------------------------------
+bool component_ok(const std::string& c) { return c.find('/') == std::string::npos && c.find('_') == std::string::npos; }
+
+// runc v1.0.0-rc92 systemd.ExpandSlice (go.mod:8; called at cgroup.go:62)
+bool expand_slice(const std::string& slice, std::string* out) {
+    static const std::string suffix = ".slice";
+    if (slice.size() < suffix.size() || slice.compare(slice.size() - suffix.size(), suffix.size(), suffix) != 0) return false;
+    if (slice.find('/') != std::string::npos) return false;
+    const std::string name = slice.substr(0, slice.size() - suffix.size());
+    if (name == "-") {
+        *out = "/";
+        return true;
+    }
+    std::string path, prefix;
+    size_t begin = 0;
+    while (true) {
+        const size_t dash = name.find('-', begin);
+        const std::string component = name.substr(begin, dash == std::string::npos ? std::string::npos : dash - begin);
+        if (component.empty()) return false;
+        path += "/" + prefix + component + suffix;
+        prefix += component + "-";
+        if (dash == std::string::npos) break;
+        begin = dash + 1;
+    }
+    *out = path;
+    return true;
+}
+
+int to_systemd(const std::vector<std::string>& parts, std::string* out) {
+    if (parts.empty() || (parts.size() == 1 && parts[0].empty())) {
+        *out = "/";
+        return GMP_OK;
+    }
+    std::string joined;
+    for (size_t i = 0; i < parts.size(); ++i) {
+        if (i) joined += '-';
+        std::string escaped = parts[i];
+        std::replace(escaped.begin(), escaped.end(), '-', '_');  // ref: cgroup.go:70-72
+        joined += escaped;
+    }
+    if (!expand_slice(joined + ".slice", out)) {
+        // the reference panics here (cgroup.go:63-66)
+        set_error("error converting cgroup name to systemd format: invalid slice name: %s.slice", joined.c_str());
+        return GMP_ERR_NAME;
+    }
+    return GMP_OK;
+}
+
+// "/" + path.Join(parts...) for slash-free parts: empties dropped, "." and ".." cleaned
+std::string to_cgroupfs(const std::vector<std::string>& parts) {
+    std::vector<std::string> kept;
+    int up = 0;
+    bool any = false;
+    for (const std::string& p : parts) {
+        if (p.empty()) continue;
+        any = true;
+        if (p == ".") continue;
+        if (p == "..") {
+            if (!kept.empty()) kept.pop_back();
+            else ++up;
+            continue;
+        }
+        kept.push_back(p);
+    }
+    if (!any) return "/";
+    std::string joined;
+    for (int i = 0; i < up; ++i) joined += (joined.empty() ? "" : "/") + std::string("..");
+    for (const std::string& k : kept) joined += (joined.empty() ? "" : "/") + k;
+    if (joined.empty()) joined = ".";
+    return "/" + joined;
+}
+
+int cgroup_driver(const gmp_mount_env* env, std::string* out) {
+    const char* v = (env != nullptr && env->cgroup_driver != nullptr) ? env->cgroup_driver : getenv("CGROUP_DRIVER");
+    const std::string value = v ? v : "";
+    if (value != "systemd" && value != "cgroupfs") {
+        set_error("unsupported cgroup driver: %s", value.c_str());  // ref: cgroup.go:81
+        return GMP_ERR_CGROUP_DRIVER;
+    }
+    *out = value;
+    return GMP_OK;
+}
+
+int cgroup_name(const std::string& driver, const gmp_pod* pod, const std::string& container_id, std::string* out) {
+    int qos = 0;
+    int rc = pod_qos(pod, &qos);
+    if (rc != GMP_OK) return rc;
+    std::vector<std::string> parts = {"kubepods"};  // ref: cgroup.go:87
+    if (qos == GMP_QOS_BURSTABLE) parts.push_back("burstable");
+    if (qos == GMP_QOS_BESTEFFORT) parts.push_back("besteffort");
+    const std::string pod_part = std::string("pod") + (pod->uid ? pod->uid : "");  // ref: cgroup.go:101
+    if (!component_ok(pod_part)) {
+        set_error("invalid character in component [\"%s\"] of CgroupName", pod_part.c_str());  // ref: cgroup.go:38
+        return GMP_ERR_NAME;
+    }
+    parts.push_back(pod_part);
+    if (driver == "systemd") {
+        std::string base;
+        rc = to_systemd(parts, &base);
+        if (rc != GMP_OK) return rc;
+        *out = base + "/docker-" + container_id + ".scope";  // ref: cgroup.go:106
+        return GMP_OK;
+    }
+    if (driver == "cgroupfs") {
+        *out = to_cgroupfs(parts) + "/" + container_id;  // ref: cgroup.go:108
+        return GMP_OK;
+    }
+    set_error("unsupported cgroup driver");  // ref: cgroup.go:112
+    return GMP_ERR_CGROUP_DRIVER;
+}
+
+std::string strip_docker_scheme(const char* id) {  // strings.Replace(id, "docker://", "", 1), ref: util.go:23
+    std::string s = id ? id : "";
+    const size_t at = s.find("docker://");
+    if (at != std::string::npos) s.erase(at, strlen("docker://"));
+    return s;
+}
+
+int pod_cgroup_path(const gmp_mount_env* env, const gmp_pod* pod, std::string* out) {
+    if (pod == nullptr || pod->container_id == nullptr) {
+        set_error("pod has no container status");  // Go: index out of range on ContainerStatuses[0]
+        return GMP_ERR_INVALID;
+    }
+    std::string driver;
+    int rc = cgroup_driver(env, &driver);  // ref: util.go:25-29
+    if (rc != GMP_OK) return rc;
+    return cgroup_name(driver, pod, strip_docker_scheme(pod->container_id), out);  // ref: util.go:30-34
+}
+
+// ---- cgroup files -------------------------------------------------------------------------------
+int read_cgroup_pids(const gmp_mount_env* env, const std::string& cgroup_path, std::vector<std::string>* pids) {
+    const std::string file = devices_root(env) + cgroup_path + "/cgroup.procs";
+    const int fd = open(file.c_str(), O_RDONLY | O_CLOEXEC);
+    if (fd < 0) {
+        set_error("open %s: %s", file.c_str(), strerror(errno));
+        return GMP_ERR_SYS;
+    }
+    std::string content;
+    char buf[4096];
+    ssize_t r;
+    while ((r = read(fd, buf, sizeof(buf))) > 0) content.append(buf, (size_t)r);
+    close(fd);
+    size_t begin = 0;
+    for (size_t nl; (nl = content.find('\n', begin)) != std::string::npos; begin = nl + 1)
+        pids->push_back(content.substr(begin, nl - begin));
+    // whatever follows the last '\n' is dropped, as bufio.ReadString+break does (ref: cgroup.go:131-135)
+    return GMP_OK;
+}
+
+int write_permission(const gmp_mount_env* env, const std::string& cgroup_path, int minor, const char* file_name) {
+    const std::string file = devices_root(env) + cgroup_path + "/" + file_name;
+    // what `echo '...' > file` does: O_WRONLY|O_CREAT|O_TRUNC and a trailing newline
+    const int fd = open(file.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);
+    if (fd < 0) {
+        set_error("open %s: %s", file.c_str(), strerror(errno));
+        return GMP_ERR_SYS;
+    }
+    char line[64];
+    const int len = snprintf(line, sizeof(line), "c %d:%d %s\n", GMP_NVIDIA_MAJOR, minor, kCgroupPermission);
+    const ssize_t w = write(fd, line, (size_t)len);
+    const int saved = errno;
+    close(fd);
+    if (w != len) {
+        set_error("write '%.*s' to %s: %s", len - 1, line, file.c_str(), w < 0 ? strerror(saved) : "short write");
+        return GMP_ERR_SYS;
+    }
+    return GMP_OK;
+}
+
+// ---- namespace work in a forked child ---------------------------------------------------------------
+enum class NodeOp { kCreate, kRemove };
+
+struct NodeJob {
+    NodeOp op;
+    std::string path;
+    int minor;
+};
+
+// Runs `jobs` inside the mount namespace named by ns_path.  Returns GMP_OK or GMP_ERR_SYS and, through
+// *done, how many jobs completed.  The child reports (jobs done, errno, failing syscall) over a pipe.
+int run_in_mount_ns(const std::string& ns_path, const std::vector<NodeJob>& jobs, int* done) {
+    struct Report {
+        int32_t done;
+        int32_t err;
+        int32_t stage;  // 0 ok, 1 open ns, 2 setns, 3 mknod, 4 chmod, 5 unlink
+    };
+    if (done) *done = 0;
+    int pfd[2];
+    if (pipe2(pfd, O_CLOEXEC) != 0) {
+        set_error("pipe2: %s", strerror(errno));
+        return GMP_ERR_SYS;
+    }
+    const pid_t child = fork();
+    if (child < 0) {
+        set_error("fork: %s", strerror(errno));
+        close(pfd[0]);
+        close(pfd[1]);
+        return GMP_ERR_SYS;
+    }
+    if (child == 0) {
+        // async-signal-safe territory: only raw system calls until _exit
+        Report rep = {0, 0, 0};
+        const int nsfd = open(ns_path.c_str(), O_RDONLY | O_CLOEXEC);
+        if (nsfd < 0) {
+            rep.err = errno;
+            rep.stage = 1;
+        } else if (setns(nsfd, CLONE_NEWNS) != 0) {
+            rep.err = errno;
+            rep.stage = 2;
+        } else {
+            umask(0);
+            for (const NodeJob& j : jobs) {
+                if (j.op == NodeOp::kCreate) {
+                    if (mknod(j.path.c_str(), S_IFCHR | kDeviceFileMode, makedev(GMP_NVIDIA_MAJOR, (unsigned)j.minor)) != 0) {
+                        rep.err = errno;
+                        rep.stage = 3;
+                        break;
+                    }
+                    if (chmod(j.path.c_str(), kDeviceFileMode) != 0) {  // `mknod -m 666` sets the mode exactly
+                        rep.err = errno;
+                        rep.stage = 4;
+                        break;
+                    }
+                } else if (unlink(j.path.c_str()) != 0) {
+                    rep.err = errno;
+                    rep.stage = 5;
+                    break;
+                }
+                ++rep.done;
+            }
+        }
+        ssize_t ignored = write(pfd[1], &rep, sizeof(rep));
+        (void)ignored;
+        _exit(rep.stage == 0 ? 0 : 1);
+    }
+    close(pfd[1]);
+    Report rep = {0, EIO, -1};
+    ssize_t got;
+    do {
+        got = read(pfd[0], &rep, sizeof(rep));
+    } while (got < 0 && errno == EINTR);
+    close(pfd[0]);
+    int status = 0;
+    while (waitpid(child, &status, 0) < 0 && errno == EINTR) {
+    }
+    if (got != (ssize_t)sizeof(rep)) {
+        set_error("namespace helper died without a report (wait status 0x%x)", status);
+        return GMP_ERR_SYS;
+    }
+    if (done) *done = rep.done;
+    if (rep.stage == 0) return GMP_OK;
+    static const char* const what[] = {"", "open", "setns", "mknod", "chmod", "unlink"};
+    const char* target = rep.stage <= 2 ? ns_path.c_str()
+                                        : (rep.done < (int)jobs.size() ? jobs[(size_t)rep.done].path.c_str() : "?");
+    set_error("%s %s: %s", what[rep.stage], target, strerror(rep.err));
+    return GMP_ERR_SYS;
+}
+
+int mount_ns_path(const gmp_mount_env* env, const gmp_ns_config* cfg, std::string* out) {
+    if (cfg == nullptr || cfg->target == 0) {
+        set_error("Target must be specified ");  // ref: namespace.go:72
+        return GMP_ERR_TARGET;
+    }
+    if (cfg->mount_file != nullptr && cfg->mount_file[0] != '\0') *out = cfg->mount_file;  // --mount=<file>
+    else *out = proc_root(env) + "/" + std::to_string(cfg->target) + "/ns/mnt";
+    return GMP_OK;
+}
+
+bool go_atoi(const std::string& s, int* out) {  // strconv.Atoi: sign + digits, nothing else
+    size_t i = (!s.empty() && (s[0] == '+' || s[0] == '-')) ? 1 : 0;
+    if (i >= s.size()) return false;
+    for (size_t k = i; k < s.size(); ++k)
+        if (!isdigit((unsigned char)s[k])) return false;
+    errno = 0;
+    const long v = strtol(s.c_str(), nullptr, 10);
+    if (errno != 0 || v > INT32_MAX || v < INT32_MIN) return false;
+    *out = (int)v;
+    return true;
+}
+
+int first_pid(const std::vector<std::string>& pids, int* pid) {
+    if (pids.empty()) {
+        set_error("cgroup.procs lists no process (the reference indexes pids[0] and panics, util.go:50)");
+        return GMP_ERR_EMPTY_CGROUP;
+    }
+    if (!go_atoi(pids[0], pid)) {
+        set_error("Invalid PID: %s", pids[0].c_str());  // ref: util.go:52
+        return GMP_ERR_INVALID;
+    }
+    return GMP_OK;
+}
+
+// cgroup.procs ∩ NVML pids for one GPU (ref: util.go:169-195), NVML order kept.
+int busy_pids(const std::vector<std::string>& cgroup_pids, const gmp_gpu* gpu, std::vector<std::string>* out) {
+    std::vector<gmp_process_info> procs(2048);
+    int n = 0;
+    int rc = gmp_gpu_running_processes(gpu->uuid, procs.data(), (int)procs.size(), &n);
+    if (rc != GMP_OK) return rc;
+    for (int i = 0; i < n; ++i) {
+        const std::string pid = std::to_string((int)procs[(size_t)i].pid);
+        if (std::find(cgroup_pids.begin(), cgroup_pids.end(), pid) != cgroup_pids.end()) out->push_back(pid);
+    }
+    return GMP_OK;
+}
+
+int kill_pids(const std::vector<std::string>& pids) {
+    // the reference runs `kill p1 p2 ...` (SIGTERM) with host pids: only the mount namespace was entered
+    int failures = 0, last_errno = 0;
+    for (const std::string& p : pids) {
+        int pid = 0;
+        if (!go_atoi(p, &pid) || kill(pid, SIGTERM) != 0) {
+            ++failures;
+            last_errno = errno;
+        }
+    }
+    if (failures) {
+        set_error("kill: %d of %zu processes could not be signalled (%s)", failures, pids.size(), strerror(last_errno));
+        return GMP_ERR_SYS;
+    }
+    return GMP_OK;
+}
+
+int mount_many(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int* done) {
+    if (done) *done = 0;
+    std::string cgroup_path;
+    int rc = pod_cgroup_path(env, pod, &cgroup_path);
+    if (rc != GMP_OK) return rc;
+    for (int i = 0; i < n; ++i) {  // ref: util.go:37-40
+        rc = write_permission(env, cgroup_path, gpus[i].minor_number, "devices.allow");
+        if (rc != GMP_OK) return rc;
+    }
+    std::vector<std::string> pids;  // ref: util.go:44-55
+    rc = read_cgroup_pids(env, cgroup_path, &pids);
+    if (rc != GMP_OK) return rc;
+    int pid = 0;
+    rc = first_pid(pids, &pid);
+    if (rc != GMP_OK) return rc;
+    gmp_ns_config cfg;  // ref: util.go:60-63
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.mount = 1;
+    cfg.target = pid;
+    std::string ns_path;
+    rc = mount_ns_path(env, &cfg, &ns_path);
+    if (rc != GMP_OK) return rc;
+    std::vector<NodeJob> jobs;
+    for (int i = 0; i < n; ++i) jobs.push_back({NodeOp::kCreate, device_node_path(env, &gpus[i]), gpus[i].minor_number});
+    return run_in_mount_ns(ns_path, jobs, done);  // ref: util.go:64-67
+}
+
+int unmount_many(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int force, int* done) {
+    if (done) *done = 0;
+    std::string cgroup_path;
+    int rc = pod_cgroup_path(env, pod, &cgroup_path);
+    if (rc != GMP_OK) return rc;
+    std::vector<std::string> pids;  // ref: util.go:93-98
+    rc = read_cgroup_pids(env, cgroup_path, &pids);
+    if (rc != GMP_OK) return rc;
+    std::vector<std::string> victims;  // ref: util.go:100-109
+    for (int i = 0; i < n; ++i) {
+        std::vector<std::string> busy;
+        rc = busy_pids(pids, &gpus[i], &busy);
+        if (rc != GMP_OK) return rc;
+        if (!busy.empty() && !force) {
+            set_error("GPU: %s is busy", gpus[i].device_file_path);
+            return GMP_ERR_BUSY;
+        }
+        for (const std::string& b : busy)
+            if (std::find(victims.begin(), victims.end(), b) == victims.end()) victims.push_back(b);
+    }
+    for (int i = 0; i < n; ++i) {  // ref: util.go:112-115
+        rc = write_permission(env, cgroup_path, gpus[i].minor_number, "devices.deny");
+        if (rc != GMP_OK) return rc;
+    }
+    int pid = 0;  // ref: util.go:118-124
+    rc = first_pid(pids, &pid);
+    if (rc != GMP_OK) return rc;
+    gmp_ns_config cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.mount = 1;
+    cfg.target = pid;
+    std::string ns_path;
+    rc = mount_ns_path(env, &cfg, &ns_path);
+    if (rc != GMP_OK) return rc;
+    std::vector<NodeJob> jobs;
+    for (int i = 0; i < n; ++i) jobs.push_back({NodeOp::kRemove, device_node_path(env, &gpus[i]), gpus[i].minor_number});
+    rc = run_in_mount_ns(ns_path, jobs, done);  // ref: util.go:131-134
+    if (rc != GMP_OK) return rc;
+    if (!victims.empty()) return kill_pids(victims);  // ref: util.go:137-142
+    return GMP_OK;
+}
+
+std::vector<std::string> to_vector(const char* const* parts, int n) {
+    std::vector<std::string> v;
+    for (int i = 0; i < n; ++i) v.emplace_back(parts[i] ? parts[i] : "");
+    return v;
+}
+
+// encoding/json string in json.Marshal's default (HTML-escaping) mode
+std::string json_quote(const char* text) {
+    std::string out = "\"";
+    for (const unsigned char* c = reinterpret_cast<const unsigned char*>(text); *c; ++c) {
+        char esc[8];
+        if (*c == '"') out += "\\\"";
+        else if (*c == '\\') out += "\\\\";
+        else if (*c == '\n') out += "\\n";
+        else if (*c == '\r') out += "\\r";
+        else if (*c == '\t') out += "\\t";
+        else if (*c < 0x20 || *c == '<' || *c == '>' || *c == '&') {
+            snprintf(esc, sizeof(esc), "\\u%04x", *c);
+            out += esc;
+        } else out += (char)*c;
+    }
+    return out + "\"";
+}
+
+std::vector<int> pod_gpu_indices(const gmp_gpu* list, int n, const std::string& pod_name, const std::string& ns) {
+    std::vector<int> idx;
+    const std::string needle = pod_name + "-slave-pod-";
+    for (int i = 0; i < n; ++i) {
+        const std::string owner = list[i].pod_name, owner_ns = list[i].ns;
+        const bool own = owner == pod_name && owner_ns == ns;
+        const bool slave = owner.find(needle) != std::string::npos && owner_ns == kGpuPoolNamespace;  // substring, ref: collector.go:158
+        if (own || slave) idx.push_back(i);
+    }
+    return idx;
+}
+
+int mount_type_of(const gmp_gpu* list, const std::vector<int>& idx, const std::string& pod_name) {
+    if (idx.empty()) return GMP_MOUNT_NONE;
+    std::vector<std::string> slaves;
+    for (int i : idx) {
+        const std::string owner = list[i].pod_name;
+        if (owner != pod_name && std::find(slaves.begin(), slaves.end(), owner) == slaves.end()) slaves.push_back(owner);
+    }
+    return slaves.size() < idx.size() ? GMP_MOUNT_ENTIRE : GMP_MOUNT_SINGLE;  // ref: allocator.go:182-186
+}
+
+// Every entry point funnels through this so that no C++ exception crosses the C ABI.
+template <typename F>
+int guarded(F&& body) {
+    clear_error();
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        set_error("out of host memory");
+        return GMP_ERR_NOMEM;
+    } catch (...) {
+        set_error("unexpected C++ exception");
+        return GMP_ERR_INVALID;
+    }
+}
+
+#define REQUIRE(cond)                          \
+    do {                                       \
+        if (!(cond)) {                         \
+            set_error("bad argument: %s", #cond); \
+            return GMP_ERR_INVALID;            \
+        }                                      \
+    } while (0)
+
+}  // namespace
+
+// ---- C ABI ---------------------------------------------------------------------------------------------
+extern "C" int gmp_device_new(int minor, const char* uuid, gmp_gpu* out) {
+    return guarded([&]() -> int {
+        REQUIRE(out != nullptr && uuid != nullptr);
+        memset(out, 0, sizeof(*out));
+        out->minor_number = minor;
+        put(out->device_file_path, std::string(kDevPrefix) + std::to_string(minor));
+        put(out->uuid, uuid);
+        put(out->state, kFreeState);
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_device_string(const gmp_gpu* g, char* buf, size_t cap) {
+    return guarded([&]() -> int {
+        REQUIRE(g != nullptr);
+        std::string s = "{\"MinorNumber\":" + std::to_string(g->minor_number);
+        s += ",\"DeviceFilePath\":" + json_quote(g->device_file_path);
+        s += ",\"UUID\":" + json_quote(g->uuid);
+        s += ",\"State\":" + json_quote(g->state);
+        s += ",\"PodName\":" + json_quote(g->pod_name);
+        s += ",\"Namespace\":" + json_quote(g->ns) + "}";
+        return emit(s, buf, cap);
+    });
+}
+
+extern "C" int gmp_device_reset_state(gmp_gpu* g) {
+    return guarded([&]() -> int {
+        REQUIRE(g != nullptr);
+        g->pod_name[0] = '\0';
+        g->ns[0] = '\0';
+        put(g->state, kFreeState);
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_get_pod_qos(const gmp_pod* pod, int* qos) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && qos != nullptr && (pod->n_containers == 0 || pod->containers != nullptr));
+        return pod_qos(pod, qos);
+    });
+}
+
+extern "C" int gmp_cgroup_name_check(const char* component) {
+    return guarded([&]() -> int {
+        REQUIRE(component != nullptr);
+        if (!component_ok(component)) {
+            set_error("invalid character in component [\"%s\"] of CgroupName", component);
+            return GMP_ERR_NAME;
+        }
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_cgroup_name_to_systemd(const char* const* parts, int n, char* out, size_t cap) {
+    return guarded([&]() -> int {
+        REQUIRE(n >= 0 && (n == 0 || parts != nullptr));
+        std::string s;
+        int rc = to_systemd(to_vector(parts, n), &s);
+        return rc != GMP_OK ? rc : emit(s, out, cap);
+    });
+}
+
+extern "C" int gmp_cgroup_name_to_cgroupfs(const char* const* parts, int n, char* out, size_t cap) {
+    return guarded([&]() -> int {
+        REQUIRE(n >= 0 && (n == 0 || parts != nullptr));
+        return emit(to_cgroupfs(to_vector(parts, n)), out, cap);
+    });
+}
+
+extern "C" int gmp_get_cgroup_driver(char* out, size_t cap) {
+    return guarded([&]() -> int {
+        std::string d;
+        int rc = cgroup_driver(nullptr, &d);
+        if (rc != GMP_OK) {
+            if (out && cap) out[0] = '\0';
+            return rc;
+        }
+        return emit(d, out, cap);
+    });
+}
+
+extern "C" int gmp_get_cgroup_name(const char* driver, const gmp_pod* pod, const char* container_id, char* out, size_t cap) {
+    return guarded([&]() -> int {
+        REQUIRE(driver != nullptr && pod != nullptr && container_id != nullptr);
+        std::string s;
+        int rc = cgroup_name(driver, pod, container_id, &s);
+        return rc != GMP_OK ? rc : emit(s, out, cap);
+    });
+}
+
+extern "C" int gmp_get_device_group_path(const gmp_mount_env* env, const char* cgroup_path, char* out, size_t cap) {
+    return guarded([&]() -> int {
+        REQUIRE(cgroup_path != nullptr);
+        return emit(devices_root(env) + cgroup_path, out, cap);
+    });
+}
+
+extern "C" int gmp_get_cgroup_pids(const gmp_mount_env* env, const char* cgroup_path, char (*pids)[16], int cap, int* n) {
+    return guarded([&]() -> int {
+        REQUIRE(cgroup_path != nullptr && n != nullptr && cap >= 0 && (cap == 0 || pids != nullptr));
+        *n = 0;
+        std::vector<std::string> v;
+        int rc = read_cgroup_pids(env, cgroup_path, &v);
+        if (rc != GMP_OK) return rc;
+        *n = (int)v.size();
+        for (int i = 0; i < (int)v.size() && i < cap; ++i) put(pids[i], v[(size_t)i]);
+        if ((int)v.size() > cap) {
+            set_error("%zu pids, capacity %d", v.size(), cap);
+            return GMP_ERR_BUFFER_TOO_SMALL;
+        }
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_add_gpu_device_permission(const gmp_mount_env* env, const char* cgroup_path, const gmp_gpu* gpu) {
+    return guarded([&]() -> int {
+        REQUIRE(cgroup_path != nullptr && gpu != nullptr);
+        return write_permission(env, cgroup_path, gpu->minor_number, "devices.allow");
+    });
+}
+
+extern "C" int gmp_remove_gpu_device_permission(const gmp_mount_env* env, const char* cgroup_path, const gmp_gpu* gpu) {
+    return guarded([&]() -> int {
+        REQUIRE(cgroup_path != nullptr && gpu != nullptr);
+        return write_permission(env, cgroup_path, gpu->minor_number, "devices.deny");
+    });
+}
+
+namespace {
+// ref: namespace.go:70-165, flag for flag and in the same order
+int build_nsenter_argv(const gmp_ns_config* c, std::vector<std::string>* argv) {
+    if (c->target == 0) {
+        set_error("Target must be specified ");
+        return GMP_ERR_TARGET;
+    }
+    auto flag = [&](int enabled, const char* file, const char* with_file, const char* bare) {
+        if (!enabled) return;
+        if (file != nullptr && file[0] != '\0') argv->push_back(std::string(with_file) + file);
+        else argv->push_back(bare);
+    };
+    argv->assign({"nsenter", "--target", std::to_string(c->target)});
+    flag(c->cgroup, c->cgroup_file, "--cgroup=", "--cgroup");
+    if (c->follow_context) argv->push_back("--follow-context");
+    if (c->gid != 0) {
+        argv->push_back("--setgid");
+        argv->push_back(std::to_string(c->gid));
+    }
+    flag(c->ipc, c->ipc_file, "--ip=", "--ipc");  // "--ip=" as spelled at namespace.go:96
+    flag(c->mount, c->mount_file, "--mount=", "--mount");
+    flag(c->net, c->net_file, "--net=", "--net");
+    if (c->no_fork) argv->push_back("--no-fork");
+    flag(c->pid, c->pid_file, "--pid=", "--pid");
+    if (c->preserve_credentials) argv->push_back("--preserve-credentials");
+    if (c->root_directory != nullptr && c->root_directory[0] != '\0') {
+        argv->push_back("--root");
+        argv->push_back(c->root_directory);
+    }
+    if (c->uid != 0) {
+        argv->push_back("--setuid");
+        argv->push_back(std::to_string(c->uid));
+    }
+    flag(c->user, c->user_file, "--user=", "--user");
+    flag(c->uts, c->uts_file, "--uts=", "--uts");
+    if (c->working_directory != nullptr && c->working_directory[0] != '\0') {
+        argv->push_back("--wd");
+        argv->push_back(c->working_directory);
+    }
+    return GMP_OK;
+}
+}  // namespace
+
+extern "C" int gmp_ns_build_command(const gmp_ns_config* cfg, char* out, size_t cap, int* argc) {
+    return guarded([&]() -> int {
+        REQUIRE(cfg != nullptr && argc != nullptr);
+        std::vector<std::string> argv;
+        int rc = build_nsenter_argv(cfg, &argv);
+        if (rc != GMP_OK) return rc;
+        std::string flat;
+        for (const std::string& a : argv) {
+            flat += a;
+            flat += '\0';
+        }
+        if (out == nullptr || cap < flat.size()) {
+            set_error("output buffer of %zu bytes too small for %zu", cap, flat.size());
+            return GMP_ERR_BUFFER_TOO_SMALL;
+        }
+        memcpy(out, flat.data(), flat.size());
+        *argc = (int)argv.size();
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_ns_execute(const gmp_ns_config* cfg, const char* program, const char* const* args, int nargs, char* out,
+                              size_t out_cap, char* err, size_t err_cap) {
+    return guarded([&]() -> int {
+        REQUIRE(cfg != nullptr && program != nullptr && nargs >= 0 && (nargs == 0 || args != nullptr));
+        std::vector<std::string> argv;
+        int rc = build_nsenter_argv(cfg, &argv);
+        if (rc != GMP_OK) {
+            set_error("Error while building command: Target must be specified  ");  // ref: namespace.go:51
+            return rc;
+        }
+        argv.push_back(program);  // ref: namespace.go:59-60
+        for (int i = 0; i < nargs; ++i) argv.push_back(args[i]);
+        std::vector<char*> cargv;
+        for (std::string& a : argv) cargv.push_back(&a[0]);
+        cargv.push_back(nullptr);
+        int po[2], pe[2];
+        if (pipe2(po, O_CLOEXEC) != 0 || pipe2(pe, O_CLOEXEC) != 0) {
+            set_error("pipe2: %s", strerror(errno));
+            return GMP_ERR_SYS;
+        }
+        const pid_t child = fork();
+        if (child < 0) {
+            set_error("fork: %s", strerror(errno));
+            return GMP_ERR_SYS;
+        }
+        if (child == 0) {
+            dup2(po[1], 1);
+            dup2(pe[1], 2);
+            execvp(cargv[0], cargv.data());
+            _exit(127);
+        }
+        close(po[1]);
+        close(pe[1]);
+        auto drain = [](int fd, char* dst, size_t cap) {
+            size_t len = 0;
+            char tmp[1024];
+            ssize_t r;
+            while ((r = read(fd, tmp, sizeof(tmp))) > 0) {
+                if (dst != nullptr && len + 1 < cap) {
+                    const size_t take = std::min((size_t)r, cap - 1 - len);
+                    memcpy(dst + len, tmp, take);
+                    len += take;
+                }
+            }
+            if (dst != nullptr && cap) dst[len] = '\0';
+            close(fd);
+        };
+        drain(po[0], out, out_cap);  // small outputs only: the reference's callers run mknod/rm/kill
+        drain(pe[0], err, err_cap);
+        int status = 0;
+        while (waitpid(child, &status, 0) < 0 && errno == EINTR) {
+        }
+        if (!WIFEXITED(status) || WEXITSTATUS(status) != 0) {
+            set_error("Error while executing command: exit status %d ", WIFEXITED(status) ? WEXITSTATUS(status) : -1);
+            return GMP_ERR_SYS;
+        }
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_ns_add_gpu_device_file(const gmp_mount_env* env, const gmp_ns_config* cfg, const gmp_gpu* gpu) {
+    return guarded([&]() -> int {
+        REQUIRE(gpu != nullptr);
+        std::string ns_path;
+        int rc = mount_ns_path(env, cfg, &ns_path);
+        if (rc != GMP_OK) return rc;
+        return run_in_mount_ns(ns_path, {{NodeOp::kCreate, device_node_path(env, gpu), gpu->minor_number}}, nullptr);
+    });
+}
+
+extern "C" int gmp_ns_remove_gpu_device_file(const gmp_mount_env* env, const gmp_ns_config* cfg, const gmp_gpu* gpu) {
+    return guarded([&]() -> int {
+        REQUIRE(gpu != nullptr);
+        std::string ns_path;
+        int rc = mount_ns_path(env, cfg, &ns_path);
+        if (rc != GMP_OK) return rc;
+        return run_in_mount_ns(ns_path, {{NodeOp::kRemove, device_node_path(env, gpu), gpu->minor_number}}, nullptr);
+    });
+}
+
+extern "C" int gmp_ns_kill_running_gpu_processes(const gmp_ns_config* cfg, const char* const* pids, int n) {
+    return guarded([&]() -> int {
+        REQUIRE(cfg != nullptr && n >= 0 && (n == 0 || pids != nullptr));
+        if (cfg->target == 0) {
+            set_error("Target must be specified ");
+            return GMP_ERR_TARGET;
+        }
+        return kill_pids(to_vector(pids, n));
+    });
+}
+
+extern "C" int gmp_can_mount(int mount_type, int request_is_entire_mount) {
+    // ref: util.go:207-226
+    if (mount_type == GMP_MOUNT_UNKNOWN) return 0;
+    if (mount_type != GMP_MOUNT_NONE && request_is_entire_mount) return 0;
+    if (mount_type == GMP_MOUNT_ENTIRE) return 0;
+    return (mount_type == GMP_MOUNT_NONE || mount_type == GMP_MOUNT_SINGLE) ? 1 : 0;
+}
+
+extern "C" int gmp_get_pod_gpu_processes(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpu, char (*pids)[16],
+                                         int cap, int* n) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && gpu != nullptr && n != nullptr && cap >= 0 && (cap == 0 || pids != nullptr));
+        *n = 0;
+        std::string cgroup_path;
+        int rc = pod_cgroup_path(env, pod, &cgroup_path);
+        if (rc != GMP_OK) return rc;
+        std::vector<std::string> in_pod, busy;
+        rc = read_cgroup_pids(env, cgroup_path, &in_pod);
+        if (rc != GMP_OK) return rc;
+        rc = busy_pids(in_pod, gpu, &busy);
+        if (rc != GMP_OK) return rc;
+        *n = (int)busy.size();
+        for (int i = 0; i < (int)busy.size() && i < cap; ++i) put(pids[i], busy[(size_t)i]);
+        if ((int)busy.size() > cap) return GMP_ERR_BUFFER_TOO_SMALL;
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_mount_gpu(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpu) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && gpu != nullptr);
+        return mount_many(env, pod, gpu, 1, nullptr);
+    });
+}
+
+extern "C" int gmp_unmount_gpu(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpu, int force) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && gpu != nullptr);
+        return unmount_many(env, pod, gpu, 1, force, nullptr);
+    });
+}
+
+extern "C" int gmp_mount_gpus(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int* done) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && n >= 0 && (n == 0 || gpus != nullptr));
+        if (n == 0) {
+            if (done) *done = 0;
+            return GMP_OK;
+        }
+        return mount_many(env, pod, gpus, n, done);
+    });
+}
+
+extern "C" int gmp_unmount_gpus(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int force, int* done) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && n >= 0 && (n == 0 || gpus != nullptr));
+        if (n == 0) {
+            if (done) *done = 0;
+            return GMP_OK;
+        }
+        return unmount_many(env, pod, gpus, n, force, done);
+    });
+}
+
+extern "C" int gmp_get_gpu_by_uuid(const gmp_gpu* list, int n, const char* uuid, int* index) {
+    return guarded([&]() -> int {
+        REQUIRE(uuid != nullptr && index != nullptr && n >= 0 && (n == 0 || list != nullptr));
+        for (int i = 0; i < n; ++i) {
+            if (strcmp(list[i].uuid, uuid) == 0) {
+                *index = i;
+                return GMP_OK;
+            }
+        }
+        *index = -1;
+        set_error("No GPU with UUID%s", uuid);  // ref: collector.go:87 (no space there)
+        return GMP_ERR_NO_DEVICE;
+    });
+}
+
+extern "C" int gmp_update_gpu_status(gmp_gpu* list, int n, const gmp_pod_resources* pods, int n_pods) {
+    return guarded([&]() -> int {
+        REQUIRE(n >= 0 && n_pods >= 0 && (n == 0 || list != nullptr) && (n_pods == 0 || pods != nullptr));
+        for (int i = 0; i < n; ++i) {  // resetGPUStatus, ref: collector.go:140-144
+            list[i].pod_name[0] = '\0';
+            list[i].ns[0] = '\0';
+            put(list[i].state, kFreeState);
+        }
+        for (int p = 0; p < n_pods; ++p) {
+            for (int c = 0; c < pods[p].n_containers; ++c) {
+                const gmp_container_entry& ce = pods[p].containers[c];
+                for (int d = 0; d < ce.n_devices; ++d) {
+                    const gmp_container_devices& dev = ce.devices[d];
+                    if (dev.resource_name == nullptr || strcmp(dev.resource_name, kNvidiaResourceName) != 0) continue;
+                    for (int u = 0; u < dev.n_ids; ++u) {
+                        int idx = -1;
+                        for (int i = 0; i < n && idx < 0; ++i)
+                            if (strcmp(list[i].uuid, dev.device_ids[u]) == 0) idx = i;
+                        if (idx < 0) {
+                            set_error("No GPU with UUID%s", dev.device_ids[u]);
+                            return GMP_ERR_NO_DEVICE;  // ref: collector.go:123-125
+                        }
+                        put(list[idx].state, kAllocatedState);
+                        put(list[idx].pod_name, pods[p].name ? pods[p].name : "");
+                        put(list[idx].ns, pods[p].ns ? pods[p].ns : "");
+                    }
+                }
+            }
+        }
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_get_pod_gpu_resources(const gmp_gpu* list, int n, const char* pod_name, const char* ns, int32_t* indices,
+                                         int* count) {
+    return guarded([&]() -> int {
+        REQUIRE(pod_name != nullptr && ns != nullptr && count != nullptr && n >= 0 && (n == 0 || (list != nullptr && indices != nullptr)));
+        const std::vector<int> idx = pod_gpu_indices(list, n, pod_name, ns);
+        for (size_t i = 0; i < idx.size(); ++i) indices[i] = idx[i];
+        *count = (int)idx.size();
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_get_mount_type(const gmp_gpu* list, int n, const char* pod_name, const char* ns, int* mount_type) {
+    return guarded([&]() -> int {
+        REQUIRE(pod_name != nullptr && ns != nullptr && mount_type != nullptr && n >= 0 && (n == 0 || list != nullptr));
+        *mount_type = mount_type_of(list, pod_gpu_indices(list, n, pod_name, ns), pod_name);
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_get_remove_gpu(const gmp_gpu* list, int n, const char* owner_name, const char* owner_ns,
+                                  const char* const* uuids, int n_uuids, int32_t* indices, int* count) {
+    return guarded([&]() -> int {
+        REQUIRE(owner_name != nullptr && owner_ns != nullptr && count != nullptr && n >= 0 && n_uuids >= 0);
+        REQUIRE((n == 0 || (list != nullptr && indices != nullptr)) && (n_uuids == 0 || uuids != nullptr));
+        const std::vector<int> mine = pod_gpu_indices(list, n, owner_name, owner_ns);
+        const int type = mount_type_of(list, mine, owner_name);
+        const std::vector<std::string> wanted = to_vector(uuids, n_uuids);
+        std::vector<int> picked;
+        for (int i : mine) {  // ref: allocator.go:112-119
+            const bool listed = std::find(wanted.begin(), wanted.end(), std::string(list[i].uuid)) != wanted.end();
+            if ((type == GMP_MOUNT_ENTIRE || listed) && std::string(list[i].pod_name) != owner_name) picked.push_back(i);
+        }
+        if ((size_t)n_uuids != picked.size()) picked.clear();  // ref: allocator.go:121-123
+        for (size_t i = 0; i < picked.size(); ++i) indices[i] = picked[i];
+        *count = (int)picked.size();
+        return GMP_OK;
+    });
+}
+
+extern "C" int gmp_slave_pod_name(const char* owner, const unsigned char rand3[3], char* out, size_t cap) {
+    return guarded([&]() -> int {
+        REQUIRE(owner != nullptr && rand3 != nullptr);
+        char hex[8];
+        snprintf(hex, sizeof(hex), "%02x%02x%02x", rand3[0], rand3[1], rand3[2]);
+        return emit(std::string(owner) + "-slave-pod-" + hex, out, cap);
+    });
+}

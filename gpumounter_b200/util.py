@@ -1,0 +1,59 @@
+"""ref: pkg/util/util.go — node-local mount / unmount orchestration, over the C ABI."""
+
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+from ._lib import check, lib
+from ._model import MountEnv, Pod, env_ptr
+from .device import NvidiaGPU, as_c_array
+
+# ref: pkg/util/gpu/types.go:22-27
+EntireMount, SingleMount, NoMount, UnknownMount = "entire-mount", "single-mount", "no-mount", "unknown-mount"
+MOUNT_TYPE_CODE = {EntireMount: 0, SingleMount: 1, NoMount: 2, UnknownMount: 3}
+MOUNT_TYPE_NAME = {v: k for k, v in MOUNT_TYPE_CODE.items()}
+
+
+def MountGPU(pod: Pod, gpu: NvidiaGPU, env: Optional[MountEnv] = None) -> None:  # ref: util.go:17-71
+    c = pod.to_c()
+    check(lib().gmp_mount_gpu(env_ptr(env), ctypes.byref(c), ctypes.byref(gpu._c)), "MountGPU")
+
+
+def UnmountGPU(pod: Pod, gpu: NvidiaGPU, forceRemove: bool, env: Optional[MountEnv] = None) -> None:  # ref: util.go:73-147
+    c = pod.to_c()
+    check(lib().gmp_unmount_gpu(env_ptr(env), ctypes.byref(c), ctypes.byref(gpu._c), int(forceRemove)), "UnmountGPU")
+
+
+def MountGPUs(pod: Pod, gpus: Sequence[NvidiaGPU], env: Optional[MountEnv] = None) -> int:
+    """Batched form of the loop at ref: pkg/server/gpu-mount/server.go:80-95 (no reference counterpart)."""
+    c = pod.to_c()
+    done = ctypes.c_int(0)
+    check(lib().gmp_mount_gpus(env_ptr(env), ctypes.byref(c), as_c_array(gpus), len(gpus), ctypes.byref(done)), "MountGPUs")
+    return done.value
+
+
+def UnmountGPUs(pod: Pod, gpus: Sequence[NvidiaGPU], forceRemove: bool, env: Optional[MountEnv] = None) -> int:
+    c = pod.to_c()
+    done = ctypes.c_int(0)
+    check(lib().gmp_unmount_gpus(env_ptr(env), ctypes.byref(c), as_c_array(gpus), len(gpus), int(forceRemove),
+                                 ctypes.byref(done)), "UnmountGPUs")
+    return done.value
+
+
+def GetPodGPUProcesses(pod: Pod, gpu: NvidiaGPU, env: Optional[MountEnv] = None) -> Optional[List[str]]:  # ref: util.go:152-196
+    cap = 2048
+    arr = ((ctypes.c_char * 16) * cap)()
+    n = ctypes.c_int()
+    c = pod.to_c()
+    check(lib().gmp_get_pod_gpu_processes(env_ptr(env), ctypes.byref(c), ctypes.byref(gpu._c), arr, cap, ctypes.byref(n)),
+          "GetPodGPUProcesses")
+    return None if n.value == 0 else [arr[i].value.decode() for i in range(n.value)]
+
+
+def ContainString(stringList: Sequence[str], aimString: str) -> bool:  # ref: util.go:198-205
+    return any(s == aimString for s in stringList)
+
+
+def CanMount(mountType: str, isEntireMount: bool) -> bool:  # ref: util.go:207-226 (request.IsEntireMount passed directly)
+    return bool(lib().gmp_can_mount(MOUNT_TYPE_CODE[mountType], int(isEntireMount)))

@@ -277,6 +277,164 @@ typedef struct gmp_hbm_result {
 /* uuid == NULL or "" probes CUDA ordinal 0. */
 GMP_API int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out);
 
+/* ------------------------------------------------------------------------- */
+/* 6. Node-local mount path (native restatement of the worker's L2/L3 logic)  */
+/* ------------------------------------------------------------------------- */
+/*
+ * Same functions, argument meaning and error behaviour as the reference's Go
+ * packages, so the worker can call them through cgo one for one; what changes
+ * is the mechanism: the reference shells out (`sh -c "echo ... > devices.allow"`,
+ * `nsenter --target P --mount sh -c "mknod ..."`, 2-3 fork/execs per GPU and an
+ * image that must contain sh/mknod/rm/kill, ref: docs/guide/FAQ.md:3-4); here
+ * the permission line is written with write(2) and the device node is made by
+ * a forked child that joins the target's mount namespace with setns(2) and
+ * calls mknod(2)/unlink(2) itself — no shell, nothing needed inside the image.
+ * Where Go would panic the functions return an error code instead.
+ */
+
+/* The device record, ref: pkg/device/nvidia.go:10-17 (same fields, same order). */
+typedef struct gmp_gpu {
+    int32_t minor_number;
+    char    device_file_path[64];  /* "/dev/nvidia" + minor, ref: nvidia.go:29,40 */
+    char    uuid[GMP_UUID_LEN];
+    char    state[24];             /* "GPU_FREE_STATE" | "GPU_ALLOCATED_STATE", ref: nvidia.go:20-23 */
+    char    pod_name[256];
+    char    ns[256];
+} gmp_gpu;
+
+#define GMP_NVIDIA_MAJOR 195  /* ref: nvidia.go:37 */
+
+GMP_API int gmp_device_new(int minor, const char* uuid, gmp_gpu* out);        /* ref: nvidia.go:25-34 */
+GMP_API int gmp_device_string(const gmp_gpu* gpu, char* buf, size_t cap);     /* ref: nvidia.go:43-50, Go json.Marshal output */
+GMP_API int gmp_device_reset_state(gmp_gpu* gpu);                             /* ref: nvidia.go:52-56 */
+
+/* The fields of corev1.Pod the path reads.  Quantities are the strings of the
+ * pod spec ("500m", "1Gi"); NULL = key absent.  Only cpu and memory take part
+ * in QoS (ref: pkg/util/cgroup/cgroup.go:171-175). */
+typedef struct gmp_container_resources {
+    const char* cpu_request;
+    const char* memory_request;
+    const char* cpu_limit;
+    const char* memory_limit;
+} gmp_container_resources;
+
+typedef struct gmp_pod {
+    const char* name;
+    const char* ns;
+    const char* uid;
+    const char* node_name;
+    const char* container_id;  /* Status.ContainerStatuses[0].ContainerID, "docker://<id>" (ref: util.go:22-23) */
+    int32_t     n_containers;
+    const gmp_container_resources* containers;
+} gmp_pod;
+
+enum { GMP_QOS_GUARANTEED = 0, GMP_QOS_BURSTABLE = 1, GMP_QOS_BESTEFFORT = 2 };
+enum { GMP_MOUNT_ENTIRE = 0, GMP_MOUNT_SINGLE = 1, GMP_MOUNT_NONE = 2, GMP_MOUNT_UNKNOWN = 3 }; /* ref: pkg/util/gpu/types.go:22-27 */
+
+/* ref: cgroup.go:177-237 GetPodQOS */
+GMP_API int gmp_get_pod_qos(const gmp_pod* pod, int* qos);
+/* ref: cgroup.go:32-45 NewCgroupName's check; GMP_ERR_NAME where Go panics */
+GMP_API int gmp_cgroup_name_check(const char* component);
+/* ref: cgroup.go:52-68 CgroupName.ToSystemd (with runc's ExpandSlice, go.mod:8) */
+GMP_API int gmp_cgroup_name_to_systemd(const char* const* parts, int n, char* out, size_t cap);
+/* ref: cgroup.go:74-76 CgroupName.ToCgroupfs */
+GMP_API int gmp_cgroup_name_to_cgroupfs(const char* const* parts, int n, char* out, size_t cap);
+/* ref: cgroup.go:78-84 GetCgroupDriver; reads $CGROUP_DRIVER; GMP_ERR_CGROUP_DRIVER with
+ * "unsupported cgroup driver: <value>" as the detail */
+GMP_API int gmp_get_cgroup_driver(char* out, size_t cap);
+/* ref: cgroup.go:86-113 GetCgroupName */
+GMP_API int gmp_get_cgroup_name(const char* cgroup_driver, const gmp_pod* pod, const char* container_id,
+                                char* out, size_t cap);
+
+/* Where the node's files live.  NULL (or NULL members) = the reference's constants.
+ * Tests and the cluster-less harness point these at private directories. */
+typedef struct gmp_mount_env {
+    const char* devices_root;   /* "/sys/fs/cgroup/devices", ref: cgroup.go:116 */
+    const char* dev_prefix;     /* "/dev/nvidia", ref: nvidia.go:40 */
+    const char* cgroup_driver;  /* overrides $CGROUP_DRIVER when not NULL */
+    const char* proc_root;      /* "/proc": where <pid>/ns/mnt is looked up */
+} gmp_mount_env;
+
+/* ref: cgroup.go:115-118 GetDeviceGroupPath */
+GMP_API int gmp_get_device_group_path(const gmp_mount_env* env, const char* cgroup_path, char* out, size_t cap);
+/* ref: cgroup.go:120-141 GetCgroupPIDs: the lines of cgroup.procs that end in '\n' (a last
+ * line without newline is dropped, as there).  pids: caller array of char[16]; *n = lines found. */
+GMP_API int gmp_get_cgroup_pids(const gmp_mount_env* env, const char* cgroup_path, char (*pids)[16], int cap, int* n);
+/* ref: cgroup.go:143-155 / :157-169: writes "c 195:<minor> rw" to devices.allow / devices.deny */
+GMP_API int gmp_add_gpu_device_permission(const gmp_mount_env* env, const char* cgroup_path, const gmp_gpu* gpu);
+GMP_API int gmp_remove_gpu_device_permission(const gmp_mount_env* env, const char* cgroup_path, const gmp_gpu* gpu);
+
+/* nsenter configuration, ref: pkg/util/namespace/namespace.go:16-39 (same fields). */
+typedef struct gmp_ns_config {
+    int32_t cgroup;  const char* cgroup_file;
+    int32_t follow_context;
+    int32_t gid;
+    int32_t ipc;     const char* ipc_file;
+    int32_t mount;   const char* mount_file;
+    int32_t net;     const char* net_file;
+    int32_t no_fork;
+    int32_t pid;     const char* pid_file;
+    int32_t preserve_credentials;
+    const char* root_directory;
+    int32_t target;
+    int32_t uid;
+    int32_t user;    const char* user_file;
+    int32_t uts;     const char* uts_file;
+    const char* working_directory;
+} gmp_ns_config;
+
+/* ref: namespace.go:70-165 buildCommand: the nsenter argument vector, NUL-separated in `out`
+ * ("nsenter\0--target\0<pid>\0..."), *argc = number of strings.  GMP_ERR_TARGET when target == 0. */
+GMP_API int gmp_ns_build_command(const gmp_ns_config* cfg, char* out, size_t cap, int* argc);
+/* ref: namespace.go:42-68 Execute: runs `nsenter <flags> program args...` like the reference and
+ * captures stdout / stderr.  Kept for arbitrary programs; the three calls below do not use it. */
+GMP_API int gmp_ns_execute(const gmp_ns_config* cfg, const char* program, const char* const* args, int nargs,
+                           char* out, size_t out_cap, char* err, size_t err_cap);
+/* ref: namespace.go:167-177 / :179-189 / :191-201 — native: setns + mknod(2) / unlink(2); kill(2). */
+GMP_API int gmp_ns_add_gpu_device_file(const gmp_mount_env* env, const gmp_ns_config* cfg, const gmp_gpu* gpu);
+GMP_API int gmp_ns_remove_gpu_device_file(const gmp_mount_env* env, const gmp_ns_config* cfg, const gmp_gpu* gpu);
+GMP_API int gmp_ns_kill_running_gpu_processes(const gmp_ns_config* cfg, const char* const* pids, int n);
+
+/* ref: pkg/util/util.go:207-226 CanMount; returns 1 / 0 */
+GMP_API int gmp_can_mount(int mount_type, int request_is_entire_mount);
+/* ref: util.go:152-196 GetPodGPUProcesses: cgroup.procs ∩ NVML(graphics then compute) PIDs, in
+ * NVML order.  *n = 0 is the reference's nil. */
+GMP_API int gmp_get_pod_gpu_processes(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpu,
+                                      char (*pids)[16], int cap, int* n);
+/* ref: util.go:17-71 MountGPU and util.go:73-147 UnmountGPU (GMP_ERR_BUSY = the GPUBusy sentinel). */
+GMP_API int gmp_mount_gpu(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpu);
+GMP_API int gmp_unmount_gpu(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpu, int force);
+/*
+ * Batched forms (no reference counterpart): the loop of
+ * ref: pkg/server/gpu-mount/server.go:80-95 / :155-168 done with one cgroup
+ * path resolution, one cgroup.procs read and ONE namespace-entering child
+ * for all n GPUs.  All-or-nothing is NOT promised, as in the reference: on an
+ * error the GPUs already handled stay handled; *done counts them.
+ */
+GMP_API int gmp_mount_gpus(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int* done);
+GMP_API int gmp_unmount_gpus(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int force,
+                             int* done);
+
+/* kubelet PodResources listing, ref: collector.go:114-122 (v1alpha1 messages). */
+typedef struct gmp_container_devices { const char* resource_name; int32_t n_ids; const char* const* device_ids; } gmp_container_devices;
+typedef struct gmp_container_entry   { const char* name; int32_t n_devices; const gmp_container_devices* devices; } gmp_container_entry;
+typedef struct gmp_pod_resources     { const char* name; const char* ns; int32_t n_containers; const gmp_container_entry* containers; } gmp_pod_resources;
+
+/* ref: collector.go:81-88; *index = -1 and GMP_ERR_NO_DEVICE when absent */
+GMP_API int gmp_get_gpu_by_uuid(const gmp_gpu* list, int n, const char* uuid, int* index);
+/* ref: collector.go:113-135 (+ resetGPUStatus :140-144), applied to an already fetched listing */
+GMP_API int gmp_update_gpu_status(gmp_gpu* list, int n, const gmp_pod_resources* pods, int n_pods);
+/* ref: collector.go:155-161: the pod's own GPUs and those of its "<pod>-slave-pod-" pods in gpu-pool */
+GMP_API int gmp_get_pod_gpu_resources(const gmp_gpu* list, int n, const char* pod_name, const char* ns,
+                                      int32_t* indices, int* count);
+/* ref: allocator.go:158-187 GetMountType on a refreshed list */
+GMP_API int gmp_get_mount_type(const gmp_gpu* list, int n, const char* pod_name, const char* ns, int* mount_type);
+/* ref: allocator.go:101-126 GetRemoveGPU */
+GMP_API int gmp_get_remove_gpu(const gmp_gpu* list, int n, const char* owner_name, const char* owner_ns,
+                               const char* const* uuids, int n_uuids, int32_t* indices, int* count);
+/* ref: allocator.go:191-199: "<owner>-slave-pod-<6 hex>" from three random bytes */
+GMP_API int gmp_slave_pod_name(const char* owner, const unsigned char rand3[3], char* out, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

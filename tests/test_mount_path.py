@@ -1,0 +1,213 @@
+"""The effectful mount path: the product's native MountGPU / UnmountGPU against the oracle's fork/exec restatement of
+the reference, on a cluster-less target (own mount namespace + private /dev tmpfs + device-cgroup directory).
+CPU only; needs root, unshare and nsenter (skipped otherwise)."""
+
+import os
+import time
+
+import pytest
+
+from gpumounter_b200 import ProbeError, _lib, cgroup, device, namespace, util
+from gpumounter_b200._model import MountEnv, Pod
+from oracle import gmo_ref_ctypes as ref
+from tests import harness
+from tests.conftest import FAKE_UUIDS
+
+reason = harness.can_run()
+pytestmark = pytest.mark.skipif(reason is not None, reason=reason or "")
+
+
+def product_pod():
+    return Pod("gpu-pod", uid=harness.UID, container_id="docker://" + harness.CID)
+
+
+def oracle_pod():
+    return ref.Pod(uid=harness.UID, container_id="docker://" + harness.CID)
+
+
+def env_of(t: harness.Target) -> MountEnv:
+    return MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+
+
+def oracle_kw(t: harness.Target):
+    return dict(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+
+
+def test_harness_paths_agree_with_both_implementations():
+    with harness.Target() as t:
+        assert cgroup.GetCgroupName("cgroupfs", product_pod(), harness.CID) == t.cgroup_path
+        assert ref.get_cgroup_name("cgroupfs", oracle_pod(), harness.CID) == t.cgroup_path
+        assert cgroup.GetCgroupPIDs(t.cgroup_path, env_of(t)) == [str(t.pid)]
+
+
+def test_mount_creates_the_same_node_and_permission_line_as_the_reference_path(fake_nvml):
+    fake_nvml()
+    with harness.Target() as a, harness.Target() as b:
+        gpu = device.New(3, FAKE_UUIDS[0])
+        util.MountGPU(product_pod(), gpu, env_of(a))                       # product: write(2) + setns + mknod(2)
+        ref.mount_gpu(oracle_pod(), ref.device_new(3, FAKE_UUIDS[0]), **oracle_kw(b))  # oracle: sh/echo + nsenter/sh/mknod
+        assert a.node(3) == b.node(3) == (195, 3, 0o666)
+        assert a.nodes() == b.nodes() == ["nvidia3"]
+        assert a.host_sees() == b.host_sees() == []                         # only inside the target's mount namespace
+        assert a.read("devices.allow") == b.read("devices.allow") == "c 195:3 rw\n"
+        # unmount, not busy
+        util.UnmountGPU(product_pod(), gpu, False, env_of(a))
+        ref.unmount_gpu(oracle_pod(), ref.device_new(3, FAKE_UUIDS[0]), False, [], **oracle_kw(b))
+        assert a.node(3) is None and b.node(3) is None
+        assert a.read("devices.deny") == b.read("devices.deny") == "c 195:3 rw\n"
+
+
+def test_mount_twice_fails_like_mknod_does(fake_nvml):
+    fake_nvml()
+    with harness.Target() as a, harness.Target() as b:
+        gpu = device.New(5, FAKE_UUIDS[1])
+        util.MountGPU(product_pod(), gpu, env_of(a))
+        with pytest.raises(ProbeError) as e:
+            util.MountGPU(product_pod(), gpu, env_of(a))
+        assert e.value.code == _lib.GMP_ERR_SYS and "File exists" in e.value.detail
+        ref.mount_gpu(oracle_pod(), ref.device_new(5, FAKE_UUIDS[1]), **oracle_kw(b))
+        with pytest.raises(ref.OracleError) as oe:
+            ref.mount_gpu(oracle_pod(), ref.device_new(5, FAKE_UUIDS[1]), **oracle_kw(b))
+        assert oe.value.code == ref.E_EXEC and "File exists" in str(oe.value)
+        # removing a node that is not there fails in both, too (rm without -f)
+        with pytest.raises(ProbeError):
+            util.UnmountGPU(product_pod(), device.New(6, FAKE_UUIDS[2]), False, env_of(a))
+        with pytest.raises(ref.OracleError):
+            ref.unmount_gpu(oracle_pod(), ref.device_new(6, FAKE_UUIDS[2]), False, [], **oracle_kw(b))
+
+
+def test_empty_cgroup_and_missing_cgroup(fake_nvml):
+    fake_nvml()
+    with harness.Target() as t:
+        gpu = device.New(1, FAKE_UUIDS[0])
+        open(os.path.join(t.cgroup_dir, "cgroup.procs"), "w").write(str(t.pid))  # no trailing newline -> dropped
+        with pytest.raises(ProbeError) as e:
+            util.MountGPU(product_pod(), gpu, env_of(t))
+        assert e.value.code == _lib.GMP_ERR_EMPTY_CGROUP       # Go: index out of range panic at util.go:50
+        with pytest.raises(ref.OracleError) as oe:
+            ref.mount_gpu(oracle_pod(), ref.device_new(1, FAKE_UUIDS[0]), **oracle_kw(t))
+        assert oe.value.code == ref.E_PANIC_INDEX
+        assert t.read("devices.allow") == "c 195:1 rw\n"        # both wrote the permission before failing, as the reference does
+        env = env_of(t)
+        env.devices_root = t.base + "/nowhere"
+        with pytest.raises(ProbeError) as e:
+            util.MountGPU(product_pod(), gpu, env)
+        assert e.value.code == _lib.GMP_ERR_SYS
+
+
+def test_unsupported_cgroup_driver_is_reported_first(fake_nvml, monkeypatch):
+    fake_nvml()
+    monkeypatch.delenv("CGROUP_DRIVER", raising=False)
+    with harness.Target() as t:
+        env = MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix)  # driver from $CGROUP_DRIVER: unset
+        with pytest.raises(ProbeError) as e:
+            util.MountGPU(product_pod(), device.New(0, FAKE_UUIDS[0]), env)
+        assert e.value.code == _lib.GMP_ERR_CGROUP_DRIVER and e.value.detail == "unsupported cgroup driver: "
+        assert t.read("devices.allow") is None
+        monkeypatch.setenv("CGROUP_DRIVER", "cgroupfs")
+        util.MountGPU(product_pod(), device.New(0, FAKE_UUIDS[0]), env)
+        assert t.node(0) == (195, 0, 0o666)
+
+
+def test_busy_gpu_is_refused_without_force_and_killed_with_force(fake_nvml):
+    with harness.Target() as a, harness.Target() as b:
+        pa, pb = a.spawn_member(), b.spawn_member()
+        fake_nvml(procs=[(FAKE_UUIDS[0], pa.pid, 1 << 20, "compute"), (FAKE_UUIDS[0], 999999, 5, "graphics")])
+        gpu = device.New(2, FAKE_UUIDS[0])
+        ogpu = ref.device_new(2, FAKE_UUIDS[0])
+        util.MountGPU(product_pod(), gpu, env_of(a))
+        ref.mount_gpu(oracle_pod(), ogpu, **oracle_kw(b))
+        assert util.GetPodGPUProcesses(product_pod(), gpu, env_of(a)) == [str(pa.pid)]
+        assert util.GetPodGPUProcesses(product_pod(), device.New(4, FAKE_UUIDS[3]), env_of(a)) is None
+        with pytest.raises(ProbeError) as e:
+            util.UnmountGPU(product_pod(), gpu, False, env_of(a))
+        assert e.value.code == _lib.GMP_ERR_BUSY
+        with pytest.raises(ref.OracleError) as oe:
+            ref.unmount_gpu(oracle_pod(), ogpu, False, [999999, pb.pid], **oracle_kw(b))
+        assert oe.value.code == ref.E_BUSY
+        assert a.node(2) == b.node(2) == (195, 2, 0o666) and a.read("devices.deny") is None and b.read("devices.deny") is None
+        # force: permission removed, node removed, the pod's GPU process gets SIGTERM — in both
+        util.UnmountGPU(product_pod(), gpu, True, env_of(a))
+        ref.unmount_gpu(oracle_pod(), ogpu, True, [999999, pb.pid], **oracle_kw(b))
+        assert a.node(2) is None and b.node(2) is None
+        for p in (pa, pb):
+            assert p.wait(timeout=5) == -15
+        assert a.proc.poll() is None and b.proc.poll() is None  # the container's main process is untouched
+
+
+def test_batched_mount_and_unmount_of_eight_gpus(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target() as a, harness.Target() as b:
+        gpus = [device.New(m, u) for u, m, _ in gpus_cfg]
+        assert util.MountGPUs(product_pod(), gpus, env_of(a)) == 8
+        for u, m, _ in gpus_cfg:  # the reference's serial loop, server.go:80-95
+            ref.mount_gpu(oracle_pod(), ref.device_new(m, u), **oracle_kw(b))
+        assert a.nodes() == b.nodes() == [f"nvidia{i}" for i in range(8)]
+        assert [a.node(i) for i in range(8)] == [b.node(i) for i in range(8)] == [(195, i, 0o666) for i in range(8)]
+        assert a.read("devices.allow") == b.read("devices.allow")  # the last line written wins in a plain file
+        assert util.UnmountGPUs(product_pod(), gpus, False, env_of(a)) == 8
+        assert a.nodes() == []
+        # a failure part-way reports how far it got and leaves earlier GPUs mounted (no rollback, as in the reference)
+        util.MountGPU(product_pod(), gpus[2], env_of(a))
+        done = None
+        try:
+            util.MountGPUs(product_pod(), gpus, env_of(a))
+        except ProbeError as e:
+            done = e
+        assert done is not None and done.code == _lib.GMP_ERR_SYS
+        assert a.nodes() == sorted(f"nvidia{g.MinorNumber}" for g in gpus[:3])
+
+
+def test_namespace_calls_directly(fake_nvml):
+    fake_nvml()
+    with harness.Target() as t:
+        cfg = namespace.Config(Mount=True, Target=t.pid)
+        gpu = device.New(7, FAKE_UUIDS[7])
+        env = env_of(t)
+        namespace.AddGPUDeviceFile(cfg, gpu, env)
+        assert t.node(7) == (195, 7, 0o666)
+        out, err = cfg.Execute("sh", "-c", f"ls {t.devdir}")   # the reference's generic nsenter path still works
+        assert out.split() == ["nvidia7"] and err == ""
+        namespace.RemoveGPUDeviceFile(cfg, gpu, env)
+        assert t.node(7) is None
+        with pytest.raises(ProbeError) as e:
+            namespace.AddGPUDeviceFile(namespace.Config(Mount=True, Target=0), gpu, env)
+        assert e.value.code == _lib.GMP_ERR_TARGET
+        with pytest.raises(ProbeError) as e:
+            namespace.AddGPUDeviceFile(namespace.Config(Mount=True, Target=2 ** 22 + 12345), gpu, env)
+        assert e.value.code == _lib.GMP_ERR_SYS
+        p = t.spawn_member()
+        namespace.KillRunningGPUProcesses(cfg, [str(p.pid)])
+        assert p.wait(timeout=5) == -15
+        with pytest.raises(ProbeError):
+            namespace.KillRunningGPUProcesses(cfg, [str(p.pid)])  # already gone: kill(1) would fail as well
+
+
+REAL = "/sys/fs/cgroup/devices"
+
+
+@pytest.mark.skipif(not (os.path.isdir(REAL) and os.access(REAL, os.W_OK)), reason="no writable cgroup-v1 devices hierarchy")
+def test_real_devices_cgroup_allow_and_deny(fake_nvml):
+    fake_nvml()
+    try:
+        t = harness.Target(real_cgroup=True).start()
+    except OSError as e:
+        pytest.skip(f"cannot create a devices cgroup: {e}")
+    try:
+        with open(os.path.join(t.cgroup_dir, "devices.deny"), "w") as f:
+            f.write("a")  # start from an empty allow-list so that the effect is visible in devices.list
+        assert t.read("devices.list") == ""
+        gpu = device.New(3, FAKE_UUIDS[0])
+        util.MountGPU(product_pod(), gpu, env_of(t))
+        assert t.read("devices.list") == "c 195:3 rw\n"
+        assert t.node(3) == (195, 3, 0o666)
+        util.UnmountGPU(product_pod(), gpu, False, env_of(t))
+        assert t.read("devices.list") == ""
+        ref.mount_gpu(oracle_pod(), ref.device_new(3, FAKE_UUIDS[0]), **oracle_kw(t))   # the reference path, same cgroup
+        assert t.read("devices.list") == "c 195:3 rw\n"
+        ref.unmount_gpu(oracle_pod(), ref.device_new(3, FAKE_UUIDS[0]), False, [], **oracle_kw(t))
+        assert t.read("devices.list") == "" and t.node(3) is None
+    finally:
+        with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+            f.write(f"{t.pid}\n")
+        t.stop()

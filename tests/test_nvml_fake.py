@@ -1,0 +1,109 @@
+"""The dlopen NVML layer against a fake libnvidia-ml (CPU only): enumeration order, strings, processes,
+P2P status, fault injection.  Mirrors what the reference's nvml_test.go / collector_test.go poke at by hand."""
+
+import ctypes
+
+import pytest
+
+from gpumounter_b200 import ProbeError, _lib, collector, device, lib, probe
+from tests.conftest import FAKE_UUIDS
+
+
+def test_enumeration_is_in_nvml_index_order_with_minor_and_uuid(fake_nvml):
+    gpus = fake_nvml()
+    devs = probe.enumerate_nvml()
+    assert [(d.uuid, d.minor, d.pci_bus_id) for d in devs] == [tuple(g) for g in gpus]
+    assert [d.nvml_index for d in devs] == list(range(8))
+    assert all(d.cuda_ordinal == -1 for d in devs)
+
+
+def test_collector_get_gpu_info_builds_the_reference_records(fake_nvml):
+    gpus = fake_nvml()
+    c = collector.GPUCollector()
+    c.GetGPUInfo()  # ref: collector.go:40-79
+    assert [(g.MinorNumber, g.UUID, g.DeviceFilePath, g.State) for g in c.GPUList] == [
+        (m, u, f"/dev/nvidia{m}", "GPU_FREE_STATE") for u, m, _ in gpus]
+    assert c.GetGPUByUUID(FAKE_UUIDS[2]).MinorNumber == 1
+    with pytest.raises(ProbeError) as e:
+        c.GetGPUByUUID("GPU-nope")
+    assert e.value.code == _lib.GMP_ERR_NO_DEVICE and "No GPU with UUIDGPU-nope" in e.value.detail
+
+
+def test_no_devices_and_capacity(fake_nvml):
+    fake_nvml(gpus=[])
+    assert probe.enumerate_nvml() == []
+    fake_nvml()
+    arr = (probe.gmp_device * 4)()
+    n = ctypes.c_int()
+    rc = lib().gmp_enumerate_nvml(arr, 4, ctypes.byref(n))
+    assert rc == _lib.GMP_ERR_BUFFER_TOO_SMALL and n.value == 8
+
+
+def test_library_not_found_message_matches_the_reference(monkeypatch):
+    monkeypatch.setenv("GPUMOUNTER_NVML_LIB", "/nonexistent/libnvidia-ml.so.1")
+    with pytest.raises(ProbeError) as e:
+        probe.enumerate_nvml()
+    assert e.value.code == _lib.GMP_ERR_NVML_NOT_FOUND
+    assert e.value.detail.startswith("could not load NVML library")  # ref: bindings.go:53-55
+
+
+@pytest.mark.parametrize("fn", ["nvmlInit_v2", "nvmlDeviceGetCount_v2", "nvmlDeviceGetHandleByIndex_v2",
+                                "nvmlDeviceGetMinorNumber", "nvmlDeviceGetUUID"])
+def test_nvml_errors_surface_as_nvml_colon_message(fake_nvml, fn):
+    fake_nvml(fail=[(fn, 15)])  # NVML_ERROR_GPU_IS_LOST
+    with pytest.raises(ProbeError) as e:
+        probe.enumerate_nvml()
+    assert e.value.code == _lib.GMP_ERR_NVML
+    assert e.value.detail.startswith("nvml: GPU is lost")  # ref: bindings.go:47-48
+
+
+def test_versions(fake_nvml):
+    fake_nvml(extra=["driver 580.159", "nvml 12.580.159"])
+    d, n = ctypes.create_string_buffer(80), ctypes.create_string_buffer(80)
+    assert lib().gmp_nvml_versions(d, 80, n, 80) == 0
+    assert (d.value, n.value) == (b"580.159", b"12.580.159")
+
+
+def test_running_processes_graphics_first_then_compute(fake_nvml):
+    u = FAKE_UUIDS
+    fake_nvml(procs=[(u[0], 111, 1 << 20, "compute"), (u[0], 222, 2 << 20, "graphics"), (u[1], 333, 5, "compute"),
+                     (u[0], 444, 7, "compute")])
+    g = device.New(3, u[0])
+    procs = g.GetRunningProcess()  # ref: nvidia.go:58-87 appends graphics, then compute
+    assert [(p.Pid, p.UsedGPUMemory) for p in procs] == [(222, 2 << 20), (111, 1 << 20), (444, 7)]
+    assert device.New(9, u[5]).GetRunningProcess() == []
+    with pytest.raises(ProbeError) as e:
+        device.New(9, "GPU-unknown").GetRunningProcess()
+    assert e.value.code == _lib.GMP_ERR_NVML and "Not Found" in e.value.detail
+
+
+def test_p2p_status_matrix(fake_nvml):
+    fake_nvml(p2p=[(0, 2, 0, 5), (2, 0, 1, 3)])  # READ 0->2 NOT_SUPPORTED(5); WRITE 2->0 GPU_NOT_SUPPORTED(2)+1
+    uuids = FAKE_UUIDS[:3]
+    arr = (ctypes.c_char_p * 3)(*[u.encode() for u in uuids])
+    st = (ctypes.c_int32 * 9)()
+    assert lib().gmp_nvml_p2p_status(arr, 3, 0, st) == 0
+    assert list(st) == [0, 0, 5, 0, 0, 0, 0, 0, 0]
+    assert lib().gmp_nvml_p2p_status(arr, 3, 1, st) == 0
+    assert list(st) == [0, 0, 0, 0, 0, 0, 3, 0, 0]
+    assert lib().gmp_nvml_p2p_status(arr, 3, 9, st) == _lib.GMP_ERR_INVALID
+
+
+def test_nvlink_active_links(fake_nvml):
+    fake_nvml(nvlink=[(FAKE_UUIDS[0], 18), (FAKE_UUIDS[1], 4)])
+    a, m = ctypes.c_int(), ctypes.c_int()
+    assert lib().gmp_nvml_nvlink_active(FAKE_UUIDS[0].encode(), ctypes.byref(a), ctypes.byref(m)) == 0
+    assert (a.value, m.value) == (18, 18)  # toolkit nvml.h: NVML_NVLINK_MAX_LINKS 18 (the reference's header says 12)
+    assert lib().gmp_nvml_nvlink_active(FAKE_UUIDS[1].encode(), ctypes.byref(a), None) == 0 and a.value == 4
+
+
+def test_device_set_comparison(fake_nvml):
+    fake_nvml()
+    nv = probe.enumerate_nvml()
+    cu = [probe.Device(d.uuid, None, "", -1, i) for i, d in enumerate(reversed(nv))]  # other order, minors unknown
+    assert probe.device_sets_equal(nv, cu)
+    assert not probe.device_sets_equal(nv, cu[:-1])
+    cu[0] = probe.Device("GPU-other", None, "", -1, 0)
+    assert not probe.device_sets_equal(nv, cu)
+    wrong_minor = [probe.Device(d.uuid, (d.minor + 1) % 8, "", d.nvml_index, -1) for d in nv]
+    assert not probe.device_sets_equal(nv, wrong_minor)
