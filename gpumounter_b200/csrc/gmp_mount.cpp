@@ -1085,3 +1085,105 @@ extern "C" int gmp_slave_pod_name(const char* owner, const unsigned char rand3[3
         return emit(std::string(owner) + "-slave-pod-" + hex, out, cap);
     });
 }
+
+// ---- in-pod execution of the probe -------------------------------------------------------------------
+// A probe run from the worker's own context proves nothing: the worker is privileged and sees every GPU
+// (ref: deploy/gpu-mounter-workers.yaml:23-24).  And `nsenter --mount` alone, which is all the reference
+// ever does (ref: namespace.go:102-108), does not move a process into the pod's DEVICES CGROUP, the thing
+// that actually gates open("/dev/nvidiaN").  So the child here (1) opens the probe binary while still in the
+// worker's namespace, (2) writes itself into the target's device cgroup, (3) setns()es into the target's
+// mount namespace and (4) fexecve()s the already open binary: libcuda.so.1 / libnvidia-ml.so.1 then resolve
+// from the pod's own root, the device nodes are the pod's, and the cgroup verdict is the pod's.
+extern "C" int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
+                                const char* probe_exe, const char* const* extra_args, int n_extra, char* json, size_t cap,
+                                int* exit_status) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && probe_exe != nullptr && json != nullptr && cap > 0 && n >= 0 && (n == 0 || gpus != nullptr));
+        REQUIRE(n_extra >= 0 && (n_extra == 0 || extra_args != nullptr));
+        json[0] = '\0';
+        if (exit_status) *exit_status = -1;
+        std::string cgroup_path;
+        int rc = pod_cgroup_path(env, pod, &cgroup_path);
+        if (rc != GMP_OK) return rc;
+        std::vector<std::string> pids;
+        rc = read_cgroup_pids(env, cgroup_path, &pids);
+        if (rc != GMP_OK) return rc;
+        int target = 0;
+        rc = first_pid(pids, &target);
+        if (rc != GMP_OK) return rc;
+        const std::string ns_path = proc_root(env) + "/" + std::to_string(target) + "/ns/mnt";
+        const std::string procs_file = devices_root(env) + cgroup_path + "/cgroup.procs";
+
+        std::vector<std::string> args = {"gpumounter-probe"};
+        for (int i = 0; i < n; ++i) {
+            args.push_back("--uuid");
+            args.push_back(std::string(gpus[i].uuid) + ":" + std::to_string(gpus[i].minor_number));
+        }
+        for (int i = 0; i < n_extra; ++i) args.push_back(extra_args[i]);
+        std::vector<char*> argv;
+        for (std::string& a : args) argv.push_back(&a[0]);
+        argv.push_back(nullptr);
+
+        int out_pipe[2];
+        if (pipe2(out_pipe, O_CLOEXEC) != 0) {
+            set_error("pipe2: %s", strerror(errno));
+            return GMP_ERR_SYS;
+        }
+        const pid_t child = fork();
+        if (child < 0) {
+            set_error("fork: %s", strerror(errno));
+            close(out_pipe[0]);
+            close(out_pipe[1]);
+            return GMP_ERR_SYS;
+        }
+        if (child == 0) {
+            // stage codes travel back as exit statuses 120..125 so the parent can name the failing step
+            // not O_CLOEXEC: harmless for the ELF probe (it inherits a descriptor to its own image) and required
+            // if the file is a script, whose interpreter is handed /dev/fd/N
+            const int exe_fd = open(probe_exe, O_RDONLY);
+            if (exe_fd < 0) _exit(120);
+            const int ns_fd = open(ns_path.c_str(), O_RDONLY | O_CLOEXEC);
+            if (ns_fd < 0) _exit(121);
+            const int cg_fd = open(procs_file.c_str(), O_WRONLY | O_APPEND | O_CLOEXEC);
+            if (cg_fd < 0) _exit(122);
+            char me[24];
+            const int len = snprintf(me, sizeof(me), "%d\n", (int)getpid());
+            if (write(cg_fd, me, (size_t)len) != len) _exit(123);
+            close(cg_fd);
+            if (setns(ns_fd, CLONE_NEWNS) != 0) _exit(124);
+            dup2(out_pipe[1], 1);
+            extern char** environ;
+            fexecve(exe_fd, argv.data(), environ);
+            _exit(125);
+        }
+        close(out_pipe[1]);
+        std::string output;
+        char tmp[4096];
+        ssize_t r;
+        while ((r = read(out_pipe[0], tmp, sizeof(tmp))) > 0 || (r < 0 && errno == EINTR))
+            if (r > 0) output.append(tmp, (size_t)r);
+        close(out_pipe[0]);
+        int status = 0;
+        while (waitpid(child, &status, 0) < 0 && errno == EINTR) {
+        }
+        const int code = WIFEXITED(status) ? WEXITSTATUS(status) : -1;
+        if (exit_status) *exit_status = code;
+        if (code >= 120 && code <= 125) {
+            static const char* const stage[] = {"open the probe binary", "open the target's mount namespace",
+                                                "open the target's cgroup.procs", "join the target's device cgroup",
+                                                "setns into the target's mount namespace", "fexecve the probe"};
+            set_error("in-pod probe: could not %s", stage[code - 120]);
+            return GMP_ERR_SYS;
+        }
+        while (!output.empty() && (output.back() == '\n' || output.back() == '\r')) output.pop_back();
+        const size_t last_line = output.rfind('\n');
+        const std::string line = last_line == std::string::npos ? output : output.substr(last_line + 1);
+        rc = emit(line, json, cap);
+        if (rc != GMP_OK) return rc;
+        if (code < 0) {
+            set_error("in-pod probe was killed (wait status 0x%x)", status);
+            return GMP_ERR_SYS;
+        }
+        return code == 0 ? GMP_OK : -code;  // the probe's exit status is -(GMP_ERR_*)
+    });
+}

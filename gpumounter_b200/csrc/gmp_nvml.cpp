@@ -243,3 +243,36 @@ extern "C" int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* 
     }
     return GMP_OK;
 }
+
+// All four capability matrices and the active-link counts in ONE NVML session (internal; the P2P probe
+// would otherwise pay NVML's ~100 ms load+init five times over).
+namespace gmp {
+int nvml_p2p_everything(const char* const* uuids, int n, int32_t* caps_out[4], int32_t* nvlink_active) {
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    if (!nv.DeviceGetP2PStatus) {
+        set_error("nvml: nvmlDeviceGetP2PStatus not exported by this NVML");
+        return GMP_ERR_NVML;
+    }
+    nvmlDevice_t dev[GMP_MAX_DEVICES];
+    for (int i = 0; i < n; ++i) GMP_NVML(nv, nv.DeviceGetHandleByUUID(uuids[i], &dev[i]), "nvmlDeviceGetHandleByUUID");
+    for (int caps = 0; caps < 4; ++caps)
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < n; ++j) {
+                nvmlGpuP2PStatus_t st = NVML_P2P_STATUS_OK;
+                if (i != j)
+                    GMP_NVML(nv, nv.DeviceGetP2PStatus(dev[i], dev[j], (nvmlGpuP2PCapsIndex_t)caps, &st), "nvmlDeviceGetP2PStatus");
+                caps_out[caps][i * n + j] = (int32_t)st;
+            }
+    for (int i = 0; i < n; ++i) {
+        nvlink_active[i] = 0;
+        if (!nv.DeviceGetNvLinkState) continue;
+        for (unsigned int l = 0; l < NVML_NVLINK_MAX_LINKS; ++l) {
+            nvmlEnableState_t st = NVML_FEATURE_DISABLED;
+            if (nv.DeviceGetNvLinkState(dev[i], l, &st) == NVML_SUCCESS && st == NVML_FEATURE_ENABLED) ++nvlink_active[i];
+        }
+    }
+    return GMP_OK;
+}
+}  // namespace gmp

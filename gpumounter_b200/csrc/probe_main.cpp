@@ -1,0 +1,127 @@
+// gpumounter-probe — the standalone form of gmp_probe_all().
+//
+// The worker cannot prove a mount from its own context (it is privileged and sees every GPU,
+// ref: deploy/gpu-mounter-workers.yaml:23-24, docker/GPUMounter-worker/Dockerfile:17), so after
+// util.MountGPU it runs THIS binary inside the target: join the pod's device cgroup, setns() into
+// its mount namespace, fexecve() the probe from a descriptor opened beforehand.  The binary is
+// therefore self-contained: CUDA runtime, libstdc++ and libgcc are linked statically; libcuda.so.1
+// and libnvidia-ml.so.1 are resolved from the pod's own root at run time.
+//
+// Output: one JSON line on stdout.  Exit status: 0 = usable, otherwise -(GMP_ERR_* code).
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "gpumounter_probe.h"
+
+namespace {
+
+unsigned long long parse_size(const char* s) {
+    char* end = nullptr;
+    double v = strtod(s, &end);
+    unsigned long long mult = 1;
+    if (end && *end) {
+        switch (*end) {
+            case 'k': case 'K': mult = 1ull << 10; break;
+            case 'm': case 'M': mult = 1ull << 20; break;
+            case 'g': case 'G': mult = 1ull << 30; break;
+            default: fprintf(stderr, "bad size '%s'\n", s); exit(64);
+        }
+    }
+    return (unsigned long long)(v * (double)mult);
+}
+
+void add_device(std::vector<gmp_device>* list, const std::string& spec) {
+    gmp_device d;
+    memset(&d, 0, sizeof(d));
+    d.minor = UINT32_MAX;
+    d.nvml_index = d.cuda_ordinal = -1;
+    const size_t colon = spec.rfind(':');
+    std::string uuid = spec;
+    if (colon != std::string::npos && colon + 1 < spec.size() && spec.find_first_not_of("0123456789", colon + 1) == std::string::npos) {
+        uuid = spec.substr(0, colon);
+        d.minor = (uint32_t)strtoul(spec.c_str() + colon + 1, nullptr, 10);
+    }
+    snprintf(d.uuid, sizeof(d.uuid), "%s", uuid.c_str());
+    list->push_back(d);
+}
+
+void usage() {
+    fprintf(stderr,
+            "usage: gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
+            "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
+            "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only]\n"
+            "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n");
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    gmp_probe_opts o;
+    memset(&o, 0, sizeof(o));
+    o.hbm.dma_bytes = UINT64_MAX;  // library default
+    o.flags |= GMP_PROBE_F_KEEP_DEVICE;  // a process of its own: exit releases everything, no explicit reset needed
+    std::vector<gmp_device> expected;
+    std::string dev_dir;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto need = [&](const char* what) -> const char* {
+            if (i + 1 >= argc) {
+                fprintf(stderr, "%s needs a value\n", what);
+                exit(64);
+            }
+            return argv[++i];
+        };
+        if (a == "--uuid") add_device(&expected, need("--uuid"));
+        else if (a == "--uuids") {
+            std::string all = need("--uuids");
+            size_t b = 0;
+            while (b <= all.size()) {
+                const size_t c = all.find(',', b);
+                const std::string one = all.substr(b, c == std::string::npos ? std::string::npos : c - b);
+                if (!one.empty()) add_device(&expected, one);
+                if (c == std::string::npos) break;
+                b = c + 1;
+            }
+        } else if (a == "--bytes") o.hbm.bytes = parse_size(need("--bytes"));
+        else if (a == "--iters") o.hbm.iters = (uint32_t)atoi(need("--iters"));
+        else if (a == "--patterns") {
+            const std::string v = need("--patterns");
+            o.hbm.pattern_mask = v == "all" ? (1u << GMP_PAT_COUNT) - 1 : (uint32_t)strtoul(v.c_str(), nullptr, 0);
+        } else if (a == "--seed") o.hbm.seed = strtoull(need("--seed"), nullptr, 0);
+        else if (a == "--dma-bytes") o.hbm.dma_bytes = parse_size(need("--dma-bytes"));
+        else if (a == "--p2p-bytes") o.p2p.bytes = parse_size(need("--p2p-bytes"));
+        else if (a == "--p2p-iters") o.p2p.iters = (uint32_t)atoi(need("--p2p-iters"));
+        else if (a == "--dev-dir") dev_dir = need("--dev-dir");
+        else if (a == "--skip-nodes") o.flags |= GMP_PROBE_F_SKIP_NODES;
+        else if (a == "--skip-hbm") o.flags |= GMP_PROBE_F_SKIP_HBM;
+        else if (a == "--skip-p2p") o.flags |= GMP_PROBE_F_SKIP_P2P;
+        else if (a == "--skip-nvml") o.flags |= GMP_PROBE_F_SKIP_NVML;
+        else if (a == "--skip-copy") o.hbm.flags |= GMP_HBM_F_SKIP_COPY;
+        else if (a == "--matrix-only") o.p2p.flags |= GMP_P2P_F_MATRIX_ONLY;
+        else if (a == "-h" || a == "--help") {
+            usage();
+            return 0;
+        } else {
+            fprintf(stderr, "unknown argument '%s'\n", a.c_str());
+            usage();
+            return 64;
+        }
+    }
+    if (!dev_dir.empty()) o.dev_dir = dev_dir.c_str();
+    if ((int)expected.size() > GMP_MAX_DEVICES) {
+        fprintf(stderr, "at most %d devices\n", GMP_MAX_DEVICES);
+        return 64;
+    }
+    static gmp_report report;  // ~100 KB: keep it off the stack
+    const int rc = gmp_probe_all(expected.empty() ? nullptr : expected.data(), (int)expected.size(), &o, &report);
+    static char json[1 << 16];
+    if (gmp_report_json(&report, json, sizeof(json)) == GMP_OK) puts(json);
+    else printf("{\"status\":%d,\"detail\":\"report too large\"}\n", rc);
+    fflush(stdout);
+    return rc == GMP_OK ? 0 : -rc;
+}

@@ -89,6 +89,7 @@ class gmp_hbm_result(ctypes.Structure):
         ("ns_dma", ctypes.c_uint64),
         ("ns_teardown", ctypes.c_uint64),
         ("ns_total", ctypes.c_uint64),
+        ("mono_first_verified_ns", ctypes.c_uint64),
     ]
 
     def as_dict(self) -> dict:
@@ -236,6 +237,101 @@ def probe_hbm(uuid: Optional[str] = None, *, nbytes: int = 0, iters: int = 0, pa
     if raise_on_error:
         check(rc, "gmp_probe_hbm")
     return r
+
+
+GMP_P2P_CELLS = GMP_MAX_DEVICES * GMP_MAX_DEVICES
+P2P_F_KEEP_DEVICE, P2P_F_SKIP_BIDIR, P2P_F_SKIP_ALLTOALL, P2P_F_MATRIX_ONLY = 1, 2, 4, 8
+PROBE_F_SKIP_NODES, PROBE_F_SKIP_HBM, PROBE_F_SKIP_P2P, PROBE_F_SKIP_NVML, PROBE_F_KEEP_DEVICE = 1, 2, 4, 8, 16
+
+
+class gmp_p2p_opts(ctypes.Structure):
+    _fields_ = [("bytes", ctypes.c_uint64), ("iters", ctypes.c_uint32), ("flags", ctypes.c_uint32),
+                ("seed", ctypes.c_uint64)]
+
+
+class gmp_p2p_result(ctypes.Structure):
+    _fields_ = [
+        ("n", ctypes.c_int32), ("status", ctypes.c_int32),
+        ("uuid", (ctypes.c_char * GMP_UUID_LEN) * GMP_MAX_DEVICES),
+        ("cuda_ordinal", ctypes.c_int32 * GMP_MAX_DEVICES),
+        ("nvlink_active", ctypes.c_int32 * GMP_MAX_DEVICES),
+        ("nvml_available", ctypes.c_int32), ("matrix_match", ctypes.c_int32),
+        ("can_access", ctypes.c_int32 * GMP_P2P_CELLS),
+        ("nvml_read", ctypes.c_int32 * GMP_P2P_CELLS), ("nvml_write", ctypes.c_int32 * GMP_P2P_CELLS),
+        ("nvml_nvlink", ctypes.c_int32 * GMP_P2P_CELLS), ("nvml_atomics", ctypes.c_int32 * GMP_P2P_CELLS),
+        ("write_gbs", ctypes.c_double * GMP_P2P_CELLS), ("read_gbs", ctypes.c_double * GMP_P2P_CELLS),
+        ("bidir_gbs", ctypes.c_double * GMP_MAX_DEVICES), ("alltoall_gbs", ctypes.c_double),
+        ("bytes", ctypes.c_uint64), ("mismatch_lanes", ctypes.c_uint64),
+        ("first_bad_src", ctypes.c_int32), ("first_bad_dst", ctypes.c_int32),
+        ("ns_setup", ctypes.c_uint64), ("ns_pairs", ctypes.c_uint64), ("ns_bidir", ctypes.c_uint64),
+        ("ns_alltoall", ctypes.c_uint64), ("ns_teardown", ctypes.c_uint64), ("ns_total", ctypes.c_uint64),
+    ]
+
+    def matrix(self, name: str):
+        n = self.n
+        flat = getattr(self, name)
+        return [[flat[i * n + j] for j in range(n)] for i in range(n)]
+
+
+class gmp_probe_opts(ctypes.Structure):
+    _fields_ = [("hbm", gmp_hbm_opts), ("p2p", gmp_p2p_opts), ("flags", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
+                ("dev_dir", ctypes.c_char_p)]
+
+
+class gmp_report(ctypes.Structure):
+    _fields_ = [
+        ("status", ctypes.c_int32), ("n", ctypes.c_int32), ("nodes_status", ctypes.c_int32),
+        ("device_set_status", ctypes.c_int32), ("nvml_status", ctypes.c_int32), ("reserved", ctypes.c_int32),
+        ("devices", gmp_device * GMP_MAX_DEVICES), ("hbm", gmp_hbm_result * GMP_MAX_DEVICES), ("p2p", gmp_p2p_result),
+        ("ns_nodes", ctypes.c_uint64), ("ns_enumerate", ctypes.c_uint64), ("ns_hbm", ctypes.c_uint64),
+        ("ns_p2p", ctypes.c_uint64), ("ns_total", ctypes.c_uint64), ("ns_cuda_init", ctypes.c_uint64),
+        ("ns_nvml", ctypes.c_uint64), ("mono_start_ns", ctypes.c_uint64), ("mono_usable_ns", ctypes.c_uint64),
+        ("detail", ctypes.c_char * 256),
+    ]
+
+
+def probe_p2p(uuids: Sequence[str], *, nbytes: int = 0, iters: int = 0, flags: int = 0, seed: int = 0,
+              raise_on_error: bool = True) -> gmp_p2p_result:
+    """Capability matrices (CUDA vs NVML) and NVLink bandwidth across the GPUs named by UUID."""
+    f = lib().gmp_probe_p2p
+    f.argtypes = [ctypes.POINTER(ctypes.c_char_p), ctypes.c_int, ctypes.POINTER(gmp_p2p_opts), ctypes.POINTER(gmp_p2p_result)]
+    arr = (ctypes.c_char_p * max(1, len(uuids)))(*[u.encode() for u in uuids])
+    o = gmp_p2p_opts(nbytes, iters, flags, seed & UINT64_MAX)
+    r = gmp_p2p_result()
+    rc = f(arr, len(uuids), ctypes.byref(o), ctypes.byref(r))
+    if raise_on_error:
+        check(rc, "gmp_probe_p2p")
+    return r
+
+
+def probe_all(expected: Sequence[Device] = (), *, hbm_bytes: int = 0, hbm_iters: int = 0, pattern_mask: int = 0,
+              dma_bytes: int = UINT64_MAX, p2p_bytes: int = 0, p2p_iters: int = 0, flags: int = 0, hbm_flags: int = 0,
+              p2p_flags: int = 0, dev_dir: Optional[str] = None, raise_on_error: bool = True) -> gmp_report:
+    """The whole-pod probe the worker's hook runs after AddGPU's mount loop (ref: server.go:97-98)."""
+    f = lib().gmp_probe_all
+    f.argtypes = [ctypes.POINTER(gmp_device), ctypes.c_int, ctypes.POINTER(gmp_probe_opts), ctypes.POINTER(gmp_report)]
+    o = gmp_probe_opts()
+    o.hbm = gmp_hbm_opts(hbm_bytes, hbm_iters, pattern_mask, 0, dma_bytes, hbm_flags, 0)
+    o.p2p = gmp_p2p_opts(p2p_bytes, p2p_iters, p2p_flags, 0)
+    o.flags = flags
+    o.dev_dir = dev_dir.encode() if dev_dir else None
+    r = gmp_report()
+    rc = f(_to_c_devices(expected) if expected else None, len(expected), ctypes.byref(o), ctypes.byref(r))
+    if raise_on_error and rc < 0:
+        raise ProbeError(rc, r.detail.decode(errors="replace"), "gmp_probe_all")
+    return r
+
+
+def report_json(report: gmp_report) -> str:
+    buf = ctypes.create_string_buffer(1 << 16)
+    check(lib().gmp_report_json(ctypes.byref(report), buf, 1 << 16), "gmp_report_json")
+    return buf.value.decode()
+
+
+def probe_executable() -> str:
+    """Path of the standalone gpumounter-probe binary built next to the library."""
+    import os
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "gpumounter-probe")
 
 
 __all__ = [n for n in dir() if not n.startswith("_")] + ["ProbeError"]

@@ -57,3 +57,25 @@ def ContainString(stringList: Sequence[str], aimString: str) -> bool:  # ref: ut
 
 def CanMount(mountType: str, isEntireMount: bool) -> bool:  # ref: util.go:207-226 (request.IsEntireMount passed directly)
     return bool(lib().gmp_can_mount(MOUNT_TYPE_CODE[mountType], int(isEntireMount)))
+
+
+def ProbeInPod(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = (), env: Optional[MountEnv] = None,
+               probe_exe: Optional[str] = None, raise_on_error: bool = True):
+    """Run gpumounter-probe inside the pod (device cgroup + mount namespace) and return (status, report dict).
+    No reference counterpart; this is the hook after ref: pkg/server/gpu-mount/server.go:97."""
+    import json as _json
+
+    from . import probe as _probe
+    from ._model import c_strings
+
+    exe = probe_exe or _probe.probe_executable()
+    buf = ctypes.create_string_buffer(1 << 16)
+    code = ctypes.c_int(-1)
+    c = pod.to_c()
+    rc = lib().gmp_probe_in_pod(env_ptr(env), ctypes.byref(c), as_c_array(gpus), len(gpus), exe.encode(),
+                                c_strings(list(extra_args)), len(extra_args), buf, 1 << 16, ctypes.byref(code))
+    text = buf.value.decode(errors="replace")
+    report = _json.loads(text) if text.startswith("{") else {}
+    if raise_on_error:
+        check(rc, "ProbeInPod")
+    return rc, report

@@ -267,15 +267,132 @@ typedef struct gmp_hbm_result {
     uint64_t ns_select_device;   /* cudaGetDeviceCount + UUID match + cudaSetDevice */
     uint64_t ns_context;         /* primary-context creation (cudaFree(0)) */
     uint64_t ns_alloc;
-    uint64_t ns_first_kernel;    /* first write+verify pass, launch to verified result */
+    uint64_t ns_first_kernel;    /* untimed first touch: write+verify of a 4 MiB prefix, launch to verified result */
     uint64_t ns_kernels;         /* all timed passes */
     uint64_t ns_dma;
     uint64_t ns_teardown;
     uint64_t ns_total;
+    uint64_t mono_first_verified_ns; /* absolute CLOCK_MONOTONIC time at which the first kernel result verified
+                                        (comparable across processes of one host: the "usable" instant) */
 } gmp_hbm_result;
 
 /* uuid == NULL or "" probes CUDA ordinal 0. */
 GMP_API int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out);
+
+/* ------------------------------------------------------------------------- */
+/* 5. Peer-to-peer probe across the GPUs mounted into one pod                 */
+/* ------------------------------------------------------------------------- */
+/*
+ * No reference counterpart.  For the n GPUs named by UUID (n = 1, 2, 4, 8):
+ *   - can_access[i*n+j]   = cudaDeviceCanAccessPeer(i, j)          (1 on the diagonal)
+ *   - nvml_*[i*n+j]       = nvmlDeviceGetP2PStatus(i, j, READ/WRITE/NVLINK/ATOMICS), 0 = OK
+ *   - matrix_match        = for all i != j: can_access == (nvml_read == OK && nvml_write == OK)
+ *   - write_gbs[i*n+j]    = a kernel on GPU i STORES the pattern into GPU j's HBM over NVLink
+ *                           (16/32-byte peer stores), GPU j then verifies its own memory;
+ *   - read_gbs[i*n+j]     = a kernel on GPU i LOADS and verifies GPU j's buffer over NVLink;
+ *   - bidir_gbs[i]        = GPU i's traffic (sent + received bytes / time) while all GPUs exchange
+ *                           with a partner at once, worst round of the n-1 round schedule;
+ *   - alltoall_gbs        = aggregate when every GPU writes to every peer at once.
+ * Bytes: one ordered pair moves `bytes` (algorithmic = wire bytes).
+ * Every transfer is verified; mismatch_lanes counts 16-byte lanes that differ.
+ * The call enables peer access itself and, unless GMP_P2P_F_KEEP_DEVICE is set,
+ * ends with cudaDeviceReset() on every device it touched.
+ */
+#define GMP_P2P_DEFAULT_BYTES (1ull << 30)
+#define GMP_P2P_CELLS (GMP_MAX_DEVICES * GMP_MAX_DEVICES)
+
+typedef struct gmp_p2p_opts {
+    uint64_t bytes;   /* per ordered pair; 0 -> GMP_P2P_DEFAULT_BYTES */
+    uint32_t iters;   /* timed repetitions per measurement; 0 -> 2 */
+    uint32_t flags;   /* GMP_P2P_F_* */
+    uint64_t seed;    /* 0 -> default */
+} gmp_p2p_opts;
+
+enum {
+    GMP_P2P_F_KEEP_DEVICE   = 1u << 0,
+    GMP_P2P_F_SKIP_BIDIR    = 1u << 1,
+    GMP_P2P_F_SKIP_ALLTOALL = 1u << 2,
+    GMP_P2P_F_MATRIX_ONLY   = 1u << 3   /* capability matrices only, no transfers */
+};
+
+typedef struct gmp_p2p_result {
+    int32_t  n;
+    int32_t  status;
+    char     uuid[GMP_MAX_DEVICES][GMP_UUID_LEN];
+    int32_t  cuda_ordinal[GMP_MAX_DEVICES];
+    int32_t  nvlink_active[GMP_MAX_DEVICES];   /* -1 when NVML is not available */
+    int32_t  nvml_available;
+    int32_t  matrix_match;                      /* 1 match, 0 mismatch, -1 not checkable (no NVML) */
+    int32_t  can_access[GMP_P2P_CELLS];
+    int32_t  nvml_read[GMP_P2P_CELLS];
+    int32_t  nvml_write[GMP_P2P_CELLS];
+    int32_t  nvml_nvlink[GMP_P2P_CELLS];
+    int32_t  nvml_atomics[GMP_P2P_CELLS];
+    double   write_gbs[GMP_P2P_CELLS];          /* best of iters; 0 on the diagonal / inaccessible pairs */
+    double   read_gbs[GMP_P2P_CELLS];
+    double   bidir_gbs[GMP_MAX_DEVICES];
+    double   alltoall_gbs;
+    uint64_t bytes;
+    uint64_t mismatch_lanes;
+    int32_t  first_bad_src, first_bad_dst;      /* ordered pair of the first failing transfer; -1 when none */
+    uint64_t ns_setup, ns_pairs, ns_bidir, ns_alltoall, ns_teardown, ns_total;
+} gmp_p2p_result;
+
+GMP_API int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts* opts, gmp_p2p_result* out);
+
+/* ------------------------------------------------------------------------- */
+/* 5b. Whole-pod probe and its JSON line                                       */
+/* ------------------------------------------------------------------------- */
+/*
+ * What the hook runs after AddGPU's mount loop (ref: server.go:97-98), inside the
+ * pod's device cgroup and mount namespace:
+ *   1. device nodes: /dev/nvidiactl, /dev/nvidia-uvm and every expected /dev/nvidia<minor>
+ *      exist and open (distinct GMP_ERR_NODE_* codes);
+ *   2. device set: the CUDA-visible UUID set equals the expected set (GMP_ERR_DEVICE_SET);
+ *   3. HBM probe on every GPU, one host thread per GPU (the reference's mount loop is serial);
+ *   4. NVML cross-check, loaded on its own thread while CUDA starts: (UUID, minor) equals NVML's
+ *      enumeration (ref: collector.go:56-77) when NVML is reachable from the pod;
+ *   5. P2P probe across them (n >= 2).
+ * expected may be NULL/0: probe everything CUDA sees.
+ */
+typedef struct gmp_probe_opts {
+    gmp_hbm_opts hbm;
+    gmp_p2p_opts p2p;
+    uint32_t     flags;       /* GMP_PROBE_F_* */
+    uint32_t     reserved;
+    const char*  dev_dir;     /* where the device nodes are looked up; NULL -> "/dev" */
+} gmp_probe_opts;
+
+enum {
+    GMP_PROBE_F_SKIP_NODES = 1u << 0,
+    GMP_PROBE_F_SKIP_HBM   = 1u << 1,
+    GMP_PROBE_F_SKIP_P2P   = 1u << 2,
+    GMP_PROBE_F_SKIP_NVML  = 1u << 3,
+    GMP_PROBE_F_KEEP_DEVICE = 1u << 4
+};
+
+typedef struct gmp_report {
+    int32_t        status;          /* first failing check, or GMP_OK */
+    int32_t        n;
+    int32_t        nodes_status;    /* GMP_OK or a GMP_ERR_NODE_* / GMP_ERR_DRIVER_LIB code */
+    int32_t        device_set_status;
+    int32_t        nvml_status;     /* GMP_OK, or why NVML could not be consulted */
+    int32_t        reserved;
+    gmp_device     devices[GMP_MAX_DEVICES];   /* CUDA view joined with NVML (minor, nvml_index) by UUID */
+    gmp_hbm_result hbm[GMP_MAX_DEVICES];
+    gmp_p2p_result p2p;
+    uint64_t       ns_nodes, ns_enumerate, ns_hbm, ns_p2p, ns_total;
+    uint64_t       ns_cuda_init;    /* cuInit + device enumeration (inside ns_enumerate) */
+    uint64_t       ns_nvml;         /* NVML load + init + enumeration, overlapped with CUDA start-up on its own thread */
+    uint64_t       mono_start_ns;   /* absolute CLOCK_MONOTONIC at entry */
+    uint64_t       mono_usable_ns;  /* ... when the LAST GPU's first kernel result verified; 0 if none did */
+    char           detail[256];     /* gmp_last_error() of the first failing check */
+} gmp_report;
+
+GMP_API int gmp_probe_all(const gmp_device* expected, int n_expected, const gmp_probe_opts* opts, gmp_report* out);
+/* One JSON object (single line, no trailing newline) describing the report.  GMP_ERR_BUFFER_TOO_SMALL
+ * when cap is not enough (32 KiB always is). */
+GMP_API int gmp_report_json(const gmp_report* report, char* buf, size_t cap);
 
 /* ------------------------------------------------------------------------- */
 /* 6. Node-local mount path (native restatement of the worker's L2/L3 logic)  */
@@ -414,6 +531,20 @@ GMP_API int gmp_unmount_gpu(const gmp_mount_env* env, const gmp_pod* pod, const 
 GMP_API int gmp_mount_gpus(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int* done);
 GMP_API int gmp_unmount_gpus(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int force,
                              int* done);
+
+/*
+ * Runs the standalone probe (gpumounter-probe, built next to the library) INSIDE the pod and returns its
+ * JSON line.  No reference counterpart; hook point ref: pkg/server/gpu-mount/server.go:97-98, after the
+ * mount loop.  A forked child opens `probe_exe` in the caller's namespace, joins the pod's device cgroup
+ * (the reference's `nsenter --mount` never does, so a check run its way would be gated by the WORKER's
+ * cgroup), setns()es into the pod's mount namespace and fexecve()s the binary with
+ * "--uuid <uuid>:<minor>" for each GPU plus `extra_args`.  Returns the probe's verdict (GMP_OK or the
+ * GMP_ERR_* it exited with), or GMP_ERR_SYS when the child could not be set up; *exit_status receives the
+ * raw exit status.
+ */
+GMP_API int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
+                             const char* probe_exe, const char* const* extra_args, int n_extra,
+                             char* json, size_t cap, int* exit_status);
 
 /* kubelet PodResources listing, ref: collector.go:114-122 (v1alpha1 messages). */
 typedef struct gmp_container_devices { const char* resource_name; int32_t n_ids; const char* const* device_ids; } gmp_container_devices;

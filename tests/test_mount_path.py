@@ -211,3 +211,38 @@ def test_real_devices_cgroup_allow_and_deny(fake_nvml):
         with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
             f.write(f"{t.pid}\n")
         t.stop()
+
+
+def test_probe_in_pod_runs_inside_the_targets_cgroup_and_mount_namespace(fake_nvml, tmp_path):
+    """A stand-in 'probe' (a static shell-free C-less script is not possible with fexecve of a script whose
+    interpreter must exist in the pod; the harness target shares the host root, so /bin/sh works): it reports
+    where it runs, which is what this test is about."""
+    fake_nvml()
+    fake_probe = tmp_path / "fake-probe"
+    fake_probe.write_text(
+        "#!/bin/sh\n"
+        "printf '{\"status\":0,\"args\":\"%s\",\"mnt\":\"%s\",\"nodes\":\"%s\",\"self\":%s}\\n' "
+        "\"$*\" \"$(readlink /proc/self/ns/mnt)\" \"$(ls \"$GMP_TEST_DEVDIR\" | tr '\\n' ' ')\" \"$$\"\n")
+    fake_probe.chmod(0o755)
+    with harness.Target() as t:
+        gpus = [device.New(3, FAKE_UUIDS[0]), device.New(2, FAKE_UUIDS[1])]
+        util.MountGPUs(product_pod(), gpus, env_of(t))
+        os.environ["GMP_TEST_DEVDIR"] = t.devdir
+        try:
+            rc, rep = util.ProbeInPod(product_pod(), gpus, ["--bytes", "1M"], env_of(t), probe_exe=str(fake_probe))
+        finally:
+            del os.environ["GMP_TEST_DEVDIR"]
+        assert rc == 0 and rep["status"] == 0
+        assert rep["args"] == f"--uuid {FAKE_UUIDS[0]}:3 --uuid {FAKE_UUIDS[1]}:2 --bytes 1M"
+        assert rep["mnt"] == os.readlink(f"/proc/{t.pid}/ns/mnt") != os.readlink("/proc/self/ns/mnt")
+        assert rep["nodes"].split() == ["nvidia2", "nvidia3"]          # sees the pod's /dev, not the host's
+        assert str(rep["self"]) in t.read("cgroup.procs").split()       # joined the pod's device cgroup first
+        # failures of the set-up are named, the probe's own verdict is passed through
+        with pytest.raises(ProbeError) as e:
+            util.ProbeInPod(product_pod(), gpus, [], env_of(t), probe_exe=str(tmp_path / "missing"))
+        assert e.value.code == _lib.GMP_ERR_SYS and "open the probe binary" in e.value.detail
+        bad = tmp_path / "bad-probe"
+        bad.write_text("#!/bin/sh\necho '{\"status\":-7}'\nexit 7\n")
+        bad.chmod(0o755)
+        rc, rep = util.ProbeInPod(product_pod(), gpus, [], env_of(t), probe_exe=str(bad), raise_on_error=False)
+        assert rc == _lib.GMP_ERR_VERIFY and rep["status"] == -7

@@ -1,0 +1,68 @@
+"""The standalone gpumounter-probe executable and gmp_probe_all's pre-flight checks, without a GPU."""
+
+import json
+import os
+import subprocess
+
+import pytest
+
+from gpumounter_b200 import _lib, probe
+
+EXE = probe.probe_executable()
+HAS_GPU = os.path.exists("/dev/nvidiactl")
+
+
+def run(*args):
+    p = subprocess.run([EXE, *args], capture_output=True, text=True, timeout=120)
+    line = p.stdout.strip().splitlines()[-1] if p.stdout.strip() else "{}"
+    return p.returncode, json.loads(line), p.stderr
+
+
+def test_executable_is_self_contained():
+    out = subprocess.run(["ldd", EXE], capture_output=True, text=True).stdout
+    libs = [l.split()[0] for l in out.splitlines() if "=>" in l or l.strip().startswith("/")]
+    # only the C library family: no libstdc++, no libcudart, no libcuda at link time
+    assert all(any(k in l for k in ("libc.so", "ld-linux", "libm.so", "libdl", "libpthread", "librt", "linux-vdso"))
+               for l in libs), libs
+
+
+def test_missing_nodes_have_distinct_codes(tmp_path):
+    d = tmp_path / "dev"
+    d.mkdir()
+    rc, j, _ = run("--dev-dir", str(d), "--uuid", "GPU-x:3")
+    assert rc == -_lib.GMP_ERR_NODE_CTL and j["status"] == _lib.GMP_ERR_NODE_CTL and "nvidiactl" in j["detail"]
+    (d / "nvidiactl").write_text("")
+    rc, j, _ = run("--dev-dir", str(d), "--uuid", "GPU-x:3")
+    assert rc == -_lib.GMP_ERR_NODE_UVM and "nvidia-uvm" in j["detail"]
+    (d / "nvidia-uvm").write_text("")
+    rc, j, _ = run("--dev-dir", str(d), "--uuid", "GPU-x:3")
+    assert rc == -_lib.GMP_ERR_NODE_GPU and j["detail"].startswith(str(d / "nvidia3"))
+    (d / "nvidia3").write_text("")
+    os.chmod(d / "nvidia3", 0)
+    rc, j, _ = run("--dev-dir", str(d), "--uuid", "GPU-x:3")
+    if os.geteuid() != 0:  # root ignores file modes; the device cgroup is what refuses root in a real pod
+        assert rc == -_lib.GMP_ERR_NODE_DENIED
+    else:
+        assert rc in (-_lib.GMP_ERR_DRIVER_LIB, -_lib.GMP_ERR_UNAVAILABLE, -_lib.GMP_ERR_DEVICE_SET, 0) or HAS_GPU
+
+
+@pytest.mark.skipif(HAS_GPU, reason="box has a GPU")
+def test_no_driver_is_reported_not_faked(tmp_path):
+    rc, j, _ = run("--skip-nodes")
+    assert rc == -_lib.GMP_ERR_UNAVAILABLE and j["n_gpus"] == 0 and j["hbm"] == []
+    r = probe.probe_all(flags=probe.PROBE_F_SKIP_NODES, raise_on_error=False)
+    assert r.status == _lib.GMP_ERR_UNAVAILABLE
+    assert json.loads(probe.report_json(r))["status"] == _lib.GMP_ERR_UNAVAILABLE
+
+
+def test_bad_arguments():
+    p = subprocess.run([EXE, "--nonsense"], capture_output=True, text=True)
+    assert p.returncode == 64 and "usage" in p.stderr
+    p = subprocess.run([EXE, "--bytes", "12Q"], capture_output=True, text=True)
+    assert p.returncode == 64
+    with pytest.raises(probe.ProbeError) as e:
+        probe.probe_p2p([])
+    assert e.value.code == _lib.GMP_ERR_INVALID
+    with pytest.raises(probe.ProbeError) as e:
+        probe.probe_p2p(["GPU-a", ""])
+    assert e.value.code == _lib.GMP_ERR_INVALID

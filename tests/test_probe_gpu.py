@@ -86,3 +86,85 @@ def test_probe_hbm_one_shot_subprocess_resets_the_device():
         assert x["status"] == 0 and x["mismatch_lanes"] == 0
         assert x["write_gbs_best"] > 100 and x["read_gbs_best"] > 100 and x["copy_gbs_best"] > 100
     assert r["h2d_bytes"] == 64 << 20
+
+
+def test_probe_p2p_single_gpu_is_a_trivial_matrix(cuda):
+    uuid = probe.enumerate_cuda()[0].uuid
+    r = probe.probe_p2p([uuid], nbytes=64 << 20, flags=probe.P2P_F_KEEP_DEVICE)
+    assert r.status == 0 and r.n == 1 and r.matrix("can_access") == [[1]] and r.mismatch_lanes == 0
+    assert r.nvml_available == 1 and r.matrix_match == 1 and r.matrix("nvml_read") == [[0]]
+    with pytest.raises(ProbeError) as e:
+        probe.probe_p2p([uuid, uuid], nbytes=1 << 20, flags=probe.P2P_F_KEEP_DEVICE)
+    assert e.value.code == _lib.GMP_ERR_INVALID
+
+
+def test_probe_p2p_pairs(cuda):
+    devs = probe.enumerate_cuda()
+    if len(devs) < 2:
+        pytest.skip("needs at least 2 GPUs")
+    uuids = [d.uuid for d in devs]
+    r = probe.probe_p2p(uuids, nbytes=256 << 20, iters=2, flags=probe.P2P_F_KEEP_DEVICE)
+    n = len(uuids)
+    assert r.status == 0 and r.mismatch_lanes == 0 and r.matrix_match == 1
+    ca, wr, rd = r.matrix("can_access"), r.matrix("write_gbs"), r.matrix("read_gbs")
+    for i in range(n):
+        for j in range(n):
+            if i == j:
+                assert ca[i][j] == 1 and wr[i][j] == 0
+            else:
+                assert ca[i][j] == 1, "HGX B200: every pair is NVLink-connected"
+                assert r.matrix("nvml_nvlink")[i][j] == 0
+                assert wr[i][j] > 300 and rd[i][j] > 300, (i, j, wr[i][j], rd[i][j])
+        assert r.bidir_gbs[i] > 500
+        assert r.nvlink_active[i] == 18
+    assert r.alltoall_gbs > 300 * n
+
+
+def test_probe_all_and_json_in_a_child_process():
+    code = (
+        "import json,sys; sys.path.insert(0, %r)\n"
+        "from gpumounter_b200 import probe\n"
+        "nv = {d.uuid: d for d in probe.enumerate_nvml()}\n"
+        "exp = [probe.Device(d.uuid, nv[d.uuid].minor, '', -1, -1) for d in probe.enumerate_cuda()]\n"
+        "r = probe.probe_all(exp, hbm_bytes=1<<30, hbm_iters=1, p2p_bytes=128<<20, dma_bytes=16<<20)\n"
+        "print(probe.report_json(r))\n" % ROOT
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    j = json.loads(out.stdout.strip().splitlines()[-1])
+    assert j["status"] == 0 and j["nodes_status"] == 0 and j["device_set_status"] == 0 and j["nvml_status"] == 0
+    assert j["n_gpus"] == len(j["devices"]) == len(j["hbm"]) >= 1
+    for d, h in zip(j["devices"], j["hbm"]):
+        assert d["minor"] >= 0 and d["nvml_index"] >= 0 and d["cuda_ordinal"] >= 0 and h["uuid"] == d["uuid"]
+        assert h["status"] == 0 and h["mismatch_lanes"] == 0 and h["write_gbs"] > 1000 and h["read_gbs"] > 1000
+    if j["n_gpus"] >= 2:
+        assert j["p2p"]["matrix_match"] == 1 and j["p2p"]["mismatch_lanes"] == 0
+
+
+def test_probe_all_rejects_a_wrong_device_set():
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from gpumounter_b200 import probe\n"
+        "cu = probe.enumerate_cuda()\n"
+        "bad = [probe.Device('GPU-00000000-0000-0000-0000-000000000000', None, '', -1, -1)]\n"
+        "r = probe.probe_all(bad, hbm_bytes=1<<20, raise_on_error=False, flags=probe.PROBE_F_SKIP_NODES)\n"
+        "print(r.status, r.device_set_status)\n"
+        "nv = {d.uuid: d for d in probe.enumerate_nvml()}\n"
+        "wrong_minor = [probe.Device(d.uuid, (nv[d.uuid].minor + 1) %% 200, '', -1, -1) for d in cu]\n"
+        "r = probe.probe_all(wrong_minor, hbm_bytes=1<<20, raise_on_error=False, flags=probe.PROBE_F_SKIP_NODES)\n"
+        "print(r.status, r.device_set_status, r.detail.decode())\n" % ROOT
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    l1, l2 = out.stdout.strip().splitlines()[-2:]
+    assert l1.split() == [str(_lib.GMP_ERR_DEVICE_SET)] * 2
+    assert l2.split()[:2] == [str(_lib.GMP_ERR_DEVICE_SET)] * 2 and "NVML says" in l2
+
+
+def test_probe_executable_on_the_box():
+    exe = probe.probe_executable()
+    p = subprocess.run([exe, "--bytes", "1G", "--iters", "1", "--p2p-bytes", "128M"], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    j = json.loads(p.stdout.strip().splitlines()[-1])
+    assert j["status"] == 0 and j["verdict"] == "ok" and j["n_gpus"] >= 1
+    assert j["ms_total"] < 20000

@@ -1,0 +1,243 @@
+#!/usr/bin/env python
+"""Mount latency, node-local: the reference's fork/exec path (restated in oracle/gmo_reference.c) next to the
+native path, on a cluster-less target; and, on a GPU box, mount-to-usable with the in-pod probe.
+
+    reference : per GPU `sh -c "echo 'c 195:N rw' > .../devices.allow"` + `nsenter --target P --mount sh -c "mknod ..."`,
+                serial over the G GPUs as at ref: pkg/server/gpu-mount/server.go:80-95; single-threaded.
+    native    : gmp_mount_gpus — write(2) per GPU, one setns child with G mknod(2) calls.
+    to-usable : t0 = entry of the native mount -> device nodes made -> gpumounter-probe fexecve'd inside the target
+                (device cgroup + mount namespace) -> CLOCK_MONOTONIC instant at which the first kernel result verified
+                on EVERY mounted GPU (the probe reports it).  Cold process each time: cuInit, context, cudaMalloc.
+
+Slave-pod scheduling (seconds, ref: allocator.go:40-99) needs a cluster and is not part of these numbers.
+Prints one JSON object.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import stat
+import statistics
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from gpumounter_b200 import device, probe, util  # noqa: E402
+from gpumounter_b200._model import MountEnv, Pod  # noqa: E402
+from tests import harness  # noqa: E402  (test + bench infrastructure)
+
+
+def pct(xs, q):
+    xs = sorted(xs)
+    if not xs:
+        return None
+    k = min(len(xs) - 1, max(0, int(round(q * (len(xs) - 1)))))
+    return xs[k]
+
+
+def summary(xs_s):
+    return {"p50_ms": 1e3 * statistics.median(xs_s), "p99_ms": 1e3 * pct(xs_s, 0.99), "min_ms": 1e3 * min(xs_s),
+            "mean_ms": 1e3 * statistics.fmean(xs_s), "n": len(xs_s)}
+
+
+def product_pod():
+    return Pod("gpu-pod", uid=harness.UID, container_id="docker://" + harness.CID)
+
+
+def env_of(t):
+    return MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+
+
+def fake_gpus(n):
+    return [(f"GPU-{i:08x}-0000-0000-0000-{i:012x}", i) for i in range(n)]
+
+
+def open_fds():
+    return len(os.listdir("/proc/self/fd"))
+
+
+def bench_reference(t, gpus, iters):
+    """The oracle's fork/exec restatement: the timed CPU baseline (1 thread)."""
+    from oracle import gmo_ref_ctypes as ref  # the checker doubles as the timed reference arm, nothing else
+
+    pod = ref.Pod(uid=harness.UID, container_id="docker://" + harness.CID)
+    kw = dict(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+    recs = [ref.device_new(m, u) for u, m in gpus]
+    mount_s, unmount_s = [], []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        for r in recs:  # serial, as server.go:80-95
+            ref.mount_gpu(pod, r, **kw)
+        t1 = time.perf_counter()
+        for r in recs:  # server.go:155-168
+            ref.unmount_gpu(pod, r, False, [], **kw)
+        t2 = time.perf_counter()
+        mount_s.append(t1 - t0)
+        unmount_s.append(t2 - t1)
+    return summary(mount_s), summary(unmount_s)
+
+
+def bench_native(t, gpus, iters, batched=True):
+    pod, env = product_pod(), env_of(t)
+    recs = [device.New(m, u) for u, m in gpus]
+    mount_s, unmount_s = [], []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        if batched:
+            util.MountGPUs(pod, recs, env)
+        else:
+            for r in recs:
+                util.MountGPU(pod, r, env)
+        t1 = time.perf_counter()
+        if batched:
+            util.UnmountGPUs(pod, recs, False, env)
+        else:
+            for r in recs:
+                util.UnmountGPU(pod, r, False, env)
+        t2 = time.perf_counter()
+        mount_s.append(t1 - t0)
+        unmount_s.append(t2 - t1)
+    return summary(mount_s), summary(unmount_s)
+
+
+def churn(t, rounds):
+    """1 -> 8 -> 1 GPUs, `rounds` times, native path; checks that nothing leaks."""
+    pod, env = product_pod(), env_of(t)
+    recs = [device.New(m, u) for u, m in fake_gpus(8)]
+    fds0 = open_fds()
+    step_s = []
+    t_all = time.perf_counter()
+    for _ in range(rounds):
+        for k in list(range(1, 9)) + list(range(7, 0, -1)):
+            t0 = time.perf_counter()
+            util.MountGPUs(pod, recs[:k], env)
+            assert len(t.nodes()) == k
+            util.UnmountGPUs(pod, recs[:k], False, env)
+            step_s.append(time.perf_counter() - t0)
+        assert t.nodes() == []
+    total = time.perf_counter() - t_all
+    return {"rounds": rounds, "steps": len(step_s), "total_s": total, "step": summary(step_s),
+            "leaked_fds": open_fds() - fds0, "leaked_nodes": len(t.nodes()), "host_sees": t.host_sees(),
+            "zombies": sum(1 for p in os.listdir("/proc") if p.isdigit() and _is_zombie_child(p))}
+
+
+def _is_zombie_child(pid):
+    try:
+        with open(f"/proc/{pid}/stat") as f:
+            parts = f.read().rsplit(")", 1)[1].split()
+        return parts[0] == "Z" and int(parts[1]) == os.getpid()
+    except Exception:
+        return False
+
+
+def mknod_like(src, dst):
+    st = os.stat(src)
+    os.mknod(dst, stat.S_IFCHR | 0o666, st.st_rdev)
+    os.chmod(dst, 0o666)
+
+
+def to_usable(iters, hbm_bytes, n_gpus):
+    """Real GPUs only: native mount into the target, then the in-pod probe; t1 is reported by the probe."""
+    nv = {d.uuid: d for d in probe.enumerate_nvml()}
+    cu = probe.enumerate_cuda()[:n_gpus]
+    gpus = [(d.uuid, nv[d.uuid].minor) for d in cu]
+    lat, phases = [], []
+    for _ in range(iters):
+        with harness.Target() as t:
+            # what nvidia-container-runtime provides to a pod started with NVIDIA_VISIBLE_DEVICES=none
+            # (ref: docs/guide/QuickStart.md:9,26-28): the control nodes, but no GPU node
+            for name in ("nvidiactl", "nvidia-uvm"):
+                ns_dst = f"/proc/{t.pid}/root{t.devdir}/{name}"
+                mknod_like(f"/dev/{name}", ns_dst)
+            recs = [device.New(m, u) for u, m in gpus]
+            pod, env = product_pod(), env_of(t)
+            t0 = time.monotonic_ns()
+            util.MountGPUs(pod, recs, env)
+            t_mounted = time.monotonic_ns()
+            rc, rep = util.ProbeInPod(pod, recs, ["--dev-dir", t.devdir, "--bytes", str(hbm_bytes), "--iters", "1",
+                                                   "--dma-bytes", "16M", "--p2p-bytes", "256M", "--p2p-iters", "1"], env,
+                                      raise_on_error=False)
+            t_done = time.monotonic_ns()
+            assert rc == 0 and rep.get("status") == 0, rep
+            usable = rep["mono_usable_ns"]
+            lat.append((usable - t0) / 1e9)
+            phases.append({"mount_ms": (t_mounted - t0) / 1e6, "exec_to_probe_start_ms": (rep["mono_start_ns"] - t_mounted) / 1e6,
+                           "probe_start_to_usable_ms": rep["ms_to_usable"], "cuda_init_ms": rep["ms_cuda_init"],
+                           "nvml_ms_overlapped": rep["ms_nvml"], "context_ms": max(h["ms_context"] for h in rep["hbm"]),
+                           "alloc_ms": max(h["ms_alloc"] for h in rep["hbm"]),
+                           "first_kernel_ms": max(h["ms_first_kernel"] for h in rep["hbm"]),
+                           "full_probe_ms": (t_done - t_mounted) / 1e6})
+    med = {k: statistics.median(p[k] for p in phases) for k in phases[0]}
+    return {"gpus": len(gpus), "hbm_bytes_per_gpu": hbm_bytes, "iters": iters, "p50_s": statistics.median(lat),
+            "p99_s": pct(lat, 0.99), "min_s": min(lat), "max_s": max(lat), "median_phases_ms": med}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=100)
+    ap.add_argument("--gpus", default="1,2,4,8")
+    ap.add_argument("--churn-rounds", type=int, default=100)
+    ap.add_argument("--usable-iters", type=int, default=0, help="> 0 only on a box with real GPUs")
+    ap.add_argument("--usable-bytes", type=int, default=1 << 30)
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    why = harness.can_run()
+    if why:
+        print(json.dumps({"unavailable": why}))
+        return 0
+    os.environ.setdefault("GPUMOUNTER_NVML_LIB", os.environ.get("GPUMOUNTER_NVML_LIB", ""))
+    have_gpu = os.path.exists("/dev/nvidiactl")
+    if not have_gpu:
+        # the unmount path asks NVML for the GPU's processes; without a driver use the test double
+        fake = os.path.join(ROOT, "tests", "fake_nvml", "libfake_nvml.so")
+        cfg = "/tmp/gmp_latency_fake_nvml.cfg"
+        with open(cfg, "w") as f:
+            f.write("".join(f"gpu {u} {m} 0000:00:00.0\n" for u, m in fake_gpus(8)))
+        os.environ["GPUMOUNTER_NVML_LIB"] = fake
+        os.environ["GMP_FAKE_NVML_CONFIG"] = cfg
+    else:
+        os.environ.pop("GPUMOUNTER_NVML_LIB", None)
+    out = {"host_cores": os.cpu_count(), "threads_used": 1, "iters": args.iters, "mount": {}, "unmount": {}}
+    # On a GPU box the unmount path's NVML query names a UUID: use real UUIDs where they exist, made-up ones beyond
+    real = []
+    if have_gpu:
+        nv = probe.enumerate_nvml()
+        real = [(d.uuid, d.minor + 100) for d in nv]  # minors shifted: never touch a real node name in the private /dev
+    for g in [int(x) for x in args.gpus.split(",")]:
+        gpus = (real + [x for x in fake_gpus(8)])[:g] if not have_gpu else None
+        if have_gpu:
+            # NVML only answers for real UUIDs; repeat them with distinct minors to model G GPUs' worth of work
+            gpus = [(real[i % len(real)][0], 100 + i) for i in range(g)]
+        with harness.Target() as t:
+            ref_m, ref_u = bench_reference(t, gpus, args.iters)
+        with harness.Target() as t:
+            nat_m, nat_u = bench_native(t, gpus, args.iters, batched=True)
+        with harness.Target() as t:
+            ser_m, ser_u = bench_native(t, gpus, args.iters, batched=False)
+        out["mount"][str(g)] = {"reference_fork_exec": ref_m, "native_batched": nat_m, "native_serial": ser_m,
+                                "speedup_p50": ref_m["p50_ms"] / nat_m["p50_ms"]}
+        out["unmount"][str(g)] = {"reference_fork_exec": ref_u, "native_batched": nat_u, "native_serial": ser_u,
+                                  "speedup_p50": ref_u["p50_ms"] / nat_u["p50_ms"]}
+    if args.churn_rounds and not have_gpu:
+        with harness.Target() as t:
+            out["churn_1_8_1"] = churn(t, args.churn_rounds)
+    elif args.churn_rounds:
+        out["churn_1_8_1"] = {"skipped": "churn uses made-up UUIDs, which a real NVML refuses; run on a driver-less box"}
+    if args.usable_iters > 0 and have_gpu:
+        n_vis = len(probe.enumerate_cuda())
+        out["mount_to_usable"] = {str(n): to_usable(args.usable_iters, args.usable_bytes, n)
+                                  for n in (1, 2, 4, 8) if n <= n_vis}
+    text = json.dumps(out)
+    print(text)
+    if args.out:
+        with open(args.out, "w") as f:
+            f.write(text + "\n")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
