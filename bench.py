@@ -171,7 +171,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--gib", type=float, default=8.0, help="bytes per buffer in GiB (BASELINE: 8)")
-    ap.add_argument("--dma-mib", type=int, default=64, help="pinned host<->device round trip inside the e2e call")
+    ap.add_argument("--dma-mib", type=int, default=16, help="pinned host<->device round trip inside the e2e call")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 -> min(steps, 10)")
     ap.add_argument("--cpu-sample-gib", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -5,6 +5,8 @@
 #include "gmp_internal.h"
 
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 #include <stdio.h>
 #include <string.h>
 #include <vector>
@@ -52,15 +54,40 @@ void format_uuid(const unsigned char b[16], char out[GMP_UUID_LEN]) {
              b[4], b[5], b[6], b[7], b[8], b[9], b[10], b[11], b[12], b[13], b[14], b[15]);
 }
 
+// cudaGetDeviceProperties costs milliseconds per call; a device's UUID and bus id never change within a
+// process, so they are looked up once per ordinal.
+struct DeviceIdentity {
+    std::atomic<int> ready{0};
+    char uuid[GMP_UUID_LEN];
+    char pci[GMP_PCI_LEN];
+};
+static DeviceIdentity g_identity[64];
+static std::mutex g_identity_mutex;
+
 static int device_uuid(int ordinal, char out[GMP_UUID_LEN], char pci[GMP_PCI_LEN]) {
-    cudaDeviceProp prop;
-    GMP_CUDA(cudaGetDeviceProperties(&prop, ordinal));
-    format_uuid(reinterpret_cast<const unsigned char*>(prop.uuid.bytes), out);
-    if (pci != nullptr) {
+    DeviceIdentity* slot = (ordinal >= 0 && ordinal < 64) ? &g_identity[ordinal] : nullptr;
+    if (slot == nullptr || slot->ready.load(std::memory_order_acquire) == 0) {
+        cudaDeviceProp prop;
+        GMP_CUDA(cudaGetDeviceProperties(&prop, ordinal));
+        char u[GMP_UUID_LEN], p[GMP_PCI_LEN];
+        format_uuid(reinterpret_cast<const unsigned char*>(prop.uuid.bytes), u);
         // same layout NVML uses for pci.busId: domain(8 hex):bus:device.function
-        snprintf(pci, GMP_PCI_LEN, "%08X:%02X:%02X.0", (unsigned)prop.pciDomainID, (unsigned)prop.pciBusID,
+        snprintf(p, GMP_PCI_LEN, "%08X:%02X:%02X.0", (unsigned)prop.pciDomainID, (unsigned)prop.pciBusID,
                  (unsigned)prop.pciDeviceID);
+        if (slot == nullptr) {
+            memcpy(out, u, GMP_UUID_LEN);
+            if (pci != nullptr) memcpy(pci, p, GMP_PCI_LEN);
+            return GMP_OK;
+        }
+        std::lock_guard<std::mutex> lock(g_identity_mutex);
+        if (slot->ready.load(std::memory_order_relaxed) == 0) {
+            memcpy(slot->uuid, u, GMP_UUID_LEN);
+            memcpy(slot->pci, p, GMP_PCI_LEN);
+            slot->ready.store(1, std::memory_order_release);
+        }
     }
+    memcpy(out, slot->uuid, GMP_UUID_LEN);
+    if (pci != nullptr) memcpy(pci, slot->pci, GMP_PCI_LEN);
     return GMP_OK;
 }
 
@@ -379,55 +406,55 @@ int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeReso
     out->copy_gbs_best = cp.best();
     out->copy_gbs_median = cp.median();
 
-    // host <-> device DMA round trip through pinned memory: proves the PCIe/BAR
-    // mappings of the freshly mounted device work, both directions.
+    // host <-> device DMA round trip through pinned memory: proves that the PCIe/BAR mappings of the freshly
+    // mounted device work in both directions.  device pattern -> D2H -> pinned host -> H2D -> device verify:
+    // the bulk check runs at HBM speed on the GPU; the host only spot-checks a few lanes of what arrived.
     if (o.dma_bytes != 0) {
         const uint64_t td = now_ns();
         const size_t nb = (size_t)std::min<uint64_t>(o.dma_bytes, o.bytes) & ~(size_t)15;
         if (nb != 0) {
+            const uint64_t kx = out->xor64, ks = out->sum64;
             GMP_CUDA(cudaHostAlloc(&r.pinned, nb, cudaHostAllocDefault));
-            uint64_t* h = static_cast<uint64_t*>(r.pinned);
+            const uint64_t* h = static_cast<const uint64_t*>(r.pinned);
             const uint64_t lanes = nb / 16;
-            const uint64_t s_up = o.seed ^ 0x5851F42D4C957F2Dull, s_down = o.seed ^ 0x14057B7EF767814Full;
-            for (uint64_t L = 0; L < lanes; ++L) host_lane_words(GMP_PAT_SPLITMIX, s_up, L, h[2 * L], h[2 * L + 1]);
+            const uint64_t s_rt = o.seed ^ 0x5851F42D4C957F2Dull;
+            void* back = want_copy ? r.b : r.a;  // where the data lands on its way back
             float ms = 0.f;
-            GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
-            GMP_CUDA(cudaMemcpyAsync(r.a, r.pinned, nb, cudaMemcpyHostToDevice, r.stream));
-            GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
-            GMP_CUDA(cudaEventSynchronize(r.ev[1]));
-            GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
-            out->h2d_gbs = ms > 0.f ? (double)nb / (ms * 1e-3) / 1e9 : 0.0;
-            out->h2d_bytes += nb;
-            GMP_CUDA(launch_verify(r.a, nb, GMP_PAT_SPLITMIX, s_up, r.acc, r.stream));
-            gmp_verify_result v;
-            int rc = fetch_acc(r, &v);
-            if (rc != GMP_OK) return rc;
-            out->d2h_bytes += 32;
-            note_verify(out, v, GMP_PAT_SPLITMIX);
-            GMP_CUDA(launch_write(r.a, nb, GMP_PAT_SPLITMIX, s_down, r.stream));
+            GMP_CUDA(launch_write(r.a, nb, GMP_PAT_SPLITMIX, s_rt, r.stream));
             GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
             GMP_CUDA(cudaMemcpyAsync(r.pinned, r.a, nb, cudaMemcpyDeviceToHost, r.stream));
             GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+            // scrub the landing zone while the host looks at its copy, so a no-op H2D cannot pass
+            GMP_CUDA(launch_write(back, nb, GMP_PAT_ONES, 0, r.stream));
             GMP_CUDA(cudaEventSynchronize(r.ev[1]));
             GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
             out->d2h_gbs = ms > 0.f ? (double)nb / (ms * 1e-3) / 1e9 : 0.0;
             out->d2h_bytes += nb;
-            uint64_t bad = 0, first_bad = ~0ull;
-            for (uint64_t L = 0; L < lanes; ++L) {
+            uint64_t host_bad = 0, host_first = ~0ull;
+            const uint64_t step = lanes > 64 ? lanes / 64 : 1;
+            for (uint64_t L = 0; L < lanes; L += step) {
                 uint64_t e0, e1;
-                host_lane_words(GMP_PAT_SPLITMIX, s_down, L, e0, e1);
+                host_lane_words(GMP_PAT_SPLITMIX, s_rt, L, e0, e1);
                 if (h[2 * L] != e0 || h[2 * L + 1] != e1) {
-                    if (bad == 0) first_bad = L;
-                    ++bad;
+                    if (host_bad == 0) host_first = L;
+                    ++host_bad;
                 }
             }
-            if (bad != 0) {
-                gmp_verify_result hv{bad, first_bad, 0, 0};
-                const uint64_t kx = out->xor64, ks = out->sum64;
-                note_verify(out, hv, GMP_PAT_SPLITMIX);
-                out->xor64 = kx;
-                out->sum64 = ks;
-            }
+            if (host_bad != 0) note_verify(out, gmp_verify_result{host_bad, host_first, 0, 0}, GMP_PAT_SPLITMIX);
+            GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
+            GMP_CUDA(cudaMemcpyAsync(back, r.pinned, nb, cudaMemcpyHostToDevice, r.stream));
+            GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+            GMP_CUDA(launch_verify(back, nb, GMP_PAT_SPLITMIX, s_rt, r.acc, r.stream));
+            gmp_verify_result v;
+            int rc = fetch_acc(r, &v);
+            if (rc != GMP_OK) return rc;
+            GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
+            out->h2d_gbs = ms > 0.f ? (double)nb / (ms * 1e-3) / 1e9 : 0.0;
+            out->h2d_bytes += nb;
+            out->d2h_bytes += 32;
+            note_verify(out, v, GMP_PAT_SPLITMIX);
+            out->xor64 = kx;  // the reported checksums stay those of the last full-size pass
+            out->sum64 = ks;
         }
         out->ns_dma = now_ns() - td;
     }
@@ -468,11 +495,7 @@ extern "C" int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm
     out->ns_select_device = now_ns() - t_begin;
     if (rc != GMP_OK) return out->status = rc;
     out->cuda_ordinal = ordinal;
-    {
-        cudaDeviceProp prop;
-        if (cudaGetDeviceProperties(&prop, ordinal) == cudaSuccess)
-            format_uuid(reinterpret_cast<const unsigned char*>(prop.uuid.bytes), out->uuid);
-    }
+    (void)device_uuid(ordinal, out->uuid, nullptr);
 
     int prev = -1;
     (void)cudaGetDevice(&prev);

@@ -229,7 +229,7 @@ GMP_API int gmp_tune(const char* knob, int value);
  * copy = 2*bytes.
  */
 #define GMP_HBM_DEFAULT_BYTES      (8ull << 30)
-#define GMP_HBM_DEFAULT_DMA_BYTES  (64ull << 20)
+#define GMP_HBM_DEFAULT_DMA_BYTES  (16ull << 20)
 
 typedef struct gmp_hbm_opts {
     uint64_t bytes;         /* per buffer; 0 -> GMP_HBM_DEFAULT_BYTES */
