@@ -710,3 +710,205 @@ extern "C" int gmp_tune(const char* knob, int value) {
     }
     return *slot;
 }
+
+// ---- read-verify without any allocation -----------------------------------------------------
+// gmp_hbm_read_verify() above obtains its 32-byte accumulator with cudaMalloc and returns it with
+// cudaFree on every call.  Three kinds of caller of this library cannot afford that:
+//   * a health-check sidecar re-verifying a buffer on a GPU whose memory the tenant has filled: the
+//     allocator may simply answer out-of-memory, and a probe must not compete with the workload for it;
+//   * a monitor that must not disturb the tenant: cudaFree synchronises the WHOLE device, so a periodic
+//     check through the allocating entry point stalls every stream of the workload once per call;
+//   * code that runs while the allocator is off limits, e.g. while some other thread of the process is
+//     capturing a stream in global capture mode, where cudaMalloc is a forbidden call.
+// For them the scratch lives in device memory that exists from the moment the library is loaded: a
+// file-scope array that every GPU using the library holds until the process exits (65 568 bytes).  The
+// buffer is cut into 4 MiB segments, one CTA per segment writes that segment's partial verdict into its
+// own slot (plain stores, no atomics), and a one-CTA fold kernel combines the slots into the result slot.
+// 2048 slots => at most 8 GiB per call.
+namespace gmp {
+
+constexpr size_t kNoAllocSegmentBytes = (size_t)4 << 20;
+constexpr int kNoAllocMaxSegments = 2048;
+constexpr int kNoAllocResultSlot = kNoAllocMaxSegments;  // index (in 4-word slots) of the folded result
+static_assert((unsigned long long)kNoAllocSegmentBytes * kNoAllocMaxSegments == GMP_NOALLOC_MAX_BYTES,
+              "header limit and scratch size must agree");
+
+// In HOST code this name is only a handle for cudaGetSymbolAddress(); it is not a device address.
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[(kNoAllocMaxSegments + 1) * 4];
+
+template <int PAT>
+__global__ void __launch_bounds__(256, 4)
+    k_hbm_read_verify_segments(const uint4* __restrict__ src, uint64_t nlanes, uint32_t tail_bytes, uint64_t seed,
+                               unsigned long long* __restrict__ slots) {
+    constexpr int THREADS = 256, UNROLL = 4;
+    constexpr uint64_t kSegLanes = kNoAllocSegmentBytes / 16;
+    const uint64_t seg_begin = (uint64_t)blockIdx.x * kSegLanes;
+    const uint64_t seg_end = seg_begin + kSegLanes < nlanes ? seg_begin + kSegLanes : nlanes;
+    uint64_t bad = 0, inv_first = 0, x = 0, s = 0;
+    for (uint64_t tile = seg_begin; tile < seg_end; tile += (uint64_t)THREADS * UNROLL) {
+        const uint64_t base = tile + threadIdx.x;
+        if (tile + (uint64_t)THREADS * UNROLL <= seg_end) {
+            uint4 v[UNROLL][1];
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) ld_chunk<1, HINT_DEFAULT>(src + base + (uint64_t)j * THREADS, v[j]);
+            uint32_t dirty = 0;
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) fold_lane<PAT>(v[j][0], seed, base + (uint64_t)j * THREADS, dirty, x, s);
+            if (dirty != 0) {
+#pragma unroll
+                for (int j = 0; j < UNROLL; ++j)
+                    count_bad_lane<PAT>(v[j][0], seed, base + (uint64_t)j * THREADS, &bad, &inv_first);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < UNROLL; ++j) {
+                const uint64_t L = base + (uint64_t)j * THREADS;
+                if (L < seg_end) {
+                    uint4 v[1];
+                    ld_chunk<1, HINT_DEFAULT>(src + L, v);
+                    check_lane<PAT>(v[0], seed, L, bad, inv_first, x, s);
+                }
+            }
+        }
+    }
+    // the ragged last lane belongs to the last segment's CTA
+    if (tail_bytes != 0 && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+        uint64_t e0, e1;
+        lane_words<PAT>(seed, nlanes, e0, e1);
+        const unsigned char* p = reinterpret_cast<const unsigned char*>(src + nlanes);
+        uint64_t g0 = 0, g1 = 0;
+        for (uint32_t b = 0; b < tail_bytes; ++b) {
+            const uint64_t byte = p[b];
+            if (b < 8) g0 |= byte << (8 * b);
+            else g1 |= byte << (8 * (b - 8));
+        }
+        const uint64_t m0 = tail_bytes >= 8 ? ~0ull : ((1ull << (8 * tail_bytes)) - 1);
+        const uint64_t m1 = tail_bytes <= 8 ? 0ull : ((1ull << (8 * (tail_bytes - 8))) - 1);
+        x ^= g0 ^ g1;
+        s += g0 + g1;
+        if (((g0 ^ e0) & m0) | ((g1 ^ e1) & m1)) {
+            bad += 1;
+            const uint64_t inv = ~0ull - nlanes;
+            inv_first = inv > inv_first ? inv : inv_first;
+        }
+    }
+    // fold the CTA and store its verdict into this segment's own slot (no atomics: the slot is ours alone)
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+        bad += shfl_xor64(bad, m);
+        const uint64_t o = shfl_xor64(inv_first, m);
+        inv_first = o > inv_first ? o : inv_first;
+        x ^= shfl_xor64(x, m);
+        s += shfl_xor64(s, m);
+    }
+    __shared__ uint64_t sh[4][THREADS / 32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        sh[0][warp] = bad;
+        sh[1][warp] = inv_first;
+        sh[2][warp] = x;
+        sh[3][warp] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        bad = 0, inv_first = 0, x = 0, s = 0;
+        for (int w = 0; w < THREADS / 32; ++w) {
+            bad += sh[0][w];
+            inv_first = sh[1][w] > inv_first ? sh[1][w] : inv_first;
+            x ^= sh[2][w];
+            s += sh[3][w];
+        }
+        unsigned long long* slot = slots + (size_t)blockIdx.x * 4;
+        slot[0] = bad;
+        slot[1] = inv_first;
+        slot[2] = x;
+        slot[3] = s;
+    }
+}
+
+// One CTA: combine the first `nsegs` slots into the result slot, which the host cleared beforehand.
+__global__ void __launch_bounds__(256) k_noalloc_fold(unsigned long long* __restrict__ slots, int nsegs) {
+    uint64_t bad = 0, inv_first = 0, x = 0, s = 0;
+    for (int k = threadIdx.x; k < nsegs; k += 256) {
+        const unsigned long long* slot = slots + (size_t)k * 4;
+        bad += slot[0];
+        inv_first = slot[1] > inv_first ? slot[1] : inv_first;
+        x ^= slot[2];
+        s += slot[3];
+    }
+    block_fold_and_publish<256>(bad, inv_first, x, s, slots + (size_t)kNoAllocResultSlot * 4);
+}
+
+// Device address of g_noalloc_scratch on the CURRENT device, looked up once per device.
+static cudaError_t noalloc_scratch_on_current_device(unsigned long long** out) {
+    static std::atomic<unsigned long long*> cache[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const bool cacheable = dev >= 0 && dev < 64;
+    unsigned long long* p = cacheable ? cache[dev].load(std::memory_order_acquire) : nullptr;
+    if (p == nullptr) {
+        void* addr = nullptr;
+        e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);  // `dev` is current: this is ITS copy of the array
+        if (e != cudaSuccess) return e;
+        p = static_cast<unsigned long long*>(addr);
+        if (cacheable) cache[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
+template <int PAT>
+static cudaError_t launch_segments(const uint4* src, uint64_t nlanes, uint32_t tail, uint64_t seed,
+                                   unsigned long long* slots, int nsegs, cudaStream_t s) {
+    k_hbm_read_verify_segments<PAT><<<(unsigned)nsegs, 256, 0, s>>>(src, nlanes, tail, seed, slots);
+    return cudaGetLastError();
+}
+
+}  // namespace gmp
+
+extern "C" int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int pattern, uint64_t seed,
+                                           gmp_verify_result* out, void* stream) {
+    clear_error();
+    if (out == nullptr) {
+        set_error("out is NULL");
+        return GMP_ERR_INVALID;
+    }
+    int rc = check_buffer(dptr, bytes, pattern);
+    if (rc != GMP_OK) return rc;
+    if (bytes > GMP_NOALLOC_MAX_BYTES) {
+        set_error("%zu bytes exceed the %llu-byte limit of the allocation-free verify (static scratch holds %d segments "
+                  "of %zu MiB); use gmp_hbm_read_verify or split the buffer",
+                  bytes, (unsigned long long)GMP_NOALLOC_MAX_BYTES, kNoAllocMaxSegments, kNoAllocSegmentBytes >> 20);
+        return GMP_ERR_INVALID;
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    unsigned long long* scratch = nullptr;
+    GMP_CUDA(noalloc_scratch_on_current_device(&scratch));
+    unsigned long long* result = scratch + (size_t)kNoAllocResultSlot * 4;
+    // The array still holds the previous call's slots and result.  Slots are fully rewritten by the CTAs that
+    // own them and only the first nsegs are read back; the result slot is accumulated into, so it must be zero.
+    GMP_CUDA(cudaMemsetAsync(result, 0, 4 * sizeof(unsigned long long), s));
+    const uint64_t nlanes = bytes / 16;
+    const uint32_t tail = (uint32_t)(bytes % 16);
+    const int nsegs = (int)((bytes + kNoAllocSegmentBytes - 1) / kNoAllocSegmentBytes);
+    if (nsegs > 0) {
+        const uint4* src = static_cast<const uint4*>(dptr);
+        cudaError_t e = cudaErrorInvalidValue;
+        switch (pattern) {
+            case GMP_PAT_SPLITMIX: e = launch_segments<GMP_PAT_SPLITMIX>(src, nlanes, tail, seed, scratch, nsegs, s); break;
+            case GMP_PAT_ZERO: e = launch_segments<GMP_PAT_ZERO>(src, nlanes, tail, seed, scratch, nsegs, s); break;
+            case GMP_PAT_ONES: e = launch_segments<GMP_PAT_ONES>(src, nlanes, tail, seed, scratch, nsegs, s); break;
+            case GMP_PAT_CHECKER: e = launch_segments<GMP_PAT_CHECKER>(src, nlanes, tail, seed, scratch, nsegs, s); break;
+            case GMP_PAT_ADDRESS: e = launch_segments<GMP_PAT_ADDRESS>(src, nlanes, tail, seed, scratch, nsegs, s); break;
+        }
+        GMP_CUDA(e);
+        k_noalloc_fold<<<1, 256, 0, s>>>(scratch, nsegs);
+        GMP_CUDA(cudaGetLastError());
+    }
+    unsigned long long raw[4] = {0, 0, 0, 0};
+    GMP_CUDA(cudaMemcpyAsync(raw, result, sizeof(raw), cudaMemcpyDeviceToHost, s));
+    GMP_CUDA(cudaStreamSynchronize(s));
+    decode_acc(raw, out);
+    return GMP_OK;
+}

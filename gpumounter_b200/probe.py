@@ -194,6 +194,22 @@ def hbm_read_verify(dptr: int, nbytes: int, pattern: int = PAT_SPLITMIX, seed: i
     return VerifyResult(r.mismatch_lanes, r.first_bad_lane, r.xor64, r.sum64)
 
 
+NOALLOC_MAX_BYTES = 8 << 30
+
+
+def hbm_read_verify_noalloc(dptr: int, nbytes: int, pattern: int = PAT_SPLITMIX, seed: int = 0, stream: int = 0) -> VerifyResult:
+    """hbm_read_verify() for callers that must not allocate device memory (a sidecar on a GPU the tenant has
+    filled, a monitor that must not trigger cudaFree's device-wide synchronisation, code running while another
+    thread captures a stream).  Scratch is a fixed array inside the library: at most NOALLOC_MAX_BYTES per call,
+    one call at a time per device, first call per device before any stream capture."""
+    f = lib().gmp_hbm_read_verify_noalloc
+    f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64,
+                  ctypes.POINTER(gmp_verify_result), ctypes.c_void_p]
+    r = gmp_verify_result()
+    check(f(_ptr(dptr), nbytes, pattern, seed & UINT64_MAX, ctypes.byref(r), _ptr(stream)), "gmp_hbm_read_verify_noalloc")
+    return VerifyResult(r.mismatch_lanes, r.first_bad_lane, r.xor64, r.sum64)
+
+
 def hbm_read_verify_async(dptr: int, nbytes: int, pattern: int, seed: int, d_acc: int, stream: int = 0) -> None:
     f = lib().gmp_hbm_read_verify_async
     f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]

@@ -202,6 +202,31 @@ GMP_API int gmp_hbm_copy(void* dst, const void* src, size_t bytes, void* stream)
 GMP_API int gmp_hbm_read_verify_async(const void* dptr, size_t bytes, int pattern, uint64_t seed,
                               void* d_acc, void* stream);
 GMP_API int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, void* stream);
+/*
+ * gmp_hbm_read_verify() for callers that must not allocate.  It has no counterpart in the reference
+ * (nothing there touches device memory).
+ *
+ * Who needs it: a health-check sidecar on a GPU whose memory the tenant has already filled (cudaMalloc
+ * can fail there, and a probe should not compete with the workload for memory); a monitor that must
+ * not stall the tenant (the allocating entry point ends in cudaFree, which synchronises the whole
+ * device); and code that runs while the CUDA allocator is off limits, for instance while another
+ * thread of the process is capturing a stream.  This call makes no cudaMalloc / cudaFree / other
+ * allocating call: its scratch is a 65 568-byte array that is part of the library image and sits in
+ * the memory of every GPU that uses the library, until the process exits.
+ *
+ * Same arguments, same result and the same bit-exact checksums as gmp_hbm_read_verify().  Limits and
+ * rules that come with the fixed scratch:
+ *   - bytes <= GMP_NOALLOC_MAX_BYTES (8 GiB: 2048 segments of 4 MiB, one scratch slot each); larger
+ *     buffers are refused with GMP_ERR_INVALID and a message saying so — verify them in pieces;
+ *   - every call on a device uses the same array, which still holds the previous call's data (the
+ *     call clears the part that has to start at zero).  Two calls whose GPU work overlaps — different
+ *     streams, different threads — race on it and return garbage: serialise them per device;
+ *   - the first call on each device looks up the array's device address; make that first call before
+ *     starting any stream capture.
+ */
+#define GMP_NOALLOC_MAX_BYTES (8ull << 30)
+GMP_API int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int pattern, uint64_t seed,
+                                        gmp_verify_result* out, void* stream);
 /* Fault injection for tests: XOR one byte of device memory with `mask`. */
 GMP_API int gmp_hbm_corrupt(void* dptr, size_t bytes, size_t byte_offset, uint8_t mask, void* stream);
 /*

@@ -1,0 +1,85 @@
+"""The allocation-free verify entry point against the allocating one, through the C ABI (GPU box only).
+
+gmp_hbm_read_verify_noalloc exists for callers that cannot allocate device memory: a health-check sidecar on a GPU
+whose memory the tenant has filled, a monitor that must not cause cudaFree's device-wide synchronisation, code that
+runs while another thread is capturing a stream.  Its scratch is one fixed array inside the library that every call
+on a device shares, so this file checks the thing that sharing could break: two calls in a row, on different data,
+each have to agree bit for bit with gmp_hbm_read_verify on the same buffer.
+
+The file name sorts last on purpose: if this test fails, `pytest -x` has already run everything else.  It makes no
+assumption about what ran before it and passes alone in a fresh process as well.
+"""
+
+import pytest
+
+from gpumounter_b200 import ProbeError, _lib, probe
+
+pytestmark = pytest.mark.gpu
+
+SEED = 0x9E3779B97F4A7C15
+
+
+def as_tuple(r):
+    return (r.mismatch_lanes, r.first_bad_lane, r.xor64, r.sum64)
+
+
+def test_two_calls_in_a_row_agree_with_the_allocating_entry_point(cuda):
+    torch = cuda
+    s = torch.cuda.current_stream().cuda_stream
+    # first call: a clean buffer spanning several 4 MiB segments, ragged end
+    n1 = (19 << 20) + 7
+    a = torch.empty(n1 + 64, dtype=torch.uint8, device="cuda")
+    probe.hbm_write_pattern(a.data_ptr(), n1, probe.PAT_SPLITMIX, SEED, s)
+    want1 = probe.hbm_read_verify(a.data_ptr(), n1, probe.PAT_SPLITMIX, SEED, s)
+    got1 = probe.hbm_read_verify_noalloc(a.data_ptr(), n1, probe.PAT_SPLITMIX, SEED, s)
+    assert as_tuple(got1) == as_tuple(want1) and got1.ok
+    # second call straight after, on other data with faults in three different segments and in the ragged tail:
+    # the array still holds the first call's slots and result, none of which may leak into this answer
+    n2 = (9 << 20) + 3
+    b = torch.empty(n2 + 64, dtype=torch.uint8, device="cuda")
+    probe.hbm_write_pattern(b.data_ptr(), n2, probe.PAT_ADDRESS, b.data_ptr(), s)
+    for off in (5, (4 << 20) + 1234, (8 << 20) + 99, n2 - 1):
+        probe.hbm_corrupt(b.data_ptr(), n2, off, 0x04, s)
+    want2 = probe.hbm_read_verify(b.data_ptr(), n2, probe.PAT_ADDRESS, b.data_ptr(), s)
+    got2 = probe.hbm_read_verify_noalloc(b.data_ptr(), n2, probe.PAT_ADDRESS, b.data_ptr(), s)
+    assert as_tuple(got2) == as_tuple(want2)
+    assert (got2.mismatch_lanes, got2.first_bad_lane) == (4, 0)
+    # and the first buffer again: still the first answer
+    assert as_tuple(probe.hbm_read_verify_noalloc(a.data_ptr(), n1, probe.PAT_SPLITMIX, SEED, s)) == as_tuple(want1)
+
+
+@pytest.mark.parametrize("nbytes", [0, 1, 15, 16, 17, 4 << 20, (4 << 20) + 5, (4 << 20) - 16, (64 << 20) + 48])
+@pytest.mark.parametrize("pattern", range(probe.PAT_COUNT))
+def test_sizes_and_patterns_agree(cuda, nbytes, pattern):
+    torch = cuda
+    s = torch.cuda.current_stream().cuda_stream
+    t = torch.empty(nbytes + 64, dtype=torch.uint8, device="cuda")
+    seed = SEED + pattern
+    probe.hbm_write_pattern(t.data_ptr(), nbytes, pattern, seed, s)
+    assert as_tuple(probe.hbm_read_verify_noalloc(t.data_ptr(), nbytes, pattern, seed, s)) == as_tuple(
+        probe.hbm_read_verify(t.data_ptr(), nbytes, pattern, seed, s))
+    # a wrong seed makes (nearly) every lane differ; both entry points must count the same lanes
+    if pattern in (probe.PAT_SPLITMIX, probe.PAT_ADDRESS) and nbytes:
+        assert as_tuple(probe.hbm_read_verify_noalloc(t.data_ptr(), nbytes, pattern, seed + 1, s)) == as_tuple(
+            probe.hbm_read_verify(t.data_ptr(), nbytes, pattern, seed + 1, s))
+
+
+def test_size_beyond_the_scratch_is_refused_with_a_clear_message(cuda):
+    torch = cuda
+    t = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")
+    with pytest.raises(ProbeError) as e:
+        # only the size is looked at before the refusal; nothing is launched on the too-small tensor
+        probe.hbm_read_verify_noalloc(t.data_ptr(), probe.NOALLOC_MAX_BYTES + 16)
+    assert e.value.code == _lib.GMP_ERR_INVALID
+    assert "exceed" in e.value.detail and "2048 segments" in e.value.detail
+
+
+def test_the_largest_allowed_size(cuda):
+    torch = cuda
+    s = torch.cuda.current_stream().cuda_stream
+    n = probe.NOALLOC_MAX_BYTES
+    t = torch.empty(n, dtype=torch.uint8, device="cuda")
+    probe.hbm_write_pattern(t.data_ptr(), n, probe.PAT_SPLITMIX, SEED + 9, s)
+    probe.hbm_corrupt(t.data_ptr(), n, n - 7, 0x80, s)
+    assert as_tuple(probe.hbm_read_verify_noalloc(t.data_ptr(), n, probe.PAT_SPLITMIX, SEED + 9, s)) == as_tuple(
+        probe.hbm_read_verify(t.data_ptr(), n, probe.PAT_SPLITMIX, SEED + 9, s))
