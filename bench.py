@@ -132,6 +132,31 @@ def cpu_port_run(sample_bytes: int, threads: int, min_seconds: float, max_reps: 
     return gbs, total_s / reps, reps, [p / reps for p in per]
 
 
+def mount_section(n_gpus: int, iters: int):
+    """Node-local mount latency (reference fork/exec path vs native) and mount-to-usable p50/p99 on n_gpus GPUs."""
+    try:
+        from tests import harness
+        from tools import mount_latency as ml
+
+        why = harness.can_run()
+        if why:
+            return {"unavailable": why}
+        nv = __import__("gpumounter_b200").probe.enumerate_nvml()
+        gpus = [(nv[i % len(nv)].uuid, 100 + i) for i in range(n_gpus)]  # private /dev: minors shifted off the real nodes
+        with harness.Target() as t:
+            ref_m, _ = ml.bench_reference(t, gpus, 30)
+        with harness.Target() as t:
+            nat_m, _ = ml.bench_native(t, gpus, 30, batched=True)
+        out = {"gpus": n_gpus, "host_cores": os.cpu_count(), "threads_used": 1,
+               "reference_fork_exec_mount_ms": {"p50": ref_m["p50_ms"], "p99": ref_m["p99_ms"]},
+               "native_mount_ms": {"p50": nat_m["p50_ms"], "p99": nat_m["p99_ms"]},
+               "note": "slave-pod scheduling (ref: allocator.go:40-99) needs a cluster and is not included"}
+        out["mount_to_usable"] = ml.to_usable(iters, 1 << 30, n_gpus)
+        return out
+    except Exception as e:  # the bench line must still be printed
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+
+
 def run_reference(args, rank: int, world: int):
     if rank != 0:
         return
@@ -176,6 +201,8 @@ def main():
     ap.add_argument("--cpu-sample-gib", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-clocks", action="store_true")
+    ap.add_argument("--no-mount", action="store_true", help="skip the mount-latency / mount-to-usable section")
+    ap.add_argument("--mount-iters", type=int, default=8)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -355,6 +382,12 @@ def main():
                       f"{reps} reps, {sec:.2f} s per rep (the reference has no device-memory code to time)",
             "seconds_per_pass": {"fill": per[0], "verify": per[1], "copy": per[2]},
         }
+    if not args.no_mount:
+        # the other half of BASELINE's metric: mount latency next to the reference's own mount path on this host, and
+        # mount-to-usable with the in-pod probe on all `world` GPUs (rank 0 alone; the other ranks have left)
+        del a, acc
+        torch.cuda.empty_cache()
+        line["mount"] = mount_section(world, args.mount_iters)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

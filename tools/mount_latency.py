@@ -145,7 +145,7 @@ def to_usable(iters, hbm_bytes, n_gpus):
     nv = {d.uuid: d for d in probe.enumerate_nvml()}
     cu = probe.enumerate_cuda()[:n_gpus]
     gpus = [(d.uuid, nv[d.uuid].minor) for d in cu]
-    lat, phases = [], []
+    lat, phases, last = [], [], None
     for _ in range(iters):
         with harness.Target() as t:
             # what nvidia-container-runtime provides to a pod started with NVIDIA_VISIBLE_DEVICES=none
@@ -163,6 +163,7 @@ def to_usable(iters, hbm_bytes, n_gpus):
                                       raise_on_error=False)
             t_done = time.monotonic_ns()
             assert rc == 0 and rep.get("status") == 0, rep
+            last = rep
             usable = rep["mono_usable_ns"]
             lat.append((usable - t0) / 1e9)
             phases.append({"mount_ms": (t_mounted - t0) / 1e6, "exec_to_probe_start_ms": (rep["mono_start_ns"] - t_mounted) / 1e6,
@@ -172,8 +173,24 @@ def to_usable(iters, hbm_bytes, n_gpus):
                            "first_kernel_ms": max(h["ms_first_kernel"] for h in rep["hbm"]),
                            "full_probe_ms": (t_done - t_mounted) / 1e6})
     med = {k: statistics.median(p[k] for p in phases) for k in phases[0]}
-    return {"gpus": len(gpus), "hbm_bytes_per_gpu": hbm_bytes, "iters": iters, "p50_s": statistics.median(lat),
-            "p99_s": pct(lat, 0.99), "min_s": min(lat), "max_s": max(lat), "median_phases_ms": med}
+    out = {"gpus": len(gpus), "hbm_bytes_per_gpu": hbm_bytes, "iters": iters, "p50_s": statistics.median(lat),
+           "p99_s": pct(lat, 0.99), "min_s": min(lat), "max_s": max(lat), "median_phases_ms": med,
+           "device_set_equals_nvml": last["device_set_status"] == 0 and last["nvml_status"] == 0,
+           "hbm_gbs_per_gpu_last": [{"write": h["write_gbs"], "verify": h["read_gbs"], "copy": h["copy_gbs"]} for h in last["hbm"]]}
+    if "p2p" in last:
+        q = last["p2p"]
+        n = len(q["can_access"])
+        off = [(i, j) for i in range(n) for j in range(n) if i != j]
+        wr = [q["write_gbs"][i][j] for i, j in off]
+        rd = [q["read_gbs"][i][j] for i, j in off]
+        out["p2p"] = {"matrix_match_nvml": q["matrix_match"] == 1, "pairs": len(off),
+                      "all_pairs_accessible": all(q["can_access"][i][j] == 1 for i, j in off),
+                      "all_pairs_nvlink": all(q["nvml_nvlink"][i][j] == 0 for i, j in off),
+                      "store_gbs": {"min": min(wr), "mean": statistics.fmean(wr), "max": max(wr)},
+                      "load_gbs": {"min": min(rd), "mean": statistics.fmean(rd), "max": max(rd)},
+                      "bidir_gbs_per_gpu_min": min(q["bidir_gbs"]), "alltoall_gbs": q["alltoall_gbs"],
+                      "nvlink_active": q["nvlink_active"], "bytes_per_pair": q["bytes"], "mismatch_lanes": q["mismatch_lanes"]}
+    return out
 
 
 def main():
