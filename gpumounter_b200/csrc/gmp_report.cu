@@ -354,6 +354,7 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
         j.kms("ms_dma", h.ns_dma);
         j.kms("ms_teardown", h.ns_teardown);
         j.kms("ms_total", h.ns_total);
+        j.ku("mono_first_verified_ns", h.mono_first_verified_ns);
         j.raw("}");
     }
     j.raw("]");

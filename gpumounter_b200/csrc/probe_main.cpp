@@ -61,6 +61,12 @@ void usage() {
 }  // namespace
 
 int main(int argc, char** argv) {
+    // The probe drives one stream per GPU.  The driver sizes a context's channel pool by these two variables and
+    // context creation time follows it (B200, driver 580: 8 connections (default) ~190-240 ms, 1 connection
+    // ~110-140 ms, 32 connections ~1000 ms per context).  Contexts of one process are created one after another
+    // inside the driver, so with eight GPUs this is 0.5 s of mount-to-usable latency.  An operator's own setting wins.
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "1", 0);
+    setenv("CUDA_DEVICE_MAX_COPY_CONNECTIONS", "1", 0);
     gmp_probe_opts o;
     memset(&o, 0, sizeof(o));
     o.hbm.dma_bytes = UINT64_MAX;  // library default

@@ -155,6 +155,9 @@ def to_usable(iters, hbm_bytes, n_gpus):
                 mknod_like(f"/dev/{name}", ns_dst)
             recs = [device.New(m, u) for u, m in gpus]
             pod, env = product_pod(), env_of(t)
+            # a pod sees only the GPUs mounted into it (device cgroup); the stand-in target shares the host's /dev,
+            # so the same restriction is expressed to CUDA through the environment the probe inherits
+            os.environ["CUDA_VISIBLE_DEVICES"] = ",".join(u for u, _ in gpus)
             t0 = time.monotonic_ns()
             util.MountGPUs(pod, recs, env)
             t_mounted = time.monotonic_ns()
@@ -162,6 +165,7 @@ def to_usable(iters, hbm_bytes, n_gpus):
                                                    "--dma-bytes", "16M", "--p2p-bytes", "256M", "--p2p-iters", "1"], env,
                                       raise_on_error=False)
             t_done = time.monotonic_ns()
+            os.environ.pop("CUDA_VISIBLE_DEVICES", None)
             assert rc == 0 and rep.get("status") == 0, rep
             last = rep
             usable = rep["mono_usable_ns"]
@@ -171,6 +175,7 @@ def to_usable(iters, hbm_bytes, n_gpus):
                            "nvml_ms_overlapped": rep["ms_nvml"], "context_ms": max(h["ms_context"] for h in rep["hbm"]),
                            "alloc_ms": max(h["ms_alloc"] for h in rep["hbm"]),
                            "first_kernel_ms": max(h["ms_first_kernel"] for h in rep["hbm"]),
+                           "first_gpu_usable_ms": (min(h["mono_first_verified_ns"] for h in rep["hbm"]) - t0) / 1e6,
                            "full_probe_ms": (t_done - t_mounted) / 1e6})
     med = {k: statistics.median(p[k] for p in phases) for k in phases[0]}
     out = {"gpus": len(gpus), "hbm_bytes_per_gpu": hbm_bytes, "iters": iters, "p50_s": statistics.median(lat),
