@@ -74,11 +74,19 @@ struct DeviceInfo {
 };
 cudaError_t current_device_info(DeviceInfo* info);
 
-cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, cudaStream_t s);
+// cfg == nullptr: the process-wide tunables for local HBM.
+struct LaunchCfg {
+    int variant;
+    int ctas_per_sm;
+};
+cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, cudaStream_t s,
+                         const LaunchCfg* cfg = nullptr);
 // d_acc: 4 x u64 of device memory, zeroed by this call before the kernel.
 cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed,
-                          unsigned long long* d_acc, cudaStream_t s);
-cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s);
+                          unsigned long long* d_acc, cudaStream_t s, const LaunchCfg* cfg = nullptr);
+cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s, const LaunchCfg* cfg = nullptr);
+// Geometry for kernels whose pointer is PEER memory (NVLink): picked by tools/sweep_p2p.py.
+extern const LaunchCfg kPeerStoreCfg, kPeerLoadCfg;
 void decode_acc(const unsigned long long raw[4], gmp_verify_result* out);
 
 // Launch geometry knobs (benchmarking only; see gmp_tune()).

@@ -461,8 +461,12 @@ static int pick_variant(int wanted, const void* p0, const void* p1) {
 
 template <int PAT>
 static cudaError_t launch_write_pat(uint4* dst, uint64_t nlanes, uint32_t tail, uint64_t seed, int sm_count,
-                                    cudaStream_t s) {
-    const Tunables& tn = tunables();
+                                    cudaStream_t s, const LaunchCfg* cfg) {
+    Tunables tn = tunables();
+    if (cfg) {
+        tn.write_variant = cfg->variant;
+        tn.write_ctas_per_sm = cfg->ctas_per_sm;
+    }
     switch (pick_variant(tn.write_variant, dst, nullptr)) {
 #define X(ID, T, U, V, H)                                                                            \
     case ID:                                                                                         \
@@ -481,8 +485,12 @@ static cudaError_t launch_write_pat(uint4* dst, uint64_t nlanes, uint32_t tail, 
 
 template <int PAT>
 static cudaError_t launch_verify_pat(const uint4* src, uint64_t nlanes, uint32_t tail, uint64_t seed,
-                                     unsigned long long* acc, int sm_count, cudaStream_t s) {
-    const Tunables& tn = tunables();
+                                     unsigned long long* acc, int sm_count, cudaStream_t s, const LaunchCfg* cfg) {
+    Tunables tn = tunables();
+    if (cfg) {
+        tn.read_variant = cfg->variant;
+        tn.read_ctas_per_sm = cfg->ctas_per_sm;
+    }
     switch (pick_variant(tn.read_variant, src, nullptr)) {
 #define X(ID, T, U, V, H)                                                                           \
     case ID:                                                                                        \
@@ -515,20 +523,23 @@ static cudaError_t launch_verify_pat(const uint4* src, uint64_t nlanes, uint32_t
             return cudaErrorInvalidValue;        \
     }
 
-cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, cudaStream_t s) {
+const LaunchCfg kPeerStoreCfg = {11, 8};  // 1024x1x32B .cs: peer stores plateau at ~713 GB/s whatever the geometry
+const LaunchCfg kPeerLoadCfg = {1, 32};   // 256x4x16B .cs x 32 CTAs/SM: 781 GB/s (cudaMemcpyPeer: 770)
+
+cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, cudaStream_t s, const LaunchCfg* cfg) {
     if (bytes == 0) return cudaSuccess;
     DeviceInfo di;
     cudaError_t e = current_device_info(&di);
     if (e != cudaSuccess) return e;
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
-#define CALL(P) launch_write_pat<P>(static_cast<uint4*>(dptr), nlanes, tail, seed, di.sm_count, s)
+#define CALL(P) launch_write_pat<P>(static_cast<uint4*>(dptr), nlanes, tail, seed, di.sm_count, s, cfg)
     GMP_PATTERN_SWITCH(pattern, CALL)
 #undef CALL
 }
 
 cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed, unsigned long long* d_acc,
-                          cudaStream_t s) {
+                          cudaStream_t s, const LaunchCfg* cfg) {
     if (pattern < 0 || pattern >= GMP_PAT_COUNT) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(d_acc, 0, 4 * sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
@@ -538,19 +549,23 @@ cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t 
     if (e != cudaSuccess) return e;
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
-#define CALL(P) launch_verify_pat<P>(static_cast<const uint4*>(dptr), nlanes, tail, seed, d_acc, di.sm_count, s)
+#define CALL(P) launch_verify_pat<P>(static_cast<const uint4*>(dptr), nlanes, tail, seed, d_acc, di.sm_count, s, cfg)
     GMP_PATTERN_SWITCH(pattern, CALL)
 #undef CALL
 }
 
-cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s) {
+cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s, const LaunchCfg* cfg) {
     if (bytes == 0) return cudaSuccess;
     DeviceInfo di;
     cudaError_t e = current_device_info(&di);
     if (e != cudaSuccess) return e;
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
-    const Tunables& tn = tunables();
+    Tunables tn = tunables();
+    if (cfg) {
+        tn.copy_variant = cfg->variant;
+        tn.copy_ctas_per_sm = cfg->ctas_per_sm;
+    }
     switch (pick_variant(tn.copy_variant, dst, src)) {
 #define X(ID, T, U, V, H)                                                                          \
     case ID:                                                                                       \

@@ -98,7 +98,7 @@ int run_pairs(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
                 // i stores into j's HBM
                 GMP_CUDA(cudaSetDevice(pi.ordinal));
                 GMP_CUDA(cudaEventRecord(pi.e0, pi.stream));
-                GMP_CUDA(launch_write(pj.buf, o.bytes, GMP_PAT_SPLITMIX, seed, pi.stream));
+                GMP_CUDA(launch_write(pj.buf, o.bytes, GMP_PAT_SPLITMIX, seed, pi.stream, &kPeerStoreCfg));
                 GMP_CUDA(cudaEventRecord(pi.e1, pi.stream));
                 GMP_CUDA(cudaEventSynchronize(pi.e1));
                 GMP_CUDA(cudaEventElapsedTime(&ms, pi.e0, pi.e1));
@@ -108,7 +108,7 @@ int run_pairs(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
                 // i loads j's HBM and verifies in the same pass
                 GMP_CUDA(cudaSetDevice(pi.ordinal));
                 GMP_CUDA(cudaEventRecord(pi.e0, pi.stream));
-                GMP_CUDA(launch_verify(pj.buf, o.bytes, GMP_PAT_SPLITMIX, seed, pi.acc, pi.stream));
+                GMP_CUDA(launch_verify(pj.buf, o.bytes, GMP_PAT_SPLITMIX, seed, pi.acc, pi.stream, &kPeerLoadCfg));
                 GMP_CUDA(cudaEventRecord(pi.e1, pi.stream));
                 GMP_CUDA(cudaEventSynchronize(pi.e1));
                 GMP_CUDA(cudaEventElapsedTime(&ms, pi.e0, pi.e1));
@@ -151,7 +151,8 @@ int run_bidir(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
             PeerGpu& px = s.g[(size_t)x];
             GMP_CUDA(cudaSetDevice(px.ordinal));
             GMP_CUDA(cudaEventRecord(px.e0, px.stream));
-            GMP_CUDA(launch_write(s.g[(size_t)p].buf, o.bytes, GMP_PAT_SPLITMIX, pair_seed(seed_base, x, p, 0), px.stream));
+            GMP_CUDA(launch_write(s.g[(size_t)p].buf, o.bytes, GMP_PAT_SPLITMIX, pair_seed(seed_base, x, p, 0), px.stream,
+                                  &kPeerStoreCfg));
             GMP_CUDA(cudaEventRecord(px.e1, px.stream));
         }
         std::vector<float> ms((size_t)n, 0.f);
@@ -195,7 +196,7 @@ int run_alltoall(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
         for (int k = 1; k < n; ++k) {  // step k is the permutation i -> i+k: no two senders share a receiver
             const int j = (i + k) % n;
             GMP_CUDA(launch_write(static_cast<char*>(s.g[(size_t)j].buf) + (size_t)i * slice, slice, GMP_PAT_SPLITMIX,
-                                  pair_seed(seed_base, i, j, 0), pi.stream));
+                                  pair_seed(seed_base, i, j, 0), pi.stream, &kPeerStoreCfg));
         }
         GMP_CUDA(cudaEventRecord(pi.e1, pi.stream));
     }
@@ -384,4 +385,19 @@ extern "C" int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts
         return out->status = GMP_ERR_P2P_MATRIX;
     }
     return out->status = GMP_OK;
+}
+
+extern "C" int gmp_peer_access(int device, int peer, int enable) {
+    clear_error();
+    int prev = -1;
+    (void)cudaGetDevice(&prev);
+    GMP_CUDA(cudaSetDevice(device));
+    cudaError_t e = enable ? cudaDeviceEnablePeerAccess(peer, 0) : cudaDeviceDisablePeerAccess(peer);
+    if (e == cudaErrorPeerAccessAlreadyEnabled || e == cudaErrorPeerAccessNotEnabled) {
+        (void)cudaGetLastError();
+        e = cudaSuccess;
+    }
+    if (prev >= 0) (void)cudaSetDevice(prev);
+    if (e != cudaSuccess) return cuda_fail(e, enable ? "cudaDeviceEnablePeerAccess" : "cudaDeviceDisablePeerAccess");
+    return GMP_OK;
 }

@@ -320,6 +320,10 @@ def probe_p2p(uuids: Sequence[str], *, nbytes: int = 0, iters: int = 0, flags: i
     return r
 
 
+def peer_access(device: int, peer: int, enable: bool = True) -> None:
+    check(lib().gmp_peer_access(device, peer, int(enable)), "gmp_peer_access")
+
+
 def probe_all(expected: Sequence[Device] = (), *, hbm_bytes: int = 0, hbm_iters: int = 0, pattern_mask: int = 0,
               dma_bytes: int = UINT64_MAX, p2p_bytes: int = 0, p2p_iters: int = 0, flags: int = 0, hbm_flags: int = 0,
               p2p_flags: int = 0, dev_dir: Optional[str] = None, raise_on_error: bool = True) -> gmp_report:

@@ -365,6 +365,12 @@ typedef struct gmp_p2p_result {
 
 GMP_API int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts* opts, gmp_p2p_result* out);
 
+/* Maps (enable != 0) or unmaps CUDA device `peer`'s memory into the context of CUDA device `device`, so that
+ * section-3 kernels launched on `device` may be given pointers that live on `peer`.  Already-enabled /
+ * already-disabled is not an error.  For callers that drive the peer kernels themselves; gmp_probe_p2p
+ * does this on its own. */
+GMP_API int gmp_peer_access(int device, int peer, int enable);
+
 /* ------------------------------------------------------------------------- */
 /* 5b. Whole-pod probe and its JSON line                                       */
 /* ------------------------------------------------------------------------- */

@@ -6,12 +6,15 @@
 #include <ctype.h>
 #include <errno.h>
 #include <fcntl.h>
+#include <spawn.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/types.h>
 #include <sys/wait.h>
 #include <unistd.h>
+
+extern char** environ;
 
 /* ---- tiny bounded string builder -------------------------------------------------- */
 typedef struct sb {
@@ -754,27 +757,28 @@ int gmo_remove_result_http(int result, const char* pod_name, const char* node_na
 }
 
 /* ---- fork/exec helpers (os/exec semantics) ---------------------------------------------------------------- */
-/* Runs argv via PATH lookup, captures stdout+stderr together, returns the exit status or -1. */
+/* Runs argv via PATH lookup, captures stdout+stderr together, returns the exit status or -1.
+ * Go's os/exec starts children with clone(CLONE_VFORK|CLONE_VM) (syscall.forkExec), whose cost does not grow with
+ * the parent's address space; posix_spawnp is the same mechanism in C, so the timed baseline is not inflated by the
+ * size of the process that hosts it. */
 static int run_capture(char* const argv[], char* out, size_t out_cap) {
     int pfd[2];
     if (pipe(pfd) != 0) return -1;
-    pid_t pid = fork();
-    if (pid < 0) {
+    posix_spawn_file_actions_t fa;
+    posix_spawn_file_actions_init(&fa);
+    posix_spawn_file_actions_addopen(&fa, 0, "/dev/null", O_RDONLY, 0);
+    posix_spawn_file_actions_adddup2(&fa, pfd[1], 1);
+    posix_spawn_file_actions_adddup2(&fa, pfd[1], 2);
+    posix_spawn_file_actions_addclose(&fa, pfd[0]);
+    posix_spawn_file_actions_addclose(&fa, pfd[1]);
+    pid_t pid = -1;
+    int rc = posix_spawnp(&pid, argv[0], &fa, NULL, argv, environ);
+    posix_spawn_file_actions_destroy(&fa);
+    close(pfd[1]);
+    if (rc != 0) {
         close(pfd[0]);
-        close(pfd[1]);
         return -1;
     }
-    if (pid == 0) {
-        close(pfd[0]);
-        dup2(pfd[1], 1);
-        dup2(pfd[1], 2);
-        close(pfd[1]);
-        int devnull = open("/dev/null", O_RDONLY);
-        if (devnull >= 0) dup2(devnull, 0);
-        execvp(argv[0], argv);
-        _exit(127);
-    }
-    close(pfd[1]);
     size_t len = 0;
     char tmp[512];
     ssize_t r;

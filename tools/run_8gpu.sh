@@ -14,9 +14,9 @@ for row in p.get('read_gbs',[]): print('R',[round(x) for x in row])
 for g in 1 2 4 $N; do
   [ $g -gt $N ] && continue
   if [ $g -eq 1 ]; then
-    python bench.py --steps 20 --warmup 3 --mount-iters 6 2>gpurun_out/scale_${g}.err | tail -1 > gpurun_out/scale_${g}.json
+    python bench.py --steps 10 --warmup 3 --mount-iters 5 2>gpurun_out/scale_${g}.err | tail -1 > gpurun_out/scale_${g}.json
   else
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 2951$g bench.py --gpus $g --steps 20 --warmup 3 --mount-iters 6 2>gpurun_out/scale_${g}.err | tail -1 > gpurun_out/scale_${g}.json
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 2951$g bench.py --gpus $g --steps 10 --warmup 3 --mount-iters 5 2>gpurun_out/scale_${g}.err | tail -1 > gpurun_out/scale_${g}.json
   fi
   python -c "
 import json; d=json.load(open('gpurun_out/scale_${g}.json')); m=d.get('mount',{}); u=m.get('mount_to_usable',{})
