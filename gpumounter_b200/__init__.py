@@ -13,6 +13,8 @@ like the reference's own call sites:
     gpumounter_b200.util       ref: pkg/util/util.go
     gpumounter_b200.allocator  ref: pkg/util/gpu/allocator (selection logic only)
     gpumounter_b200.collector  ref: pkg/util/gpu/collector
+    gpumounter_b200.api        ref: pkg/api/gpu-mount (wire contract, hand-built descriptor)
+    gpumounter_b200.server     ref: pkg/server/gpu-mount + cmd/GPUMounter-worker (handlers over a Cluster interface)
 
 There is no CPU fallback anywhere: importing works without a GPU, but every compute
 entry point raises ``ProbeError(GMP_ERR_UNAVAILABLE)`` on a box with no CUDA driver, and

@@ -1,0 +1,205 @@
+"""The worker's two RPC handlers (ref: pkg/server/gpu-mount/server.go) driven with a fake cluster and a cluster-less
+target, in process and through a real gRPC channel on the reference's method paths.  CPU only."""
+
+import grpc
+import pytest
+
+from gpumounter_b200 import api, device, server
+from gpumounter_b200._model import MountEnv, Pod
+from tests import harness
+from tests.conftest import FAKE_UUIDS
+
+reason = harness.can_run()
+pytestmark = pytest.mark.skipif(reason is not None, reason=reason or "")
+
+
+class FakeCluster(server.Cluster):
+    """Eight GPUs on one node; slave pods take free GPUs, stay Pending for `pending_polls` status reads, are
+    Unschedulable when the node has too few free GPUs."""
+
+    def __init__(self, pods, uuids, pending_polls=2):
+        self.pods = {(p.namespace, p.name): p for p in pods}
+        self.free = list(uuids)
+        self.alloc = {}          # slave pod name -> uuids
+        self.native = {}         # (ns, pod) -> uuids the pod owns natively
+        self.polls = {}
+        self.pending_polls = pending_polls
+        self.deleted = []        # (name, grace)
+        self.unschedulable = set()
+        self.fail_get = False
+        self.linger = {}         # name -> status reads before a deleted pod disappears
+
+    def get_pod(self, namespace, name):
+        if self.fail_get:
+            raise server.ClusterError("apiserver down")
+        try:
+            return self.pods[(namespace, name)]
+        except KeyError:
+            raise server.NotFound(name)
+
+    def create_slave_pod(self, name, owner, gpu_num):
+        assert name.startswith(owner.name + "-slave-pod-") and len(name) == len(owner.name) + len("-slave-pod-") + 6
+        if gpu_num <= len(self.free):
+            self.alloc[name] = [self.free.pop(0) for _ in range(gpu_num)]
+        else:
+            self.unschedulable.add(name)
+        self.polls[name] = 0
+
+    def pod_status(self, namespace, name):
+        assert namespace == "gpu-pool"
+        if name in self.linger:
+            self.linger[name] -= 1
+            if self.linger[name] <= 0:
+                del self.linger[name]
+            return server.PodStatus("Running")
+        if name in self.unschedulable:
+            return server.PodStatus("Pending", "Unschedulable")
+        if name not in self.alloc:
+            raise server.NotFound(name)
+        self.polls[name] += 1
+        if self.polls[name] <= self.pending_polls:
+            return server.PodStatus("Pending", None if self.polls[name] == 1 else "ContainersNotReady")
+        return server.PodStatus("Running")
+
+    def delete_pod(self, namespace, name, grace_period_seconds=None):
+        self.deleted.append((name, grace_period_seconds))
+        self.unschedulable.discard(name)
+        if name in self.alloc:
+            self.free.extend(self.alloc.pop(name))
+            if grace_period_seconds is None:
+                self.linger[name] = 2  # default grace: the pod is still there for a while
+
+    def list_pod_resources(self):
+        out = [(name, "gpu-pool", [("gpu-container", [("nvidia.com/gpu", list(u))])]) for name, u in self.alloc.items()]
+        out += [(pod, ns, [("main", [("nvidia.com/gpu", list(u))])]) for (ns, pod), u in self.native.items()]
+        return out
+
+
+def target_pod():
+    return Pod("gpu-pod", "default", uid=harness.UID, node_name="node-1", container_id="docker://" + harness.CID)
+
+
+@pytest.fixture
+def world(fake_nvml):
+    cfg = fake_nvml()
+    gpus = [device.New(m, u) for u, m, _ in cfg]
+    with harness.Target() as t:
+        cluster = FakeCluster([target_pod()], [u for u, _, _ in cfg])
+        env = MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+        probes = []
+
+        def hook(pod, mounted):
+            probes.append([g.UUID for g in mounted])
+            return 0, {"n_gpus": len(mounted)}
+
+        impl = server.GPUMountImpl(cluster, gpus=gpus, env=env, probe_hook=hook)
+        yield impl, cluster, t, fake_nvml, probes
+
+
+def add(pod="gpu-pod", ns="default", n=1, entire=False):
+    return api.AddGPURequest(pod_name=pod, namespace=ns, gpu_num=n, is_entire_mount=entire)
+
+
+def test_single_mount_then_policy(world):
+    impl, cluster, t, _, probes = world
+    assert impl.AddGPU(add(n=2)).add_gpu_result == api.AddGPUResult_Success
+    assert len(cluster.alloc) == 2 and all(len(u) == 1 for u in cluster.alloc.values())     # one slave pod per GPU
+    assert t.nodes() == ["nvidia2", "nvidia3"]                                               # minors of NVML index 0,1
+    assert probes == [[FAKE_UUIDS[0], FAKE_UUIDS[1]]] and impl.last_probe_report["status"] == 0
+    assert impl.GetMountType(target_pod()) == "single-mount"
+    with pytest.raises(server.RpcError, match="^FailedCreated$"):                            # server.go:57-59
+        impl.AddGPU(add(n=2, entire=True))
+    assert impl.AddGPU(add(n=1)).add_gpu_result == api.AddGPUResult_Success                  # more single mounts are fine
+    assert t.nodes() == ["nvidia1", "nvidia2", "nvidia3"]
+
+
+def test_entire_mount_uses_one_slave_pod_and_blocks_further_mounts(world):
+    impl, cluster, t, _, _ = world
+    assert impl.AddGPU(add(n=4, entire=True)).add_gpu_result == api.AddGPUResult_Success
+    assert [len(u) for u in cluster.alloc.values()] == [4]
+    assert len(t.nodes()) == 4 and impl.GetMountType(target_pod()) == "entire-mount"
+    for entire in (False, True):
+        with pytest.raises(server.RpcError, match="^FailedCreated$"):
+            impl.AddGPU(add(n=1, entire=entire))
+
+
+def test_pod_not_found_insufficient_and_internal_errors(world):
+    impl, cluster, t, _, _ = world
+    assert impl.AddGPU(add(pod="ghost")).add_gpu_result == api.AddGPUResult_PodNotFound
+    assert impl.RemoveGPU(api.RemoveGPURequest(pod_name="ghost", namespace="default")).remove_gpu_result == \
+        api.RemoveGPUResult_PodNotFound
+    assert impl.AddGPU(add(n=9)).add_gpu_result == api.AddGPUResult_InsufficientGPU          # 8 free, 9 asked: ninth pod unschedulable
+    assert sorted(g for _, g in cluster.deleted) == [0] * 9 and not cluster.alloc            # all nine recycled with grace 0
+    assert t.nodes() == [] and len(cluster.free) == 8
+    cluster.fail_get = True
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):
+        impl.AddGPU(add())
+    cluster.fail_get = False
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):                  # Go would divide by zero here
+        impl.AddGPU(add(n=0, entire=True))
+    assert impl.AddGPU(add(n=0)).add_gpu_result == api.AddGPUResult_Success                  # zero single mounts: a no-op success
+
+
+def test_mount_failure_rolls_back_slave_pods_but_not_nodes(world):
+    impl, cluster, t, _, _ = world
+    assert impl.AddGPU(add(n=1)).add_gpu_result == api.AddGPUResult_Success
+    # make the next GPU's node exist already so that its mknod fails
+    import os
+    os.mknod(f"/proc/{t.pid}/root{t.devdir}/nvidia2", 0o020666, os.makedev(195, 2))
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):
+        impl.AddGPU(add(n=1))
+    assert len(cluster.alloc) == 1 and cluster.deleted[-1][1] == 0                           # server.go:86-91
+    assert "nvidia3" in t.nodes()                                                            # earlier mount untouched
+
+
+def remove(uuids, force=False):
+    return api.RemoveGPURequest(pod_name="gpu-pod", namespace="default", uuids=uuids, force=force)
+
+
+def test_remove_paths(world):
+    impl, cluster, t, fake_nvml, _ = world
+    assert impl.AddGPU(add(n=2)).add_gpu_result == api.AddGPUResult_Success
+    assert impl.RemoveGPU(remove(["GPU-unknown"])).remove_gpu_result == api.RemoveGPUResult_GPUNotFound
+    assert impl.RemoveGPU(remove([])).remove_gpu_result == api.RemoveGPUResult_GPUNotFound
+    member = t.spawn_member()
+    fake_nvml(procs=[(FAKE_UUIDS[0], member.pid, 1 << 20, "compute")])
+    assert impl.RemoveGPU(remove([FAKE_UUIDS[0]])).remove_gpu_result == api.RemoveGPUResult_GPUBusy
+    assert t.nodes() == ["nvidia2", "nvidia3"] and len(cluster.alloc) == 2
+    assert impl.RemoveGPU(remove([FAKE_UUIDS[1]])).remove_gpu_result == api.RemoveGPUResult_Success   # the idle one
+    assert t.nodes() == ["nvidia3"] and len(cluster.alloc) == 1
+    assert cluster.deleted[-1][1] is None                                                     # default grace (allocator.go:136)
+    assert impl.RemoveGPU(remove([FAKE_UUIDS[0]], force=True)).remove_gpu_result == api.RemoveGPUResult_Success
+    assert member.wait(timeout=5) == -15 and t.nodes() == [] and not cluster.alloc
+    assert impl.GetMountType(target_pod()) == "no-mount"
+
+
+def test_entire_mount_removal_needs_the_right_count(world):
+    impl, cluster, t, _, _ = world
+    impl.AddGPU(add(n=3, entire=True))
+    assert impl.RemoveGPU(remove([FAKE_UUIDS[0]])).remove_gpu_result == api.RemoveGPUResult_GPUNotFound  # allocator.go:121-123
+    assert impl.RemoveGPU(remove(["x", "y", "z"])).remove_gpu_result == api.RemoveGPUResult_Success      # values irrelevant
+    assert t.nodes() == [] and not cluster.alloc
+
+
+def test_over_the_wire_on_the_reference_method_paths(world):
+    impl, cluster, t, _, _ = world
+    srv = server.serve(impl, "127.0.0.1:0")
+    try:
+        ch = grpc.insecure_channel(f"127.0.0.1:{srv.bound_port}")   # ref: grpc.Dial(workerIP:1200, WithInsecure)
+        add_rpc = ch.unary_unary(api.ADD_GPU_METHOD, request_serializer=lambda m: m.SerializeToString(),
+                                 response_deserializer=api.AddGPUResponse.FromString)
+        rm_rpc = ch.unary_unary(api.REMOVE_GPU_METHOD, request_serializer=lambda m: m.SerializeToString(),
+                                response_deserializer=api.RemoveGPUResponse.FromString)
+        assert add_rpc(add(n=2), timeout=30).add_gpu_result == api.AddGPUResult_Success
+        assert add_rpc(add(pod="ghost"), timeout=30).add_gpu_result == api.AddGPUResult_PodNotFound
+        with pytest.raises(grpc.RpcError) as e:
+            add_rpc(add(n=1, entire=True), timeout=30)
+        assert e.value.code() == grpc.StatusCode.UNKNOWN and e.value.details() == "FailedCreated"
+        assert rm_rpc(remove([FAKE_UUIDS[0], FAKE_UUIDS[1]]), timeout=30).remove_gpu_result == api.RemoveGPUResult_Success
+        assert t.nodes() == []
+        # raw bytes on the wire are what a Go client would send
+        raw = ch.unary_unary(api.ADD_GPU_METHOD)
+        assert raw(b"\x0a\x05ghost\x12\x07default\x18\x01", timeout=30) == b"\x08\x02"
+        ch.close()
+    finally:
+        srv.stop(0)
