@@ -110,6 +110,24 @@ class ClockSampler:
         return out
 
 
+def max_over_ranks(x: float, world: int, device: str = "cuda") -> float:
+    """The slowest rank's time: every multi-GPU number is bracketed by barriers and reduced with MAX, never a wall clock
+    on rank 0 alone.  Works on any backend (NCCL on the box, gloo in the CPU tests)."""
+    if world <= 1:
+        return float(x)
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def whole_job_gbs(step_bytes: int, steps: int, world: int, slowest_seconds: float) -> float:
+    """Weak scaling: every rank moves step_bytes per step on its own GPU; the job is done when the slowest rank is."""
+    return step_bytes * steps * world / slowest_seconds / 1e9
+
+
 def host_cores() -> int:
     try:
         return max(1, len(os.sched_getaffinity(0)))
@@ -287,12 +305,9 @@ def main():
     rb = probe.hbm_read_verify(pb, nbytes, probe.PAT_SPLITMIX, last_seed, s)
     assert r.ok and rb.ok and (r.xor64, r.sum64) == (rb.xor64, rb.sum64), "probe verification failed"
 
-    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    max_ms = float(t.item())
+    max_ms = max_over_ranks(dev_ms, world)
     step_bytes = 4 * nbytes
-    value = step_bytes * K * world / (max_ms * 1e-3) / 1e9
+    value = whole_job_gbs(step_bytes, K, world, max_ms * 1e-3)
 
     k_ms = {"write": [], "verify": [], "copy": []}
     for e in evs:
@@ -327,14 +342,12 @@ def main():
     torch.cuda.synchronize()
     w1 = time.perf_counter()
     barrier()
-    e2e_s = torch.tensor([w1 - w0], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = step_bytes * e2e_steps * world / float(e2e_s.item()) / 1e9
+    e2e_seconds = max_over_ranks(w1 - w0, world)
+    e2e_value = whole_job_gbs(step_bytes, e2e_steps, world, e2e_seconds)
     e2e = {
         "value": e2e_value, "unit": "GB/s",
         "h2d_bytes_per_step": int(last.h2d_bytes), "d2h_bytes_per_step": int(last.d2h_bytes),
-        "ms_per_call": 1e3 * float(e2e_s.item()) / e2e_steps, "calls": e2e_steps,
+        "ms_per_call": 1e3 * e2e_seconds / e2e_steps, "calls": e2e_steps,
         "call": "gmp_probe_hbm(uuid, {bytes, iters=1, dma_bytes}) one-shot, context warm",
         "phases_ms_last_call": {k[3:]: getattr(last, k) / 1e6 for k in
                                 ("ns_select_device", "ns_context", "ns_alloc", "ns_first_kernel", "ns_kernels",
