@@ -33,6 +33,7 @@ GMP_ERR_NODE_UVM = -19
 GMP_ERR_NODE_GPU = -20
 GMP_ERR_NODE_DENIED = -21
 GMP_ERR_DRIVER_LIB = -22
+GMP_ERR_STILL_MOUNTED = -23
 
 
 class ProbeError(RuntimeError):

@@ -150,6 +150,7 @@ extern "C" const char* gmp_strerror(int code) {
         case GMP_ERR_NODE_GPU: return "GPU device node missing";
         case GMP_ERR_NODE_DENIED: return "GPU device node not openable (device cgroup)";
         case GMP_ERR_DRIVER_LIB: return "libcuda.so.1 not found";
+        case GMP_ERR_STILL_MOUNTED: return "device node still present after unmount";
         default: return "unknown error";
     }
 }

@@ -297,6 +297,33 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
     return out->status;
 }
 
+extern "C" int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_dir) {
+    clear_error();
+    if (n < 0 || (n > 0 && gone == nullptr)) {
+        set_error("bad argument");
+        return GMP_ERR_INVALID;
+    }
+    const std::string dir = (dev_dir && dev_dir[0]) ? dev_dir : "/dev";
+    for (int i = 0; i < n; ++i) {
+        if (gone[i].minor == UINT32_MAX) {
+            set_error("%s: minor number not given", gone[i].uuid);
+            return GMP_ERR_INVALID;
+        }
+        const std::string path = dir + "/nvidia" + std::to_string(gone[i].minor);
+        const int fd = open(path.c_str(), O_RDWR | O_CLOEXEC);
+        if (fd >= 0) {
+            close(fd);
+            set_error("%s (%s) still exists and still opens", path.c_str(), gone[i].uuid);
+            return GMP_ERR_STILL_MOUNTED;
+        }
+        if (errno != ENOENT && errno != ENOTDIR) {
+            set_error("%s (%s) still exists (open: %s)", path.c_str(), gone[i].uuid, strerror(errno));
+            return GMP_ERR_STILL_MOUNTED;
+        }
+    }
+    return GMP_OK;
+}
+
 extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
     clear_error();
     if (r == nullptr || buf == nullptr) {

@@ -52,7 +52,8 @@ void add_device(std::vector<gmp_device>* list, const std::string& spec) {
 
 void usage() {
     fprintf(stderr,
-            "usage: gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
+            "usage: gpumounter-probe --gone GPU-...:minor [--gone ...] [--dev-dir DIR]     (after an unmount)\n"
+            "       gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
             "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
             "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only]\n"
             "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n");
@@ -71,7 +72,7 @@ int main(int argc, char** argv) {
     memset(&o, 0, sizeof(o));
     o.hbm.dma_bytes = UINT64_MAX;  // library default
     o.flags |= GMP_PROBE_F_KEEP_DEVICE;  // a process of its own: exit releases everything, no explicit reset needed
-    std::vector<gmp_device> expected;
+    std::vector<gmp_device> expected, gone;
     std::string dev_dir;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -83,6 +84,7 @@ int main(int argc, char** argv) {
             return argv[++i];
         };
         if (a == "--uuid") add_device(&expected, need("--uuid"));
+        else if (a == "--gone") add_device(&gone, need("--gone"));
         else if (a == "--uuids") {
             std::string all = need("--uuids");
             size_t b = 0;
@@ -119,6 +121,17 @@ int main(int argc, char** argv) {
         }
     }
     if (!dev_dir.empty()) o.dev_dir = dev_dir.c_str();
+    if (!gone.empty()) {
+        // RemoveGPU-side mode: only check that the unmounted devices' nodes are gone from this context
+        const int rc = gmp_verify_gone(gone.data(), (int)gone.size(), o.dev_dir);
+        std::string detail = gmp_last_error();
+        for (char& c : detail)
+            if (c == '"' || c == '\\') c = '\'';
+        printf("{\"status\":%d,\"verdict\":\"%s\",\"detail\":\"%s\",\"checked\":%zu}\n", rc, gmp_strerror(rc), detail.c_str(),
+               gone.size());
+        fflush(stdout);
+        return rc == GMP_OK ? 0 : -rc;
+    }
     if ((int)expected.size() > GMP_MAX_DEVICES) {
         fprintf(stderr, "at most %d devices\n", GMP_MAX_DEVICES);
         return 64;

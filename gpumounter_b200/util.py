@@ -79,3 +79,30 @@ def ProbeInPod(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = 
     if raise_on_error:
         check(rc, "ProbeInPod")
     return rc, report
+
+
+def VerifyUnmountedInPod(pod: Pod, gpus: Sequence[NvidiaGPU], env: Optional[MountEnv] = None, dev_dir: Optional[str] = None,
+                         probe_exe: Optional[str] = None, raise_on_error: bool = True):
+    """After UnmountGPU(s): from inside the pod, none of the GPUs' device nodes may exist any more.  No reference
+    counterpart (it returns Success once `rm` exited 0, ref: util.go:131-134).  Returns (status, report dict)."""
+    import json as _json
+
+    from . import probe as _probe
+    from ._model import c_strings
+
+    args = []
+    for g in gpus:
+        args += ["--gone", f"{g.UUID}:{g.MinorNumber}"]
+    if dev_dir:
+        args += ["--dev-dir", dev_dir]
+    exe = probe_exe or _probe.probe_executable()
+    buf = ctypes.create_string_buffer(1 << 16)
+    code = ctypes.c_int(-1)
+    c = pod.to_c()
+    rc = lib().gmp_probe_in_pod(env_ptr(env), ctypes.byref(c), None, 0, exe.encode(), c_strings(args), len(args), buf, 1 << 16,
+                                ctypes.byref(code))
+    text = buf.value.decode(errors="replace")
+    report = _json.loads(text) if text.startswith("{") else {}
+    if raise_on_error:
+        check(rc, "VerifyUnmountedInPod")
+    return rc, report

@@ -72,7 +72,8 @@ enum {
     GMP_ERR_NODE_UVM         = -19, /* /dev/nvidia-uvm missing or not openable */
     GMP_ERR_NODE_GPU         = -20, /* /dev/nvidiaN missing */
     GMP_ERR_NODE_DENIED      = -21, /* /dev/nvidiaN exists but open() is refused (device cgroup) */
-    GMP_ERR_DRIVER_LIB       = -22  /* libcuda.so.1 not resolvable from the probing context */
+    GMP_ERR_DRIVER_LIB       = -22, /* libcuda.so.1 not resolvable from the probing context */
+    GMP_ERR_STILL_MOUNTED    = -23  /* after an unmount: the device node is still there (or still opens) in the pod */
 };
 
 GMP_API int         gmp_abi_version(void);
@@ -421,6 +422,14 @@ typedef struct gmp_report {
 } gmp_report;
 
 GMP_API int gmp_probe_all(const gmp_device* expected, int n_expected, const gmp_probe_opts* opts, gmp_report* out);
+/*
+ * The RemoveGPU-side check (no reference counterpart; the reference returns Success as soon as `rm` exited 0,
+ * ref: pkg/util/util.go:131-134, server.go:155-168): seen from the calling context — run it in the pod, e.g. through
+ * gmp_probe_in_pod with "--gone <uuid>:<minor>" — none of the listed devices' nodes <dev_dir>/nvidia<minor> may exist any
+ * more.  A node that is still present is GMP_ERR_STILL_MOUNTED, whether or not the device cgroup would still let it
+ * open (the detail string says which).  dev_dir NULL = "/dev".
+ */
+GMP_API int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_dir);
 /* One JSON object (single line, no trailing newline) describing the report.  GMP_ERR_BUFFER_TOO_SMALL
  * when cap is not enough (32 KiB always is). */
 GMP_API int gmp_report_json(const gmp_report* report, char* buf, size_t cap);

@@ -246,3 +246,24 @@ def test_probe_in_pod_runs_inside_the_targets_cgroup_and_mount_namespace(fake_nv
         bad.chmod(0o755)
         rc, rep = util.ProbeInPod(product_pod(), gpus, [], env_of(t), probe_exe=str(bad), raise_on_error=False)
         assert rc == _lib.GMP_ERR_VERIFY and rep["status"] == -7
+
+
+def test_unmount_is_verified_from_inside_the_pod(fake_nvml):
+    """RemoveGPU-side check with the real gpumounter-probe binary in --gone mode: runs in the target's device cgroup and
+    mount namespace and must see the nodes gone; a node that survived is GMP_ERR_STILL_MOUNTED."""
+    fake_nvml()
+    with harness.Target() as t:
+        gpus = [device.New(3, FAKE_UUIDS[0]), device.New(2, FAKE_UUIDS[1])]
+        env = env_of(t)
+        util.MountGPUs(product_pod(), gpus, env)
+        rc, rep = util.VerifyUnmountedInPod(product_pod(), gpus, env, dev_dir=t.devdir, raise_on_error=False)
+        assert rc == _lib.GMP_ERR_STILL_MOUNTED and rep["status"] == rc and "nvidia3" in rep["detail"]
+        util.UnmountGPUs(product_pod(), gpus[:1], False, env)
+        rc, rep = util.VerifyUnmountedInPod(product_pod(), gpus, env, dev_dir=t.devdir, raise_on_error=False)
+        assert rc == _lib.GMP_ERR_STILL_MOUNTED and "nvidia2" in rep["detail"]      # the second one is still there
+        assert util.VerifyUnmountedInPod(product_pod(), gpus[:1], env, dev_dir=t.devdir)[0] == 0
+        util.UnmountGPUs(product_pod(), gpus[1:], False, env)
+        rc, rep = util.VerifyUnmountedInPod(product_pod(), gpus, env, dev_dir=t.devdir)
+        assert rc == 0 and rep == {"status": 0, "verdict": "ok", "detail": "", "checked": 2}
+        # the host's view of that directory was empty all along: the check really ran inside the target
+        assert t.host_sees() == []
