@@ -9,7 +9,16 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def torchrun(nproc, script, *args, port=29631, timeout=240):
+def free_port():
+    import socket
+
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        return sk.getsockname()[1]
+
+
+def torchrun(nproc, script, *args, port=None, timeout=240):
+    port = port or free_port()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), script, *args]
     return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
@@ -36,7 +45,7 @@ def test_single_rank_helpers():
 
 def test_reference_arm_under_torchrun_prints_once_from_rank_zero():
     p = torchrun(2, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0",
-                 "--cpu-sample-gib", "1", port=29632)
+                 "--cpu-sample-gib", "1")
     assert p.returncode == 0, p.stderr[-2000:]
     lines = [json.loads(l) for l in p.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
