@@ -511,6 +511,7 @@ extern "C" int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm
     if (!(o.flags & GMP_HBM_F_KEEP_DEVICE)) {
         // leave no context, allocation or mapping behind on the probed device
         (void)cudaDeviceReset();
+        forget_device_state(ordinal);
     }
     if (prev >= 0 && prev != ordinal) (void)cudaSetDevice(prev);
     out->ns_teardown = now_ns() - tt;

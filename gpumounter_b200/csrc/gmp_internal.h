@@ -104,6 +104,9 @@ Tunables& tunables();
 // READ/WRITE/NVLINK/ATOMICS status matrices (n x n each) and active NVLink counts in one NVML session.
 int nvml_p2p_everything(const char* const* uuids, int n, int32_t* caps_out[4], int32_t* nvlink_active);
 
+// Drops per-device state cached across calls (looked-up symbol addresses); call after cudaDeviceReset().
+void forget_device_state(int ordinal);
+
 // ---- misc --------------------------------------------------------------------
 void format_uuid(const unsigned char bytes[16], char out[GMP_UUID_LEN]);
 // GMP_OK and *ordinal, or GMP_ERR_UNAVAILABLE / GMP_ERR_NO_DEVICE.

@@ -362,6 +362,88 @@ __global__ void __launch_bounds__(THREADS, 1024 / THREADS)
     }
 }
 
+// ---- copy through the TMA engine -------------------------------------------------------------
+// cp.async.bulk global -> shared (completion on an mbarrier) and shared -> global (bulk group), driven by ONE
+// thread per CTA: no data ever touches a register, the LSU or the ALU; the bytes in flight per SM are
+// (STAGES-1) x CHUNK of shared memory instead of registers.  SASS: UBLKCP.S.G / UBLKCP.G.S, SYNCS.
+namespace bulk {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void store(void* gdst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+}  // namespace bulk
+
+template <int STAGES, int CHUNK>
+__global__ void __launch_bounds__(32) k_hbm_copy_bulk(unsigned char* __restrict__ dst, const unsigned char* __restrict__ src,
+                                                      uint64_t nchunks) {
+    extern __shared__ __align__(128) unsigned char stage_mem[];
+    __shared__ __align__(8) uint64_t full[STAGES];
+    if (threadIdx.x != 0) return;  // the engine needs one issuing thread; the warp's other lanes leave
+    for (int i = 0; i < STAGES; ++i) bulk::mbar_init(&full[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+
+    const uint64_t first = blockIdx.x, stride = gridDim.x;
+    const uint64_t mine = nchunks > first ? (nchunks - first + stride - 1) / stride : 0;
+    auto gsrc = [&](uint64_t k) { return src + (first + k * stride) * (uint64_t)CHUNK; };
+    auto gdst = [&](uint64_t k) { return dst + (first + k * stride) * (uint64_t)CHUNK; };
+    auto issue_load = [&](uint64_t k) {
+        const int st = (int)(k % STAGES);
+        bulk::mbar_expect_tx(&full[st], CHUNK);
+        bulk::load(stage_mem + (size_t)st * CHUNK, gsrc(k), CHUNK, &full[st]);
+    };
+    const uint64_t prologue = mine < (uint64_t)STAGES ? mine : (uint64_t)STAGES;
+    for (uint64_t k = 0; k < prologue; ++k) issue_load(k);
+    for (uint64_t k = 0; k < mine; ++k) {
+        const int st = (int)(k % STAGES);
+        bulk::mbar_wait(&full[st], (uint32_t)((k / STAGES) & 1));
+        bulk::store(gdst(k), stage_mem + (size_t)st * CHUNK, CHUNK);
+        bulk::commit();
+        // refill the stage of chunk k-1: its store must have finished READING shared memory, which is the case once
+        // at most one bulk group (the store just issued) is still pending
+        if (k >= 1 && k - 1 + STAGES < mine) {
+            bulk::wait_read<1>();
+            issue_load(k - 1 + STAGES);
+        }
+    }
+    bulk::wait_all();  // writes complete before the CTA (and its shared memory) goes away
+}
+
 __global__ void k_hbm_corrupt(unsigned char* p, size_t off, unsigned char mask) { p[off] ^= mask; }
 
 // ---- launch geometry --------------------------------------------------------------
@@ -369,8 +451,8 @@ Tunables& tunables() {
     // Picked by tools/sweep_hbm.py on a B200 (profiles/r01_sweep.md): many small CTAs (several waves, so the
     // hardware balances the ~10% speed spread between SMs) for the store-heavy kernels, exactly one resident
     // wave for the register-accumulating verify kernel.
-    static Tunables t = {/*write_ctas_per_sm*/ 24, /*read*/ 4, /*copy*/ 32,
-                         /*write_variant*/ 12, /*read_variant*/ 10, /*copy_variant*/ 11};
+    static Tunables t = {/*write_ctas_per_sm*/ 24, /*read*/ 4, /*copy*/ 128,
+                         /*write_variant*/ 12, /*read_variant*/ 10, /*copy_variant*/ 21};
     return t;
 }
 
@@ -554,6 +636,54 @@ cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t 
 #undef CALL
 }
 
+constexpr int kBulkVariantFirst = kVariantCount;  // copy variants 16..23
+
+template <int STAGES, int CHUNK>
+static cudaError_t launch_copy_bulk_cfg(unsigned char* dst, const unsigned char* src, size_t bytes, int sm_count, int ctas_per_sm,
+                                        cudaStream_t s) {
+    constexpr int kSmem = STAGES * CHUNK;
+    {
+        // set on every launch: the attribute lives in the context, and callers may have reset the device since the
+        // last call (gmp_probe_hbm does, by default); the call costs about a microsecond
+        cudaError_t e = cudaFuncSetAttribute(k_hbm_copy_bulk<STAGES, CHUNK>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e != cudaSuccess) return e;
+    }
+    const uint64_t nchunks = bytes / CHUNK;
+    if (nchunks > 0) {
+        const int fit = (227 * 1024) / (kSmem + 1024);
+        const int per_sm = ctas_per_sm > 0 ? ctas_per_sm : (fit > 0 ? fit : 1);
+        uint64_t grid = (uint64_t)sm_count * (uint64_t)per_sm;
+        if (grid > nchunks) grid = nchunks;
+        k_hbm_copy_bulk<STAGES, CHUNK><<<(unsigned)grid, 32, kSmem, s>>>(dst, src, nchunks);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    const size_t done = (size_t)nchunks * CHUNK;
+    if (done < bytes) {
+        const LaunchCfg rest = {kFallbackVariant, 0};
+        return launch_copy(dst + done, src + done, bytes - done, s, &rest);
+    }
+    return cudaSuccess;
+}
+
+static cudaError_t launch_copy_bulk(int variant, void* dst, const void* src, size_t bytes, int sm_count, int ctas_per_sm,
+                                    cudaStream_t s) {
+    if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15u) != 0) return cudaErrorNotSupported;
+    unsigned char* d = static_cast<unsigned char*>(dst);
+    const unsigned char* c = static_cast<const unsigned char*>(src);
+    switch (variant - kBulkVariantFirst) {
+        case 0: return launch_copy_bulk_cfg<6, 16384>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 1: return launch_copy_bulk_cfg<3, 32768>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 2: return launch_copy_bulk_cfg<12, 8192>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 3: return launch_copy_bulk_cfg<3, 65536>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 4: return launch_copy_bulk_cfg<2, 98304>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 5: return launch_copy_bulk_cfg<2, 114688>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 6: return launch_copy_bulk_cfg<4, 49152>(d, c, bytes, sm_count, ctas_per_sm, s);
+        case 7: return launch_copy_bulk_cfg<7, 32768>(d, c, bytes, sm_count, ctas_per_sm, s);
+        default: return cudaErrorNotSupported;
+    }
+}
+
 cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s, const LaunchCfg* cfg) {
     if (bytes == 0) return cudaSuccess;
     DeviceInfo di;
@@ -565,6 +695,12 @@ cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s
     if (cfg) {
         tn.copy_variant = cfg->variant;
         tn.copy_ctas_per_sm = cfg->ctas_per_sm;
+    }
+    if (tn.copy_variant >= kVariantCount) {
+        // TMA-bulk variants: whole chunks through the copy engine, the remainder through the vector kernel
+        cudaError_t be = launch_copy_bulk(tn.copy_variant, dst, src, bytes, di.sm_count, tn.copy_ctas_per_sm, s);
+        if (be != cudaErrorNotSupported) return be;
+        tn.copy_variant = kFallbackVariant;
     }
     switch (pick_variant(tn.copy_variant, dst, src)) {
 #define X(ID, T, U, V, H)                                                                          \
@@ -704,14 +840,14 @@ extern "C" int gmp_tune(const char* knob, int value) {
     if (knob == nullptr) return GMP_ERR_INVALID;
     Tunables& t = tunables();
     int* slot = nullptr;
-    int limit = 64;
+    int limit = 256;
     const std::string_view k(knob);
     if (k == "write_ctas_per_sm") slot = &t.write_ctas_per_sm;
     else if (k == "read_ctas_per_sm") slot = &t.read_ctas_per_sm;
     else if (k == "copy_ctas_per_sm") slot = &t.copy_ctas_per_sm;
     else if (k == "write_variant") { slot = &t.write_variant; limit = kVariantCount - 1; }
     else if (k == "read_variant") { slot = &t.read_variant; limit = kVariantCount - 1; }
-    else if (k == "copy_variant") { slot = &t.copy_variant; limit = kVariantCount - 1; }
+    else if (k == "copy_variant") { slot = &t.copy_variant; limit = kVariantCount + 8 - 1; }
     if (slot == nullptr) {
         set_error("unknown knob '%s'", knob);
         return GMP_ERR_INVALID;
@@ -855,8 +991,15 @@ __global__ void __launch_bounds__(256) k_noalloc_fold(unsigned long long* __rest
 }
 
 // Device address of g_noalloc_scratch on the CURRENT device, looked up once per device.
+static std::atomic<unsigned long long*> g_noalloc_scratch_addr[64];
+
+// A cudaDeviceReset() destroys the context the address was looked up in; the library's own resets call this.
+void forget_device_state(int ordinal) {
+    if (ordinal >= 0 && ordinal < 64) g_noalloc_scratch_addr[ordinal].store(nullptr, std::memory_order_release);
+}
+
 static cudaError_t noalloc_scratch_on_current_device(unsigned long long** out) {
-    static std::atomic<unsigned long long*> cache[64];
+    std::atomic<unsigned long long*>* cache = g_noalloc_scratch_addr;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;

@@ -44,7 +44,10 @@ struct Session {
             if (p.e1) cudaEventDestroy(p.e1);
             if (p.stream) cudaStreamDestroy(p.stream);
             p = PeerGpu{p.ordinal};
-            if (!keep) (void)cudaDeviceReset();
+            if (!keep) {
+                (void)cudaDeviceReset();
+                forget_device_state(p.ordinal);
+            }
         }
         (void)cudaGetLastError();
         if (prev_device >= 0) (void)cudaSetDevice(prev_device);

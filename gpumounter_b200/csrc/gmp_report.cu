@@ -288,7 +288,10 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
         (void)cudaGetDevice(&prev);
         for (int i = 0; i < n; ++i) {
             if (out->devices[i].cuda_ordinal < 0) continue;
-            if (cudaSetDevice(out->devices[i].cuda_ordinal) == cudaSuccess) (void)cudaDeviceReset();
+            if (cudaSetDevice(out->devices[i].cuda_ordinal) == cudaSuccess) {
+                (void)cudaDeviceReset();
+                forget_device_state(out->devices[i].cuda_ordinal);
+            }
         }
         if (prev >= 0) (void)cudaSetDevice(prev);
         (void)cudaGetLastError();

@@ -223,7 +223,10 @@ GMP_API int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, void
  *     call clears the part that has to start at zero).  Two calls whose GPU work overlaps — different
  *     streams, different threads — race on it and return garbage: serialise them per device;
  *   - the first call on each device looks up the array's device address; make that first call before
- *     starting any stream capture.
+ *     starting any stream capture.  The address belongs to the device's current context: the
+ *     library forgets it when one of its own calls resets the device (gmp_probe_hbm without
+ *     GMP_HBM_F_KEEP_DEVICE, gmp_probe_p2p, gmp_probe_all), but it cannot see a cudaDeviceReset()
+ *     made by the caller — after one of those, do not call this entry point again in the process.
  */
 #define GMP_NOALLOC_MAX_BYTES (8ull << 30)
 GMP_API int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int pattern, uint64_t seed,

@@ -114,7 +114,7 @@ def test_every_launch_variant_is_bit_exact(cuda, knob):
     want = gmo.pattern_checksum(nbytes, probe.PAT_SPLITMIX, 123)
     keep_v, keep_c = probe.tune(f"{knob}_variant"), probe.tune(f"{knob}_ctas_per_sm")
     try:
-        for variant in range(16):
+        for variant in range(24 if knob == "copy" else 16):
             for ctas in (0, 1, 5):
                 probe.tune(f"{knob}_variant", variant)
                 probe.tune(f"{knob}_ctas_per_sm", ctas)

@@ -83,3 +83,32 @@ def test_the_largest_allowed_size(cuda):
     probe.hbm_corrupt(t.data_ptr(), n, n - 7, 0x80, s)
     assert as_tuple(probe.hbm_read_verify_noalloc(t.data_ptr(), n, probe.PAT_SPLITMIX, SEED + 9, s)) == as_tuple(
         probe.hbm_read_verify(t.data_ptr(), n, probe.PAT_SPLITMIX, SEED + 9, s))
+
+
+def test_survives_a_device_reset_done_by_the_library():
+    """gmp_probe_hbm (default flags) ends in cudaDeviceReset; the scratch address looked up before it is then stale and
+    the library has to look it up again.  Run in a child so this process's torch context is not torn down."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from gpumounter_b200 import probe\n"
+        "from cuda.bindings import runtime as rt   # plain device memory without torch: a reset would orphan torch's pool\n"
+        "def check(nbytes, seed):\n"
+        "    err, p = rt.cudaMalloc(nbytes); assert int(err) == 0, err\n"
+        "    p = int(p)\n"
+        "    probe.hbm_write_pattern(p, nbytes, 0, seed)\n"
+        "    a = probe.hbm_read_verify(p, nbytes, 0, seed); b = probe.hbm_read_verify_noalloc(p, nbytes, 0, seed)\n"
+        "    assert (a.mismatch_lanes, a.xor64, a.sum64) == (b.mismatch_lanes, b.xor64, b.sum64) == (0, a.xor64, a.sum64)\n"
+        "    assert int(rt.cudaFree(p)[0]) == 0\n"
+        "check((9 << 20) + 5, 1)\n"
+        "r = probe.probe_hbm(nbytes=64 << 20, iters=1, dma_bytes=0)   # resets the device at the end\n"
+        "assert r.status == 0\n"
+        "check((9 << 20) + 5, 2)\n"
+        "print('ok')\n" % root
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stdout[-1000:] + out.stderr[-2000:]

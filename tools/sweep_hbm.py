@@ -44,6 +44,7 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--out", default="gpurun_out/sweep.json")
     ap.add_argument("--kernels", default="write,read,copy")
+    ap.add_argument("--variants", default="", help="comma list; default all")
     ap.add_argument("--ctas", default="0,1,2,4,6,8,12,16,24,32")
     args = ap.parse_args()
     n = int(args.gib * (1 << 30))
@@ -60,13 +61,18 @@ def main():
     }
     probe.hbm_write_pattern(a.data_ptr(), n, 0, 1, s)
     kinds = {k: v for k, v in kinds.items() if k in args.kernels.split(",")}
+    bulk = {16: "TMA bulk 6x16K", 17: "TMA bulk 3x32K", 18: "TMA bulk 12x8K", 19: "TMA bulk 3x64K", 20: "TMA bulk 2x96K",
+            21: "TMA bulk 2x112K", 22: "TMA bulk 4x48K", 23: "TMA bulk 7x32K"}
     for kind, (fn, nbytes) in kinds.items():
-        for v in VARIANTS:
+        variants = {**VARIANTS, **bulk} if kind == "copy" else VARIANTS
+        if args.variants:
+            variants = {v: variants[v] for v in variants if str(v) in args.variants.split(",")}
+        for v in variants:
             for c in ctas_list:
                 probe.tune(f"{kind}_variant", v)
                 probe.tune(f"{kind}_ctas_per_sm", c)
                 best, avg = timeit(fn, args.iters)
-                row = {"kernel": kind, "variant": v, "desc": VARIANTS[v], "ctas_per_sm": c,
+                row = {"kernel": kind, "variant": v, "desc": variants[v], "ctas_per_sm": c,
                        "best_gbs": nbytes / best / 1e6, "avg_gbs": nbytes / avg / 1e6}
                 rows.append(row)
                 print(json.dumps(row), flush=True)
