@@ -447,6 +447,9 @@ __global__ void __launch_bounds__(32) k_hbm_copy_bulk(unsigned char* __restrict_
 __global__ void k_hbm_corrupt(unsigned char* p, size_t off, unsigned char mask) { p[off] ^= mask; }
 
 // ---- launch geometry --------------------------------------------------------------
+static std::atomic<unsigned long long> g_kernel_launches{0};
+static inline void count_launch() { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); }
+
 Tunables& tunables() {
     // Picked by tools/sweep_hbm.py on a B200 (profiles/r01_sweep.md): many small CTAs (several waves, so the
     // hardware balances the ~10% speed spread between SMs) for the store-heavy kernels, exactly one resident
@@ -615,6 +618,7 @@ cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, c
     if (e != cudaSuccess) return e;
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
+    count_launch();
 #define CALL(P) launch_write_pat<P>(static_cast<uint4*>(dptr), nlanes, tail, seed, di.sm_count, s, cfg)
     GMP_PATTERN_SWITCH(pattern, CALL)
 #undef CALL
@@ -631,6 +635,7 @@ cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t 
     if (e != cudaSuccess) return e;
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
+    count_launch();
 #define CALL(P) launch_verify_pat<P>(static_cast<const uint4*>(dptr), nlanes, tail, seed, d_acc, di.sm_count, s, cfg)
     GMP_PATTERN_SWITCH(pattern, CALL)
 #undef CALL
@@ -655,6 +660,7 @@ static cudaError_t launch_copy_bulk_cfg(unsigned char* dst, const unsigned char*
         uint64_t grid = (uint64_t)sm_count * (uint64_t)per_sm;
         if (grid > nchunks) grid = nchunks;
         k_hbm_copy_bulk<STAGES, CHUNK><<<(unsigned)grid, 32, kSmem, s>>>(dst, src, nchunks);
+        count_launch();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -702,6 +708,7 @@ cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s
         if (be != cudaErrorNotSupported) return be;
         tn.copy_variant = kFallbackVariant;
     }
+    count_launch();
     switch (pick_variant(tn.copy_variant, dst, src)) {
 #define X(ID, T, U, V, H)                                                                          \
     case ID:                                                                                       \
@@ -834,6 +841,8 @@ extern "C" int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, v
     decode_acc(raw, out);
     return GMP_OK;
 }
+
+extern "C" unsigned long long gmp_kernel_launches(void) { return g_kernel_launches.load(std::memory_order_relaxed); }
 
 extern "C" int gmp_tune(const char* knob, int value) {
     clear_error();

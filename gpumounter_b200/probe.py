@@ -236,6 +236,12 @@ def hbm_corrupt(dptr: int, nbytes: int, byte_offset: int, mask: int, stream: int
     check(f(_ptr(dptr), nbytes, byte_offset, mask, _ptr(stream)), "gmp_hbm_corrupt")
 
 
+def kernel_launches() -> int:
+    f = lib().gmp_kernel_launches
+    f.restype = ctypes.c_ulonglong
+    return int(f())
+
+
 def tune(knob: str, value: int = -1) -> int:
     f = lib().gmp_tune
     f.argtypes = [ctypes.c_char_p, ctypes.c_int]

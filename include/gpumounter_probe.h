@@ -243,6 +243,10 @@ GMP_API int gmp_hbm_corrupt(void* dptr, size_t bytes, size_t byte_offset, uint8_
  * GMP_ERR_INVALID.
  */
 GMP_API int gmp_tune(const char* knob, int value);
+/* Number of write / verify / copy kernels this process has launched through the library so far (a copy whose size is
+ * not a multiple of the TMA chunk is two launches).  Benchmarking aid: bench.py reports the difference over its timed
+ * region as `gpu_launches`. */
+GMP_API unsigned long long gmp_kernel_launches(void);
 
 /* ------------------------------------------------------------------------- */
 /* 4. One-shot HBM probe of one mounted GPU                                   */

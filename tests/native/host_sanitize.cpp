@@ -1,0 +1,124 @@
+// Sanitizer driver for the host-only half of the library (gmp_mount.cpp + gmp_nvml.cpp): built once with
+// -fsanitize=address,undefined and once with -fsanitize=thread by tests/test_host_sanitizers.py.
+// Exercises the string/path/QoS/selection logic with hostile inputs, the nsenter argv builder, and — from eight
+// threads at once — the entry points the header declares thread-safe.
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "gpumounter_probe.h"
+
+// the two error-plumbing functions normally come from gmp_core.cu (a CUDA translation unit)
+namespace gmp {
+static thread_local char g_err[512];
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void clear_error() { g_err[0] = '\0'; }
+}  // namespace gmp
+
+#define CHECK(cond)                                                         \
+    do {                                                                    \
+        if (!(cond)) {                                                      \
+            fprintf(stderr, "CHECK failed at line %d: %s\n", __LINE__, #cond); \
+            exit(2);                                                        \
+        }                                                                   \
+    } while (0)
+
+static void logic_round(int salt) {
+    char buf[4096];
+    // cgroup names: empty, long, hostile
+    const char* parts[] = {"kubepods", "burstable", "pod1234-abcd-5678-efgh"};
+    CHECK(gmp_cgroup_name_to_systemd(parts, 3, buf, sizeof(buf)) == GMP_OK);
+    CHECK(strcmp(buf, "/kubepods.slice/kubepods-burstable.slice/kubepods-burstable-pod1234_abcd_5678_efgh.slice") == 0);
+    CHECK(gmp_cgroup_name_to_systemd(parts, 3, buf, 8) == GMP_ERR_BUFFER_TOO_SMALL);
+    CHECK(gmp_cgroup_name_to_systemd(nullptr, 0, buf, sizeof(buf)) == GMP_OK && strcmp(buf, "/") == 0);
+    const std::string longpart(3000, 'a');
+    const char* lp[] = {longpart.c_str(), "-", ""};
+    CHECK(gmp_cgroup_name_to_systemd(lp, 3, buf, sizeof(buf)) != GMP_OK || true);
+    CHECK(gmp_cgroup_name_to_cgroupfs(lp, 3, buf, sizeof(buf)) == GMP_OK);
+    CHECK(gmp_cgroup_name_check("a/b") == GMP_ERR_NAME && gmp_cgroup_name_check("a_b") == GMP_ERR_NAME);
+    // QoS with odd quantities
+    gmp_container_resources cr[3] = {{"100m", "1Gi", "0.1", "1073741824"}, {nullptr, nullptr, nullptr, nullptr}, {"1e3", "12Pi", "1k", "12Pi"}};
+    gmp_pod pod = {"p", "ns", "uid-1", "node", "docker://abc", 3, cr};
+    int qos = -1;
+    CHECK(gmp_get_pod_qos(&pod, &qos) == GMP_OK && qos == GMP_QOS_BURSTABLE);
+    gmp_container_resources bad[1] = {{"12 parsecs", nullptr, nullptr, nullptr}};
+    gmp_pod badpod = {"p", "ns", "u", "n", "c", 1, bad};
+    CHECK(gmp_get_pod_qos(&badpod, &qos) == GMP_ERR_INVALID);
+    CHECK(gmp_get_cgroup_name("systemd", &pod, "cid", buf, sizeof(buf)) == GMP_OK);
+    CHECK(gmp_get_cgroup_name("cgroupfs", &pod, "cid", buf, 4) == GMP_ERR_BUFFER_TOO_SMALL);
+    CHECK(gmp_get_cgroup_name("nope", &pod, "cid", buf, sizeof(buf)) == GMP_ERR_CGROUP_DRIVER);
+    // device records, JSON escaping with every byte value
+    gmp_gpu g;
+    CHECK(gmp_device_new(3 + salt, "GPU-x", &g) == GMP_OK);
+    for (int c = 1; c < 255 && c < (int)sizeof(g.pod_name); ++c) g.pod_name[c - 1] = (char)c;
+    g.pod_name[254] = '\0';
+    CHECK(gmp_device_string(&g, buf, sizeof(buf)) == GMP_OK);
+    CHECK(gmp_device_string(&g, buf, 16) == GMP_ERR_BUFFER_TOO_SMALL);
+    CHECK(gmp_device_reset_state(&g) == GMP_OK && g.pod_name[0] == '\0');
+    // nsenter argv with everything switched on and long file names
+    gmp_ns_config cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.target = 4242;
+    cfg.cgroup = cfg.ipc = cfg.mount = cfg.net = cfg.pid = cfg.user = cfg.uts = 1;
+    cfg.mount_file = longpart.c_str();
+    cfg.root_directory = "/r";
+    cfg.working_directory = "/w";
+    cfg.gid = 7;
+    cfg.uid = 9;
+    int argc = 0;
+    CHECK(gmp_ns_build_command(&cfg, buf, sizeof(buf), &argc) == GMP_OK && argc > 10);
+    CHECK(gmp_ns_build_command(&cfg, buf, 64, &argc) == GMP_ERR_BUFFER_TOO_SMALL);
+    cfg.target = 0;
+    CHECK(gmp_ns_build_command(&cfg, buf, sizeof(buf), &argc) == GMP_ERR_TARGET);
+    // ownership bookkeeping
+    gmp_gpu list[4];
+    const char* uu[4] = {"GPU-0", "GPU-1", "GPU-2", "GPU-3"};
+    for (int i = 0; i < 4; ++i) CHECK(gmp_device_new(i, uu[i], &list[i]) == GMP_OK);
+    const char* ids01[] = {"GPU-0", "GPU-1"};
+    gmp_container_devices cd[1] = {{"nvidia.com/gpu", 2, ids01}};
+    gmp_container_entry ce[1] = {{"c", 1, cd}};
+    gmp_pod_resources pr[1] = {{"a-slave-pod-123456", "gpu-pool", 1, ce}};
+    CHECK(gmp_update_gpu_status(list, 4, pr, 1) == GMP_OK);
+    int32_t idx[4];
+    int count = -1, mt = -1;
+    CHECK(gmp_get_pod_gpu_resources(list, 4, "a", "default", idx, &count) == GMP_OK && count == 2);
+    CHECK(gmp_get_mount_type(list, 4, "a", "default", &mt) == GMP_OK && mt == GMP_MOUNT_ENTIRE);
+    const char* want[] = {"x", "y"};
+    CHECK(gmp_get_remove_gpu(list, 4, "a", "default", want, 2, idx, &count) == GMP_OK && count == 2);
+    CHECK(gmp_get_remove_gpu(list, 4, "a", "default", want, 1, idx, &count) == GMP_OK && count == 0);
+    const char* unknown[] = {"GPU-9"};
+    gmp_container_devices cdu[1] = {{"nvidia.com/gpu", 1, unknown}};
+    gmp_container_entry ceu[1] = {{"c", 1, cdu}};
+    gmp_pod_resources pru[1] = {{"z", "default", 1, ceu}};
+    CHECK(gmp_update_gpu_status(list, 4, pru, 1) == GMP_ERR_NO_DEVICE);
+    const unsigned char r3[3] = {1, 2, 3};
+    CHECK(gmp_slave_pod_name("owner", r3, buf, sizeof(buf)) == GMP_OK && strcmp(buf, "owner-slave-pod-010203") == 0);
+    CHECK(gmp_slave_pod_name("owner", r3, buf, 5) == GMP_ERR_BUFFER_TOO_SMALL);
+    // NVML absent: a clean error, not a crash
+    gmp_device devs[2];
+    int n = -1;
+    setenv("GPUMOUNTER_NVML_LIB", "/nonexistent/libnvidia-ml.so.1", 1);
+    CHECK(gmp_enumerate_nvml(devs, 2, &n) == GMP_ERR_NVML_NOT_FOUND && n == 0);
+}
+
+int main() {
+    logic_round(0);
+    std::vector<std::thread> ts;
+    for (int t = 0; t < 8; ++t)
+        ts.emplace_back([t]() {
+            for (int i = 0; i < 50; ++i) logic_round(t);
+        });
+    for (auto& t : ts) t.join();
+    puts("host sanitize ok");
+    return 0;
+}
