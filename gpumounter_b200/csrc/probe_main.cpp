@@ -56,7 +56,8 @@ void usage() {
             "       gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
             "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
             "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only]\n"
-            "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n");
+            "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n"
+            "Defaults may come from GPUMOUNTER_PROBE_BYTES / _ITERS / _PATTERNS / _SEED / _DMA_BYTES / _P2P_BYTES / _SKIP_P2P.\n");
 }
 
 }  // namespace
@@ -74,6 +75,17 @@ int main(int argc, char** argv) {
     o.flags |= GMP_PROBE_F_KEEP_DEVICE;  // a process of its own: exit releases everything, no explicit reset needed
     std::vector<gmp_device> expected, gone;
     std::string dev_dir;
+    // environment defaults (the worker's DaemonSet can set them once; command-line flags win)
+    if (const char* v = getenv("GPUMOUNTER_PROBE_BYTES")) o.hbm.bytes = parse_size(v);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_ITERS")) o.hbm.iters = (uint32_t)atoi(v);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_PATTERNS"))
+        o.hbm.pattern_mask = strcmp(v, "all") == 0 ? (1u << GMP_PAT_COUNT) - 1 : (uint32_t)strtoul(v, nullptr, 0);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_SEED")) o.hbm.seed = strtoull(v, nullptr, 0);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_DMA_BYTES")) o.hbm.dma_bytes = parse_size(v);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_P2P_BYTES")) o.p2p.bytes = parse_size(v);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_SKIP_P2P")) {
+        if (atoi(v) != 0) o.flags |= GMP_PROBE_F_SKIP_P2P;
+    }
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto need = [&](const char* what) -> const char* {

@@ -168,3 +168,36 @@ def test_probe_executable_on_the_box():
     j = json.loads(p.stdout.strip().splitlines()[-1])
     assert j["status"] == 0 and j["verdict"] == "ok" and j["n_gpus"] >= 1
     assert j["ms_total"] < 20000
+
+
+def test_p2p_matrix_mismatch_against_nvml_is_reported(cuda, tmp_path, monkeypatch):
+    """Fault injection: a fake NVML that lists the REAL devices but claims READ is not supported from GPU 0 to GPU 1,
+    while CUDA says the pair is accessible -> GMP_ERR_P2P_MATRIX (bandwidth still measured and verified)."""
+    devs = probe.enumerate_cuda()
+    if len(devs) < 2:
+        pytest.skip("needs at least 2 GPUs")
+    real = {d.uuid: d for d in probe.enumerate_nvml()}
+    fake = os.path.join(ROOT, "tests", "fake_nvml", "libfake_nvml.so")
+    if not os.path.exists(fake):
+        subprocess.run(["make", "-s", "-C", os.path.dirname(fake)], check=True)
+    cfg = tmp_path / "nvml.cfg"
+    lines = [f"gpu {d.uuid} {real[d.uuid].minor} {d.pci_bus_id}" for d in devs[:2]]
+    lines += ["p2p 0 1 0 5", f"nvlink {devs[0].uuid} 18", f"nvlink {devs[1].uuid} 18"]   # READ 0->1: NOT_SUPPORTED
+    cfg.write_text("\n".join(lines) + "\n")
+    monkeypatch.setenv("GPUMOUNTER_NVML_LIB", fake)
+    monkeypatch.setenv("GMP_FAKE_NVML_CONFIG", str(cfg))
+    r = probe.probe_p2p([d.uuid for d in devs[:2]], nbytes=64 << 20, iters=1, flags=probe.P2P_F_KEEP_DEVICE,
+                        raise_on_error=False)
+    assert r.status == _lib.GMP_ERR_P2P_MATRIX and r.matrix_match == 0 and r.nvml_available == 1
+    assert r.matrix("nvml_read") == [[0, 5], [0, 0]] and r.matrix("can_access") == [[1, 1], [1, 1]]
+    assert r.mismatch_lanes == 0 and r.matrix("write_gbs")[0][1] > 100
+
+
+def test_probe_executable_reads_environment_defaults():
+    exe = probe.probe_executable()
+    env = dict(os.environ, GPUMOUNTER_PROBE_BYTES="64M", GPUMOUNTER_PROBE_ITERS="1", GPUMOUNTER_PROBE_DMA_BYTES="0",
+               GPUMOUNTER_PROBE_SKIP_P2P="1", GPUMOUNTER_PROBE_PATTERNS="all")
+    p = subprocess.run([exe], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stdout[-1000:] + p.stderr[-1000:]
+    j = json.loads(p.stdout.strip().splitlines()[-1])
+    assert j["status"] == 0 and all(h["bytes"] == 64 << 20 and h["h2d_gbs"] == 0 for h in j["hbm"]) and "p2p" not in j
