@@ -256,10 +256,7 @@ def main():
     stream = torch.cuda.current_stream()
     s = stream.cuda_stream
     pa, pb, pacc = a.data_ptr(), b.data_ptr(), acc.data_ptr()
-    launches = 0
-
     def step(i, ev=None):
-        nonlocal launches
         seed = SEED + i
         if ev:
             ev[0].record(stream)
@@ -272,7 +269,6 @@ def main():
         probe.hbm_copy(pb, pa, nbytes, s)
         if ev:
             ev[3].record(stream)
-        launches += 3
 
     for i in range(args.warmup):
         step(i)
