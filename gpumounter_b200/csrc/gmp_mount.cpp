@@ -117,7 +117,9 @@ bool parse_quantity(const char* text, i128* nano) {
         if (j >= suffix.size()) return false;
         for (size_t k = j; k < suffix.size(); ++k)
             if (!isdigit((unsigned char)suffix[k])) return false;
-        const long e = strtol(suffix.c_str() + 1, nullptr, 10);
+        long e = 0;
+        for (size_t k = j; k < suffix.size() && e <= 1000; ++k) e = e * 10 + (suffix[k] - '0');
+        if (suffix[1] == '-') e = -e;
         if (e > 30 || e < -30) return false;
         pow10 += (int)e;
     }
@@ -501,9 +503,13 @@ bool go_atoi(const std::string& s, int* out) {  // strconv.Atoi: sign + digits, 
     if (i >= s.size()) return false;
     for (size_t k = i; k < s.size(); ++k)
         if (!isdigit((unsigned char)s[k])) return false;
-    errno = 0;
-    const long v = strtol(s.c_str(), nullptr, 10);
-    if (errno != 0 || v > INT32_MAX || v < INT32_MIN) return false;
+    long long v = 0;
+    for (size_t k = i; k < s.size(); ++k) {
+        v = v * 10 + (s[k] - '0');
+        if (v > (long long)INT32_MAX + 1) return false;  // strconv.Atoi: value out of range
+    }
+    if (s[0] == '-') v = -v;
+    if (v > INT32_MAX || v < INT32_MIN) return false;
     *out = (int)v;
     return true;
 }

@@ -18,22 +18,104 @@
 
 #include "gpumounter_probe.h"
 
+// ---- keeping the glibc floor low ----------------------------------------------------------------------
+// The binary is fexecve'd inside arbitrary pods, so it must start against THEIR libc.  Built here against glibc 2.39
+// it would otherwise ask for GLIBC_2.38 (strtoul & co. are redirected to __isoc23_* by the headers), GLIBC_2.36
+// (arc4random, referenced by the static libstdc++'s std::random_device) and GLIBC_2.35 (_dl_find_object, used by the
+// static libgcc unwinder as a fast path).  Own parsers and two local definitions bring the requirement down to
+// GLIBC_2.34 (the release that merged libpthread/libdl into libc: unavoidable without an older sysroot).
+extern "C" {
+unsigned int arc4random(void) {  // never reached by this program (no std::random_device); must merely resolve locally
+    unsigned int v = 0x9E3779B9u;
+    FILE* f = fopen("/dev/urandom", "rb");
+    if (f) {
+        if (fread(&v, sizeof(v), 1, f) != 1) v ^= 0x85EBCA6Bu;
+        fclose(f);
+    }
+    return v;
+}
+int _dl_find_object(void*, void*) { return -1; }  // "not found": the unwinder falls back to dl_iterate_phdr
+// the static libstdc++ (eh_alloc.o, parsing GLIBCXX_TUNABLES) was itself compiled against the C23 redirect
+unsigned long __isoc23_strtoul(const char* s, char** end, int base) {
+    while (*s == ' ' || *s == '\t') ++s;
+    if (*s == '+') ++s;
+    if ((base == 0 || base == 16) && s[0] == '0' && (s[1] == 'x' || s[1] == 'X')) {
+        s += 2;
+        base = 16;
+    } else if (base == 0) {
+        base = s[0] == '0' ? 8 : 10;
+    }
+    unsigned long v = 0;
+    for (;; ++s) {
+        int d;
+        if (*s >= '0' && *s <= '9') d = *s - '0';
+        else if (*s >= 'a' && *s <= 'z') d = *s - 'a' + 10;
+        else if (*s >= 'A' && *s <= 'Z') d = *s - 'A' + 10;
+        else break;
+        if (d >= base) break;
+        v = v * (unsigned long)base + (unsigned long)d;
+    }
+    if (end) *end = const_cast<char*>(s);
+    return v;
+}
+}
+
 namespace {
 
+// unsigned integer in decimal, 0x-hex or 0-octal; *end receives the first unparsed character
+unsigned long long parse_u64(const char* s, const char** end) {
+    unsigned long long v = 0;
+    int base = 10;
+    if (s[0] == '0' && (s[1] == 'x' || s[1] == 'X')) {
+        base = 16;
+        s += 2;
+    } else if (s[0] == '0' && s[1] >= '0' && s[1] <= '7') {
+        base = 8;
+        s += 1;
+    }
+    for (;; ++s) {
+        int d;
+        if (*s >= '0' && *s <= '9') d = *s - '0';
+        else if (base == 16 && *s >= 'a' && *s <= 'f') d = *s - 'a' + 10;
+        else if (base == 16 && *s >= 'A' && *s <= 'F') d = *s - 'A' + 10;
+        else break;
+        if (d >= base) break;
+        v = v * (unsigned)base + (unsigned)d;
+    }
+    if (end) *end = s;
+    return v;
+}
+
+// "<number>[.<fraction>][K|M|G]"
 unsigned long long parse_size(const char* s) {
-    char* end = nullptr;
-    double v = strtod(s, &end);
+    const char* end = nullptr;
+    const unsigned long long whole = parse_u64(s, &end);
+    double v = (double)whole;
+    if (end == s) {
+        fprintf(stderr, "bad size '%s'\n", s);
+        exit(64);
+    }
+    if (*end == '.') {
+        double scale = 0.1;
+        for (++end; *end >= '0' && *end <= '9'; ++end, scale *= 0.1) v += (*end - '0') * scale;
+    }
     unsigned long long mult = 1;
-    if (end && *end) {
+    if (*end) {
         switch (*end) {
             case 'k': case 'K': mult = 1ull << 10; break;
             case 'm': case 'M': mult = 1ull << 20; break;
             case 'g': case 'G': mult = 1ull << 30; break;
             default: fprintf(stderr, "bad size '%s'\n", s); exit(64);
         }
+        if (end[1] != '\0') {
+            fprintf(stderr, "bad size '%s'\n", s);
+            exit(64);
+        }
     }
     return (unsigned long long)(v * (double)mult);
 }
+
+unsigned parse_u32(const char* s) { return (unsigned)parse_u64(s, nullptr); }
 
 void add_device(std::vector<gmp_device>* list, const std::string& spec) {
     gmp_device d;
@@ -44,7 +126,7 @@ void add_device(std::vector<gmp_device>* list, const std::string& spec) {
     std::string uuid = spec;
     if (colon != std::string::npos && colon + 1 < spec.size() && spec.find_first_not_of("0123456789", colon + 1) == std::string::npos) {
         uuid = spec.substr(0, colon);
-        d.minor = (uint32_t)strtoul(spec.c_str() + colon + 1, nullptr, 10);
+        d.minor = parse_u32(spec.c_str() + colon + 1);
     }
     snprintf(d.uuid, sizeof(d.uuid), "%s", uuid.c_str());
     list->push_back(d);
@@ -77,14 +159,14 @@ int main(int argc, char** argv) {
     std::string dev_dir;
     // environment defaults (the worker's DaemonSet can set them once; command-line flags win)
     if (const char* v = getenv("GPUMOUNTER_PROBE_BYTES")) o.hbm.bytes = parse_size(v);
-    if (const char* v = getenv("GPUMOUNTER_PROBE_ITERS")) o.hbm.iters = (uint32_t)atoi(v);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_ITERS")) o.hbm.iters = parse_u32(v);
     if (const char* v = getenv("GPUMOUNTER_PROBE_PATTERNS"))
-        o.hbm.pattern_mask = strcmp(v, "all") == 0 ? (1u << GMP_PAT_COUNT) - 1 : (uint32_t)strtoul(v, nullptr, 0);
-    if (const char* v = getenv("GPUMOUNTER_PROBE_SEED")) o.hbm.seed = strtoull(v, nullptr, 0);
+        o.hbm.pattern_mask = strcmp(v, "all") == 0 ? (1u << GMP_PAT_COUNT) - 1 : parse_u32(v);
+    if (const char* v = getenv("GPUMOUNTER_PROBE_SEED")) o.hbm.seed = parse_u64(v, nullptr);
     if (const char* v = getenv("GPUMOUNTER_PROBE_DMA_BYTES")) o.hbm.dma_bytes = parse_size(v);
     if (const char* v = getenv("GPUMOUNTER_PROBE_P2P_BYTES")) o.p2p.bytes = parse_size(v);
     if (const char* v = getenv("GPUMOUNTER_PROBE_SKIP_P2P")) {
-        if (atoi(v) != 0) o.flags |= GMP_PROBE_F_SKIP_P2P;
+        if (parse_u32(v) != 0) o.flags |= GMP_PROBE_F_SKIP_P2P;
     }
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
@@ -108,14 +190,14 @@ int main(int argc, char** argv) {
                 b = c + 1;
             }
         } else if (a == "--bytes") o.hbm.bytes = parse_size(need("--bytes"));
-        else if (a == "--iters") o.hbm.iters = (uint32_t)atoi(need("--iters"));
+        else if (a == "--iters") o.hbm.iters = parse_u32(need("--iters"));
         else if (a == "--patterns") {
             const std::string v = need("--patterns");
-            o.hbm.pattern_mask = v == "all" ? (1u << GMP_PAT_COUNT) - 1 : (uint32_t)strtoul(v.c_str(), nullptr, 0);
-        } else if (a == "--seed") o.hbm.seed = strtoull(need("--seed"), nullptr, 0);
+            o.hbm.pattern_mask = v == "all" ? (1u << GMP_PAT_COUNT) - 1 : parse_u32(v.c_str());
+        } else if (a == "--seed") o.hbm.seed = parse_u64(need("--seed"), nullptr);
         else if (a == "--dma-bytes") o.hbm.dma_bytes = parse_size(need("--dma-bytes"));
         else if (a == "--p2p-bytes") o.p2p.bytes = parse_size(need("--p2p-bytes"));
-        else if (a == "--p2p-iters") o.p2p.iters = (uint32_t)atoi(need("--p2p-iters"));
+        else if (a == "--p2p-iters") o.p2p.iters = parse_u32(need("--p2p-iters"));
         else if (a == "--dev-dir") dev_dir = need("--dev-dir");
         else if (a == "--skip-nodes") o.flags |= GMP_PROBE_F_SKIP_NODES;
         else if (a == "--skip-hbm") o.flags |= GMP_PROBE_F_SKIP_HBM;

@@ -26,6 +26,15 @@ def test_executable_is_self_contained():
                for l in libs), libs
 
 
+def test_glibc_floor_is_2_34():
+    """The probe is exec'ed inside arbitrary pods: it must not need a newer libc than 2.34 (see probe_main.cpp)."""
+    import re
+
+    out = subprocess.run(["objdump", "-T", EXE], capture_output=True, text=True).stdout
+    versions = sorted({tuple(int(x) for x in v.split(".")) for v in re.findall(r"GLIBC_([0-9.]+)", out)})
+    assert versions and versions[-1] <= (2, 34), versions
+
+
 def test_missing_nodes_have_distinct_codes(tmp_path):
     d = tmp_path / "dev"
     d.mkdir()
