@@ -1,0 +1,84 @@
+"""ref: pkg/util/gpu/collector/collector.go:165-194 — the kubelet PodResources client (connectToServer + ListPods).
+
+The reference imports k8s.io/kubernetes v1.18.6 pkg/kubelet/apis/podresources/v1alpha1 (go.mod:14), which is not vendored;
+the five messages and the one method are restated here from that API's published definition (parity
+unpinned — there is no kubelet in this environment; tests run against a stand-in server on a unix socket):
+
+    service PodResourcesLister { rpc List(ListPodResourcesRequest) returns (ListPodResourcesResponse) }   package v1alpha1
+    ListPodResourcesResponse { repeated PodResources pod_resources = 1 }
+    PodResources            { string name = 1; string namespace = 2; repeated ContainerResources containers = 3 }
+    ContainerResources      { string name = 1; repeated ContainerDevices devices = 2 }
+    ContainerDevices        { string resource_name = 1; repeated string device_ids = 2 }
+"""
+
+from __future__ import annotations
+
+import os
+from typing import List, Tuple
+
+from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+
+SocketDir = "/var/lib/kubelet/pod-resources"   # ref: pkg/util/gpu/types.go:6
+SocketPath = SocketDir + "/kubelet.sock"       # ref: types.go:7
+ConnectionTimeout = 10.0                        # seconds, ref: types.go:9
+LIST_METHOD = "/v1alpha1.PodResourcesLister/List"
+
+_F = descriptor_pb2.FieldDescriptorProto
+
+
+def _file() -> descriptor_pb2.FileDescriptorProto:
+    fd = descriptor_pb2.FileDescriptorProto(name="podresources_v1alpha1.proto", package="v1alpha1", syntax="proto3")
+
+    def msg(name, fields):
+        m = fd.message_type.add(name=name)
+        for fname, num, ftype, label, tname in fields:
+            f = m.field.add(name=fname, number=num, type=ftype, label=label)
+            if tname:
+                f.type_name = ".v1alpha1." + tname
+
+    opt, rep = _F.LABEL_OPTIONAL, _F.LABEL_REPEATED
+    msg("ListPodResourcesRequest", [])
+    msg("ListPodResourcesResponse", [("pod_resources", 1, _F.TYPE_MESSAGE, rep, "PodResources")])
+    msg("PodResources", [("name", 1, _F.TYPE_STRING, opt, None), ("namespace", 2, _F.TYPE_STRING, opt, None),
+                         ("containers", 3, _F.TYPE_MESSAGE, rep, "ContainerResources")])
+    msg("ContainerResources", [("name", 1, _F.TYPE_STRING, opt, None), ("devices", 2, _F.TYPE_MESSAGE, rep, "ContainerDevices")])
+    msg("ContainerDevices", [("resource_name", 1, _F.TYPE_STRING, opt, None), ("device_ids", 2, _F.TYPE_STRING, rep, None)])
+    s = fd.service.add(name="PodResourcesLister")
+    s.method.add(name="List", input_type=".v1alpha1.ListPodResourcesRequest", output_type=".v1alpha1.ListPodResourcesResponse")
+    return fd
+
+
+_pool = descriptor_pool.DescriptorPool()
+_pool.Add(_file())
+ListPodResourcesRequest = message_factory.GetMessageClass(_pool.FindMessageTypeByName("v1alpha1.ListPodResourcesRequest"))
+ListPodResourcesResponse = message_factory.GetMessageClass(_pool.FindMessageTypeByName("v1alpha1.ListPodResourcesResponse"))
+
+Listing = List[Tuple[str, str, List[Tuple[str, List[Tuple[str, List[str]]]]]]]
+
+
+def to_listing(resp) -> Listing:
+    """The (pod, namespace, [(container, [(resource_name, [device_ids])])]) form GPUCollector.UpdateGPUStatus takes."""
+    return [(p.name, p.namespace, [(c.name, [(d.resource_name, list(d.device_ids)) for d in c.devices]) for c in p.containers])
+            for p in resp.pod_resources]
+
+
+def ListPods(socket_path: str = SocketPath, timeout: float = ConnectionTimeout) -> Listing:
+    """ref: collector.go:92-111 (stat the socket), :165-180 (blocking dial over unix, 10 s), :182-194 (List, 10 s)."""
+    import grpc
+
+    if not os.path.exists(socket_path):
+        raise FileNotFoundError(f"Can not found {socket_path}")  # collector.go:93-97
+    channel = grpc.insecure_channel("unix://" + socket_path)
+    try:
+        try:
+            grpc.channel_ready_future(channel).result(timeout=timeout)  # grpc.WithBlock()
+        except grpc.FutureTimeoutError:
+            raise ConnectionError(f"failure connecting to {socket_path}: context deadline exceeded")
+        call = channel.unary_unary(LIST_METHOD, request_serializer=lambda m: m.SerializeToString(),
+                                   response_deserializer=ListPodResourcesResponse.FromString)
+        try:
+            return to_listing(call(ListPodResourcesRequest(), timeout=timeout))
+        except grpc.RpcError as e:
+            raise ConnectionError(f"failure getting pod resources {e.code().name}: {e.details()}")
+    finally:
+        channel.close()
