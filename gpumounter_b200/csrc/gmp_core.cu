@@ -399,6 +399,25 @@ int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeReso
         out->d2h_bytes += 32;
         note_verify(out, v, last_pattern);
     }
+    if (o.flags & GMP_HBM_F_LIB_BASELINES) {
+        // the same buffers through the driver's own memset / device-to-device copy (SURVEY 2.3 baselines)
+        for (uint32_t it = 0; it < o.iters; ++it) {
+            float ms = 0.f;
+            GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
+            GMP_CUDA(cudaMemsetAsync(r.a, 0x5A, o.bytes, r.stream));
+            GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+            GMP_CUDA(cudaEventSynchronize(r.ev[1]));
+            GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
+            if (ms > 0.f) out->lib_memset_gbs = std::max(out->lib_memset_gbs, (double)o.bytes / (ms * 1e-3) / 1e9);
+            if (!want_copy) continue;
+            GMP_CUDA(cudaEventRecord(r.ev[0], r.stream));
+            GMP_CUDA(cudaMemcpyAsync(r.b, r.a, o.bytes, cudaMemcpyDeviceToDevice, r.stream));
+            GMP_CUDA(cudaEventRecord(r.ev[1], r.stream));
+            GMP_CUDA(cudaEventSynchronize(r.ev[1]));
+            GMP_CUDA(cudaEventElapsedTime(&ms, r.ev[0], r.ev[1]));
+            if (ms > 0.f) out->lib_memcpy_gbs = std::max(out->lib_memcpy_gbs, 2.0 * (double)o.bytes / (ms * 1e-3) / 1e9);
+        }
+    }
     out->ns_kernels = now_ns() - tk0;
     out->write_gbs_best = wr.best();
     out->write_gbs_median = wr.median();

@@ -123,6 +123,23 @@ int run_pairs(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
             }
             out->write_gbs[cell(n, i, j)] = best_w;
             out->read_gbs[cell(n, i, j)] = best_r;
+            // library baseline: the copy engines move i's buffer into j's; j verifies what arrived
+            double best_c = 0.0;
+            for (uint32_t it = 0; it < o.iters; ++it) {
+                const uint64_t seed = pair_seed(o.seed ^ 0xC0FFEEull, i, j, it);
+                float ms = 0.f;
+                GMP_CUDA(cudaSetDevice(pi.ordinal));
+                GMP_CUDA(launch_write(pi.buf, o.bytes, GMP_PAT_SPLITMIX, seed, pi.stream));
+                GMP_CUDA(cudaEventRecord(pi.e0, pi.stream));
+                GMP_CUDA(cudaMemcpyPeerAsync(pj.buf, pj.ordinal, pi.buf, pi.ordinal, o.bytes, pi.stream));
+                GMP_CUDA(cudaEventRecord(pi.e1, pi.stream));
+                GMP_CUDA(cudaEventSynchronize(pi.e1));
+                GMP_CUDA(cudaEventElapsedTime(&ms, pi.e0, pi.e1));
+                if (ms > 0.f) best_c = std::max(best_c, (double)o.bytes / (ms * 1e-3) / 1e9);
+                int rc = verify_local(s, out, i, j, 0, o.bytes, seed);
+                if (rc != GMP_OK) return rc;
+            }
+            out->memcpy_gbs[cell(n, i, j)] = best_c;
         }
     }
     return GMP_OK;

@@ -373,6 +373,8 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
         j.knum("copy_gbs_median", h.copy_gbs_median);
         j.knum("h2d_gbs", h.h2d_gbs);
         j.knum("d2h_gbs", h.d2h_gbs);
+        j.knum("lib_memset_gbs", h.lib_memset_gbs);
+        j.knum("lib_memcpy_gbs", h.lib_memcpy_gbs);
         j.ku("mismatch_lanes", h.mismatch_lanes);
         j.ku("xor64", h.xor64);
         j.ku("sum64", h.sum64);
@@ -404,6 +406,7 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
         j.matrix("nvml_atomics", p.nvml_atomics, p.n, false);
         j.matrix("write_gbs", p.write_gbs, p.n, true);
         j.matrix("read_gbs", p.read_gbs, p.n, true);
+        j.matrix("memcpy_peer_gbs", p.memcpy_gbs, p.n, true);
         j.key("bidir_gbs");
         j.raw("[");
         for (int i = 0; i < p.n; ++i) {

@@ -137,7 +137,7 @@ void usage() {
             "usage: gpumounter-probe --gone GPU-...:minor [--gone ...] [--dev-dir DIR]     (after an unmount)\n"
             "       gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
             "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
-            "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only]\n"
+            "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only] [--lib-baselines]\n"
             "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n"
             "Defaults may come from GPUMOUNTER_PROBE_BYTES / _ITERS / _PATTERNS / _SEED / _DMA_BYTES / _P2P_BYTES / _SKIP_P2P.\n");
 }
@@ -204,6 +204,7 @@ int main(int argc, char** argv) {
         else if (a == "--skip-p2p") o.flags |= GMP_PROBE_F_SKIP_P2P;
         else if (a == "--skip-nvml") o.flags |= GMP_PROBE_F_SKIP_NVML;
         else if (a == "--skip-copy") o.hbm.flags |= GMP_HBM_F_SKIP_COPY;
+        else if (a == "--lib-baselines") o.hbm.flags |= GMP_HBM_F_LIB_BASELINES;
         else if (a == "--matrix-only") o.p2p.flags |= GMP_P2P_F_MATRIX_ONLY;
         else if (a == "-h" || a == "--help") {
             usage();

@@ -23,6 +23,7 @@ PATTERN_NAMES = ("splitmix", "zero", "ones", "checker", "address")
 
 HBM_F_SKIP_COPY = 1 << 0
 HBM_F_KEEP_DEVICE = 1 << 1
+HBM_F_LIB_BASELINES = 1 << 2
 UINT64_MAX = (1 << 64) - 1
 
 
@@ -90,6 +91,8 @@ class gmp_hbm_result(ctypes.Structure):
         ("ns_teardown", ctypes.c_uint64),
         ("ns_total", ctypes.c_uint64),
         ("mono_first_verified_ns", ctypes.c_uint64),
+        ("lib_memset_gbs", ctypes.c_double),
+        ("lib_memcpy_gbs", ctypes.c_double),
     ]
 
     def as_dict(self) -> dict:
@@ -282,6 +285,7 @@ class gmp_p2p_result(ctypes.Structure):
         ("nvml_read", ctypes.c_int32 * GMP_P2P_CELLS), ("nvml_write", ctypes.c_int32 * GMP_P2P_CELLS),
         ("nvml_nvlink", ctypes.c_int32 * GMP_P2P_CELLS), ("nvml_atomics", ctypes.c_int32 * GMP_P2P_CELLS),
         ("write_gbs", ctypes.c_double * GMP_P2P_CELLS), ("read_gbs", ctypes.c_double * GMP_P2P_CELLS),
+        ("memcpy_gbs", ctypes.c_double * GMP_P2P_CELLS),
         ("bidir_gbs", ctypes.c_double * GMP_MAX_DEVICES), ("alltoall_gbs", ctypes.c_double),
         ("bytes", ctypes.c_uint64), ("mismatch_lanes", ctypes.c_uint64),
         ("first_bad_src", ctypes.c_int32), ("first_bad_dst", ctypes.c_int32),

@@ -276,7 +276,8 @@ typedef struct gmp_hbm_opts {
 
 enum {
     GMP_HBM_F_SKIP_COPY   = 1u << 0,
-    GMP_HBM_F_KEEP_DEVICE = 1u << 1   /* do not cudaDeviceReset() at the end (in-process callers that share the context) */
+    GMP_HBM_F_KEEP_DEVICE = 1u << 1,  /* do not cudaDeviceReset() at the end (in-process callers that share the context) */
+    GMP_HBM_F_LIB_BASELINES = 1u << 2 /* also time cudaMemsetAsync and cudaMemcpyAsync D2D on the same buffers */
 };
 
 typedef struct gmp_hbm_result {
@@ -307,6 +308,9 @@ typedef struct gmp_hbm_result {
     uint64_t ns_total;
     uint64_t mono_first_verified_ns; /* absolute CLOCK_MONOTONIC time at which the first kernel result verified
                                         (comparable across processes of one host: the "usable" instant) */
+    double   lib_memset_gbs;         /* same buffer through cudaMemsetAsync (bytes written / time), best of iters */
+    double   lib_memcpy_gbs;         /* A -> B through cudaMemcpyAsync device-to-device (2N bytes / time), best of iters;
+                                        both 0 unless GMP_HBM_F_LIB_BASELINES is set */
 } gmp_hbm_result;
 
 /* uuid == NULL or "" probes CUDA ordinal 0. */
@@ -323,6 +327,7 @@ GMP_API int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_re
  *   - write_gbs[i*n+j]    = a kernel on GPU i STORES the pattern into GPU j's HBM over NVLink
  *                           (16/32-byte peer stores), GPU j then verifies its own memory;
  *   - read_gbs[i*n+j]     = a kernel on GPU i LOADS and verifies GPU j's buffer over NVLink;
+ *   - memcpy_gbs[i*n+j]   = cudaMemcpyPeerAsync from GPU i's buffer to GPU j's (copy engines), verified by j;
  *   - bidir_gbs[i]        = GPU i's traffic (sent + received bytes / time) while all GPUs exchange
  *                           with a partner at once, worst round of the n-1 round schedule;
  *   - alltoall_gbs        = aggregate when every GPU writes to every peer at once.
@@ -363,6 +368,7 @@ typedef struct gmp_p2p_result {
     int32_t  nvml_atomics[GMP_P2P_CELLS];
     double   write_gbs[GMP_P2P_CELLS];          /* best of iters; 0 on the diagonal / inaccessible pairs */
     double   read_gbs[GMP_P2P_CELLS];
+    double   memcpy_gbs[GMP_P2P_CELLS];         /* cudaMemcpyPeerAsync i -> j (copy engines), the library baseline */
     double   bidir_gbs[GMP_MAX_DEVICES];
     double   alltoall_gbs;
     uint64_t bytes;

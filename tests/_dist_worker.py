@@ -18,5 +18,5 @@ mine_ms = 10.0 + 5.0 * rank
 slowest = bench.max_over_ranks(mine_ms, world, device="cpu")
 value = bench.whole_job_gbs(step_bytes=4 << 30, steps=7, world=world, slowest_seconds=slowest * 1e-3)
 dist.barrier()
-print(json.dumps({"rank": rank, "slowest_ms": slowest, "value": value}), flush=True)
+os.write(1, (json.dumps({"rank": rank, "slowest_ms": slowest, "value": value}) + "\n").encode())  # one atomic write per rank
 dist.destroy_process_group()

@@ -40,7 +40,8 @@ def test_probe_hbm_in_process_keep_device(cuda):
     nbytes = (256 << 20) + 48
     mask = (1 << probe.PAT_COUNT) - 1
     r = probe.probe_hbm(nbytes=nbytes, iters=2, pattern_mask=mask, seed=77, dma_bytes=8 << 20,
-                        flags=probe.HBM_F_KEEP_DEVICE)
+                        flags=probe.HBM_F_KEEP_DEVICE | probe.HBM_F_LIB_BASELINES)
+    assert r.lib_memset_gbs > 100 and r.lib_memcpy_gbs > 100
     assert r.status == 0 and r.mismatch_lanes == 0 and r.first_bad_pattern == -1
     assert r.patterns_run == mask and r.bytes == nbytes and r.sm_count == 148
     assert r.uuid.decode() == probe.enumerate_cuda()[0].uuid
@@ -115,6 +116,7 @@ def test_probe_p2p_pairs(cuda):
                 assert ca[i][j] == 1, "HGX B200: every pair is NVLink-connected"
                 assert r.matrix("nvml_nvlink")[i][j] == 0
                 assert wr[i][j] > 300 and rd[i][j] > 300, (i, j, wr[i][j], rd[i][j])
+                assert r.matrix("memcpy_gbs")[i][j] > 300
         assert r.bidir_gbs[i] > 500
         assert r.nvlink_active[i] == 18
     assert r.alltoall_gbs > 300 * n
