@@ -203,3 +203,44 @@ def test_probe_executable_reads_environment_defaults():
     assert p.returncode == 0, p.stdout[-1000:] + p.stderr[-1000:]
     j = json.loads(p.stdout.strip().splitlines()[-1])
     assert j["status"] == 0 and all(h["bytes"] == 64 << 20 and h["h2d_gbs"] == 0 for h in j["hbm"]) and "p2p" not in j
+
+
+def test_impossible_allocation_is_a_clean_nomem():
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from gpumounter_b200 import probe\n"
+        "r = probe.probe_hbm(nbytes=400 << 30, iters=1, dma_bytes=0, raise_on_error=False)\n"
+        "print(r.status)\n"
+        "r = probe.probe_hbm(nbytes=64 << 20, iters=1, dma_bytes=0)\n"
+        "print(r.status)\n" % ROOT
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout.split() == [str(_lib.GMP_ERR_NOMEM), "0"]     # and the device is still usable afterwards
+
+
+def test_repeated_one_shot_probes_leave_nothing_behind():
+    """Config 5's leak-free contract on the probe side: after each call (default flags: cudaDeviceReset) the device's free
+    memory is back where it started, and after KEEP_DEVICE calls only the context itself remains."""
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from cuda.bindings import runtime as rt\n"
+        "from gpumounter_b200 import probe\n"
+        "def free():\n"
+        "    err, f, t = rt.cudaMemGetInfo(); assert int(err) == 0; return f\n"
+        "probe.probe_hbm(nbytes=256 << 20, iters=1, dma_bytes=1 << 20, flags=probe.HBM_F_KEEP_DEVICE)\n"
+        "base = free()\n"
+        "for i in range(12):\n"
+        "    r = probe.probe_hbm(nbytes=(512 << 20) + 16 * i, iters=1, dma_bytes=4 << 20, flags=probe.HBM_F_KEEP_DEVICE)\n"
+        "    assert r.status == 0\n"
+        "kept = free()\n"
+        "for i in range(4):\n"
+        "    assert probe.probe_hbm(nbytes=512 << 20, iters=1, dma_bytes=4 << 20).status == 0   # resets the device\n"
+        "uuid = probe.enumerate_cuda()[0].uuid\n"
+        "assert probe.probe_p2p([uuid], nbytes=64 << 20).status == 0\n"
+        "print(base, kept)\n" % ROOT
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    base, kept = (int(x) for x in out.stdout.split()[-2:])
+    assert abs(base - kept) <= 64 << 20, (base, kept)   # nothing accumulates over a dozen calls (allocator granularity aside)
