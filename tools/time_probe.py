@@ -20,5 +20,5 @@ if j["hbm"]:
     out["hbm0"] = {k: h[k] for k in h if k.startswith("ms_") or k.endswith("_gbs")}
 if "p2p" in j:
     q = j["p2p"]
-    out["p2p"] = {k: q[k] for k in q if k.startswith("ms_") or k in ("matrix_match", "alltoall_gbs", "bidir_gbs", "write_gbs", "read_gbs", "can_access", "nvml_nvlink", "nvlink_active")}
+    out["p2p"] = {k: q[k] for k in q if k.startswith("ms_") or k in ("matrix_match", "alltoall_gbs", "bidir_gbs", "write_gbs", "read_gbs", "memcpy_peer_gbs", "can_access", "nvml_nvlink", "nvlink_active")}
 print(json.dumps(out))
