@@ -1,26 +1,26 @@
 // HBM probe kernels for NVIDIA B200 (sm_100a): pattern write, read-verify, copy.
 //
-// All three are pure streaming kernels bound by HBM3e bandwidth (0 reuse, a few
-// integer ops per 16 bytes), so the design rules are the memory ones:
-//   * every global access is a 16-byte vector (one warp instruction = 512
-//     contiguous bytes = four full 128-byte lines);
-//   * each thread keeps UNROLL independent 16-byte requests in flight before it
-//     touches any of them (memory-level parallelism hides the ~600-cycle DRAM
-//     latency);
-//   * a CTA walks contiguous THREADS*UNROLL*16-byte tiles (4-16 KiB), and the
-//     grid is persistent: (SM count) x (CTAs per SM) CTAs stride over the tiles,
-//     so the launch is exactly one wave on all 148 SMs;
-//   * streaming cache hints keep the 126 MB L2 from being polluted by data that
-//     is never re-read;
-//   * the verify kernel folds mismatch count, first bad lane and two checksums
-//     in registers, reduces with warp shuffles and shared memory, and issues four
-//     atomics per CTA (<= a few thousand per launch).
+// All three are pure streaming kernels bound by HBM3e bandwidth (no reuse, a few integer ops per 16 bytes), so the
+// design rules are the memory ones:
+//   * every register-path access is one vector instruction per thread: 16 bytes (LDG/STG.E.128) or, Blackwell only,
+//     32 bytes (LDG/STG.E.ENL2.256); a warp instruction covers 512 B or 1 KiB of contiguous memory;
+//   * each thread issues all UNROLL loads of a tile before it touches any of them (memory-level parallelism hides the
+//     ~600-cycle DRAM latency); __launch_bounds__(T, 1024/T) keeps ptxas from chasing 32 registers and serialising them;
+//   * CTAs walk contiguous tiles in grid-stride order, so the whole chip sweeps one narrow window of memory at a time;
+//   * the grid is sized per kernel from a sweep on silicon (profiles/r01_sweep.md): many small waves for the write
+//     kernel (the hardware scheduler evens out the ~10 % speed spread between SMs), exactly one resident wave for the
+//     verify kernel (its accumulators live in registers; four atomics per CTA at the end);
+//   * streaming cache hints (.cs) keep the 126 MB L2 from being polluted by data that is never re-read;
+//   * the copy does not use the register path at all: cp.async.bulk moves 112 KiB chunks global -> shared -> global
+//     through the TMA engine, one issuing thread per CTA (k_hbm_copy_bulk); the vector kernel k_hbm_copy remains for
+//     the last partial chunk, for misaligned pointers and for peer copies;
+//   * the verify fast path only ORs difference bits into one word per tile and re-walks a dirty tile in a
+//     __noinline__ slow path: 33 instead of 47 instructions per lane, which moved the kernel off the ALU roof.
 //
-// Algorithmic bytes per launch (used for every GB/s figure): write = N,
-// verify = N, copy = 2N for an N-byte buffer.
+// Algorithmic bytes per launch (used for every GB/s figure): write = N, verify = N, copy = 2N for an N-byte buffer.
 //
-// There is no reference counterpart (the reference has no device code); the CPU
-// statement of the same arithmetic used by the tests is oracle/gmo_pattern.c.
+// There is no reference counterpart (the reference has no device code); the CPU statement of the same arithmetic used
+// by the tests is oracle/gmo_pattern.c.
 
 #include "gmp_internal.h"
 

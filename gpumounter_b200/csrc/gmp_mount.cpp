@@ -3,10 +3,11 @@
 // Behavioural contract = the reference's Go packages (cited per function); mechanism =
 // direct system calls.  The reference spends two to three fork/exec chains per GPU
 // (sh -> echo; nsenter -> sh -> mknod) and needs sh/mknod/rm/kill inside the target image
-// (ref: docs/guide/FAQ.md:3-4).  Here: open/write for the device-cgroup line and one forked
-// child per call that setns()es into the target's mount namespace and issues mknod(2) /
-// unlink(2) itself.  A child is still needed because setns(CLONE_NEWNS) is refused for a
-// multithreaded caller (the worker is one), but it never exec()s anything.
+// (ref: docs/guide/FAQ.md:3-4).  Here: open/write for the device-cgroup line and one helper
+// process per call (clone(CLONE_VM|CLONE_VFORK) on a private stack) that setns()es into the
+// target's mount namespace and issues mknod(2) / unlink(2) itself.  A helper is still needed
+// because setns(CLONE_NEWNS) is refused for a multithreaded caller (the worker is one), but it
+// never exec()s anything and never copies the worker's page tables.
 
 #include <errno.h>
 #include <fcntl.h>
