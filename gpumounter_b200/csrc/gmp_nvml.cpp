@@ -47,6 +47,12 @@ int NvmlSession::open() {
         {(void**)&DeviceGetGraphicsRunningProcesses, "nvmlDeviceGetGraphicsRunningProcesses_v3", false},
         {(void**)&SystemGetDriverVersion, "nvmlSystemGetDriverVersion", false},
         {(void**)&SystemGetNVMLVersion, "nvmlSystemGetNVMLVersion", false},
+        {(void**)&DeviceGetClockInfo, "nvmlDeviceGetClockInfo", false},
+        {(void**)&DeviceGetMaxClockInfo, "nvmlDeviceGetMaxClockInfo", false},
+        {(void**)&DeviceGetTemperature, "nvmlDeviceGetTemperature", false},
+        {(void**)&DeviceGetPowerUsage, "nvmlDeviceGetPowerUsage", false},
+        {(void**)&DeviceGetClocksReasons, "nvmlDeviceGetCurrentClocksThrottleReasons", false},
+        {(void**)&DeviceGetTotalEccErrors, "nvmlDeviceGetTotalEccErrors", false},
     };
     for (const Sym& s : syms) {
         *s.slot = dlsym(h, s.name);
@@ -219,6 +225,36 @@ extern "C" int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_ind
                      "nvmlDeviceGetP2PStatus");
             status[i * n + j] = (int32_t)st;
         }
+    }
+    return GMP_OK;
+}
+
+extern "C" int gmp_nvml_health(const char* uuid, gmp_gpu_health* out) {
+    clear_error();
+    if (uuid == nullptr || out == nullptr) {
+        set_error("NULL argument");
+        return GMP_ERR_INVALID;
+    }
+    memset(out, 0xFF, sizeof(*out));  // every field "unknown" until NVML answers it
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    nvmlDevice_t dev;
+    GMP_NVML(nv, nv.DeviceGetHandleByUUID(uuid, &dev), "nvmlDeviceGetHandleByUUID");
+    unsigned int v = 0;
+    if (nv.DeviceGetClockInfo && nv.DeviceGetClockInfo(dev, NVML_CLOCK_SM, &v) == NVML_SUCCESS) out->sm_mhz = v;
+    if (nv.DeviceGetClockInfo && nv.DeviceGetClockInfo(dev, NVML_CLOCK_MEM, &v) == NVML_SUCCESS) out->mem_mhz = v;
+    if (nv.DeviceGetMaxClockInfo && nv.DeviceGetMaxClockInfo(dev, NVML_CLOCK_SM, &v) == NVML_SUCCESS) out->sm_max_mhz = v;
+    if (nv.DeviceGetMaxClockInfo && nv.DeviceGetMaxClockInfo(dev, NVML_CLOCK_MEM, &v) == NVML_SUCCESS) out->mem_max_mhz = v;
+    if (nv.DeviceGetTemperature && nv.DeviceGetTemperature(dev, NVML_TEMPERATURE_GPU, &v) == NVML_SUCCESS) out->temperature_c = v;
+    if (nv.DeviceGetPowerUsage && nv.DeviceGetPowerUsage(dev, &v) == NVML_SUCCESS) out->power_mw = v;
+    unsigned long long w = 0;
+    if (nv.DeviceGetClocksReasons && nv.DeviceGetClocksReasons(dev, &w) == NVML_SUCCESS) out->throttle_reasons = w;
+    if (nv.DeviceGetTotalEccErrors) {
+        if (nv.DeviceGetTotalEccErrors(dev, NVML_MEMORY_ERROR_TYPE_UNCORRECTED, NVML_VOLATILE_ECC, &w) == NVML_SUCCESS)
+            out->ecc_uncorrected_volatile = w;
+        if (nv.DeviceGetTotalEccErrors(dev, NVML_MEMORY_ERROR_TYPE_CORRECTED, NVML_VOLATILE_ECC, &w) == NVML_SUCCESS)
+            out->ecc_corrected_volatile = w;
     }
     return GMP_OK;
 }

@@ -42,6 +42,12 @@ class NvmlSession {
     nvmlReturn_t (*DeviceGetGraphicsRunningProcesses)(nvmlDevice_t, unsigned int*, nvmlProcessInfo_t*) = nullptr;
     nvmlReturn_t (*SystemGetDriverVersion)(char*, unsigned int) = nullptr;
     nvmlReturn_t (*SystemGetNVMLVersion)(char*, unsigned int) = nullptr;
+    nvmlReturn_t (*DeviceGetClockInfo)(nvmlDevice_t, nvmlClockType_t, unsigned int*) = nullptr;
+    nvmlReturn_t (*DeviceGetMaxClockInfo)(nvmlDevice_t, nvmlClockType_t, unsigned int*) = nullptr;
+    nvmlReturn_t (*DeviceGetTemperature)(nvmlDevice_t, nvmlTemperatureSensors_t, unsigned int*) = nullptr;
+    nvmlReturn_t (*DeviceGetPowerUsage)(nvmlDevice_t, unsigned int*) = nullptr;
+    nvmlReturn_t (*DeviceGetClocksReasons)(nvmlDevice_t, unsigned long long*) = nullptr;
+    nvmlReturn_t (*DeviceGetTotalEccErrors)(nvmlDevice_t, nvmlMemoryErrorType_t, nvmlEccCounterType_t, unsigned long long*) = nullptr;
 
   private:
     void* handle_ = nullptr;

@@ -248,6 +248,11 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
 
     // 4. NVML's view joins in: minor numbers and NVML indices by UUID, and the (UUID, minor) cross-check
     if (nvml_thread.joinable()) nvml_thread.join();
+    for (int i = 0; i < n; ++i) {  // clocks / throttle reasons / ECC while the GPUs are still warm from the passes
+        memset(&out->health[i], 0xFF, sizeof(out->health[i]));
+        if (n_nvml > 0) (void)gmp_nvml_health(out->devices[i].uuid, &out->health[i]);
+    }
+    clear_error();
     for (int i = 0; i < n && n_nvml > 0; ++i) {
         const int k = find_uuid(nvml, n_nvml, out->devices[i].uuid);
         if (k < 0) {
@@ -387,6 +392,26 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
         j.kms("ms_teardown", h.ns_teardown);
         j.kms("ms_total", h.ns_total);
         j.ku("mono_first_verified_ns", h.mono_first_verified_ns);
+        j.raw("}");
+    }
+    j.raw("]");
+    j.key("health");
+    j.raw("[");
+    for (int i = 0; i < n; ++i) {
+        const gmp_gpu_health& h = r->health[i];
+        auto opt32 = [](uint32_t v) { return v == UINT32_MAX ? -1ll : (long long)v; };
+        auto opt64 = [](uint64_t v) { return v == UINT64_MAX ? -1ll : (long long)v; };
+        j.sep();
+        j.raw("{");
+        j.ki("sm_mhz", opt32(h.sm_mhz));
+        j.ki("mem_mhz", opt32(h.mem_mhz));
+        j.ki("sm_max_mhz", opt32(h.sm_max_mhz));
+        j.ki("mem_max_mhz", opt32(h.mem_max_mhz));
+        j.ki("temperature_c", opt32(h.temperature_c));
+        j.ki("power_mw", opt32(h.power_mw));
+        j.ki("throttle_reasons", opt64(h.throttle_reasons));
+        j.ki("ecc_uncorrected_volatile", opt64(h.ecc_uncorrected_volatile));
+        j.ki("ecc_corrected_volatile", opt64(h.ecc_corrected_volatile));
         j.raw("}");
     }
     j.raw("]");

@@ -299,6 +299,20 @@ class gmp_p2p_result(ctypes.Structure):
         return [[flat[i * n + j] for j in range(n)] for i in range(n)]
 
 
+class gmp_gpu_health(ctypes.Structure):
+    _fields_ = [("sm_mhz", ctypes.c_uint32), ("mem_mhz", ctypes.c_uint32), ("sm_max_mhz", ctypes.c_uint32),
+                ("mem_max_mhz", ctypes.c_uint32), ("temperature_c", ctypes.c_uint32), ("power_mw", ctypes.c_uint32),
+                ("throttle_reasons", ctypes.c_uint64), ("ecc_uncorrected_volatile", ctypes.c_uint64),
+                ("ecc_corrected_volatile", ctypes.c_uint64)]
+
+
+def nvml_health(uuid: str) -> gmp_gpu_health:
+    """Clocks, throttle reasons, temperature, power and ECC counters of one GPU (unknown fields are all-ones)."""
+    h = gmp_gpu_health()
+    check(lib().gmp_nvml_health(uuid.encode(), ctypes.byref(h)), "gmp_nvml_health")
+    return h
+
+
 class gmp_probe_opts(ctypes.Structure):
     _fields_ = [("hbm", gmp_hbm_opts), ("p2p", gmp_p2p_opts), ("flags", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
                 ("dev_dir", ctypes.c_char_p)]
@@ -309,6 +323,7 @@ class gmp_report(ctypes.Structure):
         ("status", ctypes.c_int32), ("n", ctypes.c_int32), ("nodes_status", ctypes.c_int32),
         ("device_set_status", ctypes.c_int32), ("nvml_status", ctypes.c_int32), ("reserved", ctypes.c_int32),
         ("devices", gmp_device * GMP_MAX_DEVICES), ("hbm", gmp_hbm_result * GMP_MAX_DEVICES), ("p2p", gmp_p2p_result),
+        ("health", gmp_gpu_health * GMP_MAX_DEVICES),
         ("ns_nodes", ctypes.c_uint64), ("ns_enumerate", ctypes.c_uint64), ("ns_hbm", ctypes.c_uint64),
         ("ns_p2p", ctypes.c_uint64), ("ns_total", ctypes.c_uint64), ("ns_cuda_init", ctypes.c_uint64),
         ("ns_nvml", ctypes.c_uint64), ("mono_start_ns", ctypes.c_uint64), ("mono_usable_ns", ctypes.c_uint64),

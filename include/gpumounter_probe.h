@@ -145,6 +145,23 @@ GMP_API int gmp_gpu_running_processes(const char* uuid, gmp_process_info* out, i
  */
 GMP_API int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_index, int32_t* status);
 
+/*
+ * Clocks, throttle reasons, temperature, power and ECC counters of one GPU as NVML reports them at the moment of the
+ * call (every bandwidth figure is recorded with the clocks it was taken at).  No reference counterpart.
+ * A field NVML cannot answer is left at UINT32_MAX / UINT64_MAX.  throttle_reasons is NVML's clocks-event bit mask
+ * (0x8 hw_slowdown, 0x40 hw_thermal, 0x20 sw_thermal, 0x4 sw_power_cap, 0x1 gpu_idle).
+ */
+typedef struct gmp_gpu_health {
+    uint32_t sm_mhz, mem_mhz, sm_max_mhz, mem_max_mhz;
+    uint32_t temperature_c;
+    uint32_t power_mw;
+    uint64_t throttle_reasons;
+    uint64_t ecc_uncorrected_volatile;
+    uint64_t ecc_corrected_volatile;
+} gmp_gpu_health;
+
+GMP_API int gmp_nvml_health(const char* uuid, gmp_gpu_health* out);
+
 /* Number of NVLink links NVML reports enabled on the GPU (18 on an HGX B200). */
 GMP_API int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* max_links);
 
@@ -426,6 +443,7 @@ typedef struct gmp_report {
     gmp_device     devices[GMP_MAX_DEVICES];   /* CUDA view joined with NVML (minor, nvml_index) by UUID */
     gmp_hbm_result hbm[GMP_MAX_DEVICES];
     gmp_p2p_result p2p;
+    gmp_gpu_health health[GMP_MAX_DEVICES];    /* sampled right after the HBM passes, while the GPUs are still warm */
     uint64_t       ns_nodes, ns_enumerate, ns_hbm, ns_p2p, ns_total;
     uint64_t       ns_cuda_init;    /* cuInit + device enumeration (inside ns_enumerate) */
     uint64_t       ns_nvml;         /* NVML load + init + enumeration, overlapped with CUDA start-up on its own thread */

@@ -237,3 +237,80 @@ nvmlReturn_t nvmlSystemGetNVMLVersion(char* v, unsigned int len) {
     snprintf(v, len, "%s", g_nvml);
     return NVML_SUCCESS;
 }
+
+/* ---- health: fixed answers, overridable per device with "health <uuid> <sm> <mem> <temp> <power_mw> <reasons> <ecc_unc>" */
+struct fake_health { int gpu; unsigned sm, mem, temp, power; unsigned long long reasons, ecc_unc; };
+static struct fake_health g_health[MAX_GPUS];
+static int g_nhealth;
+
+static const struct fake_health* health_of(int i) {
+    static const struct fake_health dflt = {-1, 1965, 3996, 41, 250000, 0, 0};
+    const char* path = getenv("GMP_FAKE_NVML_CONFIG");
+    g_nhealth = 0;
+    if (path) {
+        FILE* f = fopen(path, "r");
+        char line[512];
+        while (f && fgets(line, sizeof(line), f)) {
+            char uuid[96];
+            struct fake_health h;
+            if (strncmp(line, "health ", 7) == 0 && g_nhealth < MAX_GPUS &&
+                sscanf(line, "%*s %95s %u %u %u %u %llu %llu", uuid, &h.sm, &h.mem, &h.temp, &h.power, &h.reasons, &h.ecc_unc) == 7) {
+                h.gpu = gpu_index(uuid);
+                g_health[g_nhealth++] = h;
+            }
+        }
+        if (f) fclose(f);
+    }
+    for (int k = 0; k < g_nhealth; ++k)
+        if (g_health[k].gpu == i) return &g_health[k];
+    return &dflt;
+}
+
+nvmlReturn_t nvmlDeviceGetClockInfo(nvmlDevice_t d, nvmlClockType_t t, unsigned int* c) {
+    MAYBE_FAIL("nvmlDeviceGetClockInfo");
+    int i = index_of(d);
+    if (i < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *c = t == NVML_CLOCK_MEM ? health_of(i)->mem : health_of(i)->sm;
+    return NVML_SUCCESS;
+}
+
+nvmlReturn_t nvmlDeviceGetMaxClockInfo(nvmlDevice_t d, nvmlClockType_t t, unsigned int* c) {
+    MAYBE_FAIL("nvmlDeviceGetMaxClockInfo");
+    if (index_of(d) < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *c = t == NVML_CLOCK_MEM ? 3996 : 1965;
+    return NVML_SUCCESS;
+}
+
+nvmlReturn_t nvmlDeviceGetTemperature(nvmlDevice_t d, nvmlTemperatureSensors_t s, unsigned int* t) {
+    MAYBE_FAIL("nvmlDeviceGetTemperature");
+    (void)s;
+    int i = index_of(d);
+    if (i < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *t = health_of(i)->temp;
+    return NVML_SUCCESS;
+}
+
+nvmlReturn_t nvmlDeviceGetPowerUsage(nvmlDevice_t d, unsigned int* mw) {
+    MAYBE_FAIL("nvmlDeviceGetPowerUsage");
+    int i = index_of(d);
+    if (i < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *mw = health_of(i)->power;
+    return NVML_SUCCESS;
+}
+
+nvmlReturn_t nvmlDeviceGetCurrentClocksThrottleReasons(nvmlDevice_t d, unsigned long long* r) {
+    MAYBE_FAIL("nvmlDeviceGetCurrentClocksThrottleReasons");
+    int i = index_of(d);
+    if (i < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *r = health_of(i)->reasons;
+    return NVML_SUCCESS;
+}
+
+nvmlReturn_t nvmlDeviceGetTotalEccErrors(nvmlDevice_t d, nvmlMemoryErrorType_t et, nvmlEccCounterType_t ct, unsigned long long* n) {
+    MAYBE_FAIL("nvmlDeviceGetTotalEccErrors");
+    (void)ct;
+    int i = index_of(d);
+    if (i < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *n = et == NVML_MEMORY_ERROR_TYPE_UNCORRECTED ? health_of(i)->ecc_unc : 0;
+    return NVML_SUCCESS;
+}

@@ -104,7 +104,7 @@ def test_python_struct_mirrors_match_the_compiled_sizes(tmp_path):
 
     names = ["gmp_device", "gmp_verify_result", "gmp_hbm_opts", "gmp_hbm_result", "gmp_p2p_opts", "gmp_p2p_result",
              "gmp_probe_opts", "gmp_report", "gmp_gpu", "gmp_pod", "gmp_container_resources", "gmp_mount_env", "gmp_ns_config",
-             "gmp_process_info", "gmp_container_devices", "gmp_container_entry", "gmp_pod_resources"]
+             "gmp_process_info", "gmp_gpu_health", "gmp_container_devices", "gmp_container_entry", "gmp_pod_resources"]
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include "gpumounter_probe.h"\nint main(void) {\n' +
                    "".join(f'  printf("{n} %zu\\n", sizeof({n}));\n' for n in names) + "  return 0;\n}\n")

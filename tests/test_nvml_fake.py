@@ -107,3 +107,20 @@ def test_device_set_comparison(fake_nvml):
     assert not probe.device_sets_equal(nv, cu)
     wrong_minor = [probe.Device(d.uuid, (d.minor + 1) % 8, "", d.nvml_index, -1) for d in nv]
     assert not probe.device_sets_equal(nv, wrong_minor)
+
+
+def test_health_reports_clocks_reasons_and_ecc(fake_nvml):
+    fake_nvml(extra=[f"health {FAKE_UUIDS[1]} 1357 3996 83 999600 4 2"])   # sw_power_cap, two uncorrected ECC errors
+    h = probe.nvml_health(FAKE_UUIDS[0])
+    assert (h.sm_mhz, h.mem_mhz, h.sm_max_mhz, h.mem_max_mhz, h.throttle_reasons, h.ecc_uncorrected_volatile) == (
+        1965, 3996, 1965, 3996, 0, 0)
+    h = probe.nvml_health(FAKE_UUIDS[1])
+    assert (h.sm_mhz, h.temperature_c, h.power_mw, h.throttle_reasons, h.ecc_uncorrected_volatile, h.ecc_corrected_volatile) == (
+        1357, 83, 999600, 4, 2, 0)
+    # a query NVML refuses leaves its field "unknown" instead of failing the whole call
+    fake_nvml(fail=[("nvmlDeviceGetTemperature", 3), ("nvmlDeviceGetTotalEccErrors", 3)])
+    h = probe.nvml_health(FAKE_UUIDS[0])
+    assert h.temperature_c == 0xFFFFFFFF and h.ecc_uncorrected_volatile == (1 << 64) - 1 and h.sm_mhz == 1965
+    with pytest.raises(ProbeError) as e:
+        probe.nvml_health("GPU-unknown")
+    assert e.value.code == _lib.GMP_ERR_NVML

@@ -141,6 +141,9 @@ def test_probe_all_and_json_in_a_child_process():
         assert h["status"] == 0 and h["mismatch_lanes"] == 0 and h["write_gbs"] > 1000 and h["read_gbs"] > 1000
     if j["n_gpus"] >= 2:
         assert j["p2p"]["matrix_match"] == 1 and j["p2p"]["mismatch_lanes"] == 0
+    for h in j["health"]:   # clocks and throttle reasons are recorded next to the bandwidths
+        assert 1000 <= h["sm_mhz"] <= h["sm_max_mhz"] and h["mem_mhz"] > 1000 and h["ecc_uncorrected_volatile"] <= 0
+        assert h["throttle_reasons"] & (0x8 | 0x40 | 0x20) == 0, "hardware / thermal slowdown during the probe"
 
 
 def test_probe_all_rejects_a_wrong_device_set():
