@@ -20,6 +20,14 @@ namespace {
 
 using namespace gmp;
 
+// 256 CTAs x 256 threads, every thread adds (its global index + 1) to a 64-bit counter that lives on the PEER:
+// the adds are resolved by the remote GPU's L2 atomic unit after crossing NVLink.  Expected sum = n(n+1)/2.
+constexpr unsigned kAtomicCtas = 256, kAtomicThreads = 256;
+__global__ void __launch_bounds__(256) k_peer_atomic_add(unsigned long long* counter) {
+    const unsigned long long mine = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x + 1;
+    atomicAdd(counter, mine);
+}
+
 struct PeerGpu {
     int ordinal = -1;
     cudaStream_t stream = nullptr;
@@ -140,6 +148,24 @@ int run_pairs(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
                 if (rc != GMP_OK) return rc;
             }
             out->memcpy_gbs[cell(n, i, j)] = best_c;
+            // native atomics from i on a counter in j's memory
+            {
+                unsigned long long got = 0;
+                const unsigned long long total = (unsigned long long)kAtomicCtas * kAtomicThreads;
+                GMP_CUDA(cudaSetDevice(pj.ordinal));
+                GMP_CUDA(cudaMemsetAsync(pj.acc, 0, sizeof(unsigned long long), pj.stream));
+                GMP_CUDA(cudaStreamSynchronize(pj.stream));
+                GMP_CUDA(cudaSetDevice(pi.ordinal));
+                k_peer_atomic_add<<<kAtomicCtas, kAtomicThreads, 0, pi.stream>>>(pj.acc);
+                GMP_CUDA(cudaGetLastError());
+                GMP_CUDA(cudaStreamSynchronize(pi.stream));
+                GMP_CUDA(cudaSetDevice(pj.ordinal));
+                GMP_CUDA(cudaMemcpyAsync(&got, pj.acc, sizeof(got), cudaMemcpyDeviceToHost, pj.stream));
+                GMP_CUDA(cudaStreamSynchronize(pj.stream));
+                const bool ok = got == total * (total + 1) / 2;
+                out->atomics_ok[cell(n, i, j)] = ok ? 1 : 0;
+                if (!ok) note(out, gmp_verify_result{1, 0, 0, 0}, i, j);
+            }
         }
     }
     return GMP_OK;
@@ -350,6 +376,7 @@ extern "C" int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts
     }
     memset(out, 0, sizeof(*out));
     out->first_bad_src = out->first_bad_dst = -1;
+    for (int k = 0; k < GMP_P2P_CELLS; ++k) out->atomics_ok[k] = -1;
     for (int i = 0; i < GMP_MAX_DEVICES; ++i) {
         out->cuda_ordinal[i] = -1;
         out->nvlink_active[i] = -1;

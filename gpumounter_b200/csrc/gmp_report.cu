@@ -432,6 +432,7 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
         j.matrix("write_gbs", p.write_gbs, p.n, true);
         j.matrix("read_gbs", p.read_gbs, p.n, true);
         j.matrix("memcpy_peer_gbs", p.memcpy_gbs, p.n, true);
+        j.matrix("atomics_ok", p.atomics_ok, p.n, false);
         j.key("bidir_gbs");
         j.raw("[");
         for (int i = 0; i < p.n; ++i) {

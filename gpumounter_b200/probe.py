@@ -285,7 +285,7 @@ class gmp_p2p_result(ctypes.Structure):
         ("nvml_read", ctypes.c_int32 * GMP_P2P_CELLS), ("nvml_write", ctypes.c_int32 * GMP_P2P_CELLS),
         ("nvml_nvlink", ctypes.c_int32 * GMP_P2P_CELLS), ("nvml_atomics", ctypes.c_int32 * GMP_P2P_CELLS),
         ("write_gbs", ctypes.c_double * GMP_P2P_CELLS), ("read_gbs", ctypes.c_double * GMP_P2P_CELLS),
-        ("memcpy_gbs", ctypes.c_double * GMP_P2P_CELLS),
+        ("memcpy_gbs", ctypes.c_double * GMP_P2P_CELLS), ("atomics_ok", ctypes.c_int32 * GMP_P2P_CELLS),
         ("bidir_gbs", ctypes.c_double * GMP_MAX_DEVICES), ("alltoall_gbs", ctypes.c_double),
         ("bytes", ctypes.c_uint64), ("mismatch_lanes", ctypes.c_uint64),
         ("first_bad_src", ctypes.c_int32), ("first_bad_dst", ctypes.c_int32),

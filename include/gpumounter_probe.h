@@ -345,6 +345,8 @@ GMP_API int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_re
  *                           (16/32-byte peer stores), GPU j then verifies its own memory;
  *   - read_gbs[i*n+j]     = a kernel on GPU i LOADS and verifies GPU j's buffer over NVLink;
  *   - memcpy_gbs[i*n+j]   = cudaMemcpyPeerAsync from GPU i's buffer to GPU j's (copy engines), verified by j;
+ *   - atomics_ok[i*n+j]   = native atomics over NVLink work from i on j's memory (what NCCL/NVSHMEM-style
+ *                           workloads in the pod will rely on); a wrong sum is counted as a verification failure;
  *   - bidir_gbs[i]        = GPU i's traffic (sent + received bytes / time) while all GPUs exchange
  *                           with a partner at once, worst round of the n-1 round schedule;
  *   - alltoall_gbs        = aggregate when every GPU writes to every peer at once.
@@ -386,6 +388,8 @@ typedef struct gmp_p2p_result {
     double   write_gbs[GMP_P2P_CELLS];          /* best of iters; 0 on the diagonal / inaccessible pairs */
     double   read_gbs[GMP_P2P_CELLS];
     double   memcpy_gbs[GMP_P2P_CELLS];         /* cudaMemcpyPeerAsync i -> j (copy engines), the library baseline */
+    int32_t  atomics_ok[GMP_P2P_CELLS];         /* 65 536 atomicAdd's from GPU i on a counter in GPU j's memory summed
+                                                   exactly: 1 yes, 0 no, -1 not run (diagonal, inaccessible pair) */
     double   bidir_gbs[GMP_MAX_DEVICES];
     double   alltoall_gbs;
     uint64_t bytes;

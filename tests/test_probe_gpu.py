@@ -117,6 +117,7 @@ def test_probe_p2p_pairs(cuda):
                 assert r.matrix("nvml_nvlink")[i][j] == 0
                 assert wr[i][j] > 300 and rd[i][j] > 300, (i, j, wr[i][j], rd[i][j])
                 assert r.matrix("memcpy_gbs")[i][j] > 300
+                assert r.matrix("atomics_ok")[i][j] == 1 and r.matrix("nvml_atomics")[i][j] == 0
         assert r.bidir_gbs[i] > 500
         assert r.nvlink_active[i] == 18
     assert r.alltoall_gbs > 300 * n
