@@ -11,17 +11,45 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <map>
+#include <mutex>
+#include <string>
 #include <vector>
 
 namespace gmp {
 void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
 void clear_error();
 
+namespace {
+
+// The library image stays loaded for the life of the process, one handle per name.  The reference
+// dlopens and dlcloses around every query (ref: nvml_dl.go:29-53); with the 580 driver's libnvidia-ml
+// each fresh image leaves two eventfds and two pipes behind at its first nvmlInit_v2 that neither
+// nvmlShutdown nor dlclose gives back (tools/nvml_fd_leak.py, profiles/r01_nvml_fd_leak.json), so a
+// worker that mounts and unmounts for weeks would run out of descriptors.  Loaded once, the cost is
+// paid once; nvmlInit_v2 / nvmlShutdown still bracket every session, so the device list is fresh.
+std::mutex g_images_mu;
+std::map<std::string, void*>& images() {
+    static std::map<std::string, void*>* m = new std::map<std::string, void*>();  // never destroyed: no exit-time dlclose
+    return *m;
+}
+
+void* load_image(const char* name) {
+    std::lock_guard<std::mutex> lock(g_images_mu);
+    auto it = images().find(name);
+    if (it != images().end()) return it->second;
+    void* h = dlopen(name, RTLD_LAZY | RTLD_LOCAL);
+    if (h != nullptr) images().emplace(name, h);
+    return h;
+}
+
+}  // namespace
+
 int NvmlSession::open() {
     if (handle_ != nullptr) return GMP_OK;
     const char* name = getenv("GPUMOUNTER_NVML_LIB");
     if (name == nullptr || name[0] == '\0') name = "libnvidia-ml.so.1";  // ref: nvml_dl.go:30
-    void* h = dlopen(name, RTLD_LAZY | RTLD_LOCAL);
+    void* h = load_image(name);
     if (h == nullptr) {
         set_error("could not load NVML library (%s)", dlerror());  // ref: bindings.go:53-55
         return GMP_ERR_NVML_NOT_FOUND;
@@ -58,7 +86,6 @@ int NvmlSession::open() {
         *s.slot = dlsym(h, s.name);
         if (*s.slot == nullptr && s.required) {
             set_error("could not load NVML library (%s lacks %s)", name, s.name);
-            dlclose(h);
             return GMP_ERR_NVML_NOT_FOUND;
         }
     }
@@ -67,7 +94,6 @@ int NvmlSession::open() {
         handle_ = h;
         int rc = fail(r, "nvmlInit_v2");
         handle_ = nullptr;
-        dlclose(h);
         return rc;
     }
     handle_ = h;
@@ -77,8 +103,7 @@ int NvmlSession::open() {
 void NvmlSession::close() {
     if (handle_ == nullptr) return;
     if (Shutdown) (void)Shutdown();
-    dlclose(handle_);
-    handle_ = nullptr;
+    handle_ = nullptr;  // the image stays loaded, see load_image()
 }
 
 int NvmlSession::fail(nvmlReturn_t r, const char* what) const {

@@ -18,9 +18,10 @@ class NvmlSession {
     NvmlSession(const NvmlSession&) = delete;
     NvmlSession& operator=(const NvmlSession&) = delete;
 
-    // dlopen + nvmlInit_v2.  GMP_OK, GMP_ERR_NVML_NOT_FOUND or GMP_ERR_NVML.
+    // dlopen (once per process and library name; the image is kept) + nvmlInit_v2.  GMP_OK, GMP_ERR_NVML_NOT_FOUND or GMP_ERR_NVML.
     int open();
-    // nvmlShutdown + dlclose (ref: nvml_dl.go:39-53).
+    // nvmlShutdown.  Unlike ref: nvml_dl.go:39-53 there is no dlclose: every fresh image of the driver's
+    // library leaks descriptors at its first init (gmp_nvml.cpp, load_image).
     void close();
     bool is_open() const { return handle_ != nullptr; }
 

@@ -124,3 +124,26 @@ def test_health_reports_clocks_reasons_and_ecc(fake_nvml):
     with pytest.raises(ProbeError) as e:
         probe.nvml_health("GPU-unknown")
     assert e.value.code == _lib.GMP_ERR_NVML
+
+
+def _maps_count(needle):
+    with open("/proc/self/maps") as f:
+        return len({line.split()[-1] for line in f if needle in line})
+
+
+def test_sessions_reuse_one_library_image_and_leak_no_descriptors(fake_nvml):
+    """The driver's libnvidia-ml leaves descriptors behind per fresh image (profiles/r01_nvml_fd_leak.json), so the
+    image is loaded once per process; nvmlInit_v2/nvmlShutdown still bracket every call, so a changed device list
+    is seen by the next call."""
+    import os
+
+    fake_nvml()
+    probe.enumerate_nvml()
+    fds0 = len(os.listdir("/proc/self/fd"))
+    for i in range(50):
+        gpus = fake_nvml(gpus=[(FAKE_UUIDS[j], j, f"00000000:{0x10 + j:02X}:00.0") for j in range(1 + i % 8)])
+        assert [d.uuid for d in probe.enumerate_nvml()] == [g[0] for g in gpus]
+        d, n = ctypes.create_string_buffer(80), ctypes.create_string_buffer(80)
+        assert lib().gmp_nvml_versions(d, 80, n, 80) == 0
+    assert len(os.listdir("/proc/self/fd")) == fds0
+    assert _maps_count("libfake_nvml") == 1

@@ -198,6 +198,48 @@ def to_usable(iters, hbm_bytes, n_gpus):
     return out
 
 
+def churn_real(rounds, hbm_bytes=256 << 20):
+    """Config 5 on real GPUs: 1 -> N -> 1 mounted GPUs, `rounds` times.  Every step: native mount, in-pod probe (HBM only),
+    native unmount, in-pod check that the nodes are gone, and NVML's process list of every touched GPU back to its
+    baseline (no probe context left behind).  Latencies: mount-to-usable per step, unmount-to-verified per step."""
+    nv = {d.uuid: d for d in probe.enumerate_nvml()}
+    cu = probe.enumerate_cuda()
+    gpus = [(d.uuid, nv[d.uuid].minor) for d in cu]
+    n = len(gpus)
+    recs_all = [device.New(m, u) for u, m in gpus]
+    baseline = [len(r.GetRunningProcess()) for r in recs_all]
+    fds0 = open_fds()
+    usable_s, gone_s, steps = [], [], 0
+    with harness.Target() as t:
+        for name in ("nvidiactl", "nvidia-uvm"):
+            mknod_like(f"/dev/{name}", f"/proc/{t.pid}/root{t.devdir}/{name}")
+        pod, env = product_pod(), env_of(t)
+        for _ in range(rounds):
+            for k in list(range(1, n + 1)) + list(range(n - 1, 0, -1)):
+                recs = recs_all[:k]
+                os.environ["CUDA_VISIBLE_DEVICES"] = ",".join(u for u, _ in gpus[:k])
+                t0 = time.monotonic_ns()
+                util.MountGPUs(pod, recs, env)
+                rc, rep = util.ProbeInPod(pod, recs, ["--dev-dir", t.devdir, "--bytes", str(hbm_bytes), "--iters", "1",
+                                                       "--dma-bytes", "1M", "--skip-p2p"], env, raise_on_error=False)
+                os.environ.pop("CUDA_VISIBLE_DEVICES", None)
+                assert rc == 0 and rep.get("status") == 0, rep
+                usable_s.append((rep["mono_usable_ns"] - t0) / 1e9)
+                t1 = time.monotonic_ns()
+                util.UnmountGPUs(pod, recs, False, env)
+                rc, gone = util.VerifyUnmountedInPod(pod, recs, env, dev_dir=t.devdir, raise_on_error=False)
+                gone_s.append((time.monotonic_ns() - t1) / 1e9)
+                assert rc == 0 and gone.get("status") == 0, gone
+                assert [x for x in t.nodes() if x.startswith("nvidia") and x[6:].isdigit()] == []
+                steps += 1
+        leaked_procs = [len(r.GetRunningProcess()) - b for r, b in zip(recs_all, baseline)]
+    return {"gpus": n, "rounds": rounds, "steps": steps, "hbm_bytes_per_gpu": hbm_bytes,
+            "mount_to_usable": {"p50_s": statistics.median(usable_s), "p99_s": pct(usable_s, 0.99), "max_s": max(usable_s)},
+            "unmount_to_verified_gone": {"p50_ms": 1e3 * statistics.median(gone_s), "p99_ms": 1e3 * pct(gone_s, 0.99)},
+            "leaked_fds": open_fds() - fds0, "leaked_gpu_processes": leaked_procs,
+            "zombies": sum(1 for p in os.listdir("/proc") if p.isdigit() and _is_zombie_child(p))}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=100)
@@ -205,6 +247,7 @@ def main():
     ap.add_argument("--churn-rounds", type=int, default=100)
     ap.add_argument("--usable-iters", type=int, default=0, help="> 0 only on a box with real GPUs")
     ap.add_argument("--usable-bytes", type=int, default=1 << 30)
+    ap.add_argument("--churn-real-rounds", type=int, default=0, help="> 0 only on a box with real GPUs")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     why = harness.can_run()
@@ -253,6 +296,8 @@ def main():
         n_vis = len(probe.enumerate_cuda())
         out["mount_to_usable"] = {str(n): to_usable(args.usable_iters, args.usable_bytes, n)
                                   for n in (1, 2, 4, 8) if n <= n_vis}
+    if args.churn_real_rounds > 0 and have_gpu:
+        out["churn_real"] = churn_real(args.churn_real_rounds)
     text = json.dumps(out)
     print(text)
     if args.out:
