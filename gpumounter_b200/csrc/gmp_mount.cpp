@@ -28,6 +28,7 @@
 #include <string>
 #include <vector>
 
+#include "gmp_nvml_hold.h"
 #include "gpumounter_probe.h"
 
 namespace gmp {
@@ -593,6 +594,7 @@ int unmount_many(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gp
     rc = read_cgroup_pids(env, cgroup_path, &pids);
     if (rc != GMP_OK) return rc;
     std::vector<std::string> victims;  // ref: util.go:100-109
+    gmp::NvmlHold one_attach_for_all_gpus;
     for (int i = 0; i < n; ++i) {
         std::vector<std::string> busy;
         rc = busy_pids(pids, &gpus[i], &busy);

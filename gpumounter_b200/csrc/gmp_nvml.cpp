@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <map>
+#include <new>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -111,6 +112,23 @@ int NvmlSession::fail(nvmlReturn_t r, const char* what) const {
     set_error("nvml: %s (%s)", s, what);  // ref: bindings.go:47-48
     return GMP_ERR_NVML;
 }
+
+}  // namespace gmp
+
+#include "gmp_nvml_hold.h"
+
+namespace gmp {
+
+NvmlHold::NvmlHold() : session_(nullptr) {
+    NvmlSession* s = new (std::nothrow) NvmlSession();
+    if (s != nullptr && s->open() != GMP_OK) {
+        delete s;
+        s = nullptr;
+    }
+    session_ = s;
+}
+
+NvmlHold::~NvmlHold() { delete static_cast<NvmlSession*>(session_); }
 
 }  // namespace gmp
 

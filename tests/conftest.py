@@ -45,8 +45,7 @@ def fake_nvml(tmp_path, monkeypatch):
     Usage: fake_nvml(gpus=[(uuid, minor, bus)], procs=[(uuid, pid, bytes, 'compute')], p2p=[(i, j, caps, status)],
                      fail=[('nvmlDeviceGetUUID', 999)], nvlink=[(uuid, 18)])
     """
-    if not os.path.exists(FAKE_NVML):
-        subprocess.run(["make", "-s", "-C", os.path.dirname(FAKE_NVML)], check=True)
+    subprocess.run(["make", "-s", "-C", os.path.dirname(FAKE_NVML)], check=True)  # no-op when up to date
     cfg = tmp_path / "fake_nvml.cfg"
     monkeypatch.setenv("GPUMOUNTER_NVML_LIB", FAKE_NVML)
     monkeypatch.setenv("GMP_FAKE_NVML_CONFIG", str(cfg))

@@ -102,16 +102,21 @@ static int index_of(nvmlDevice_t d) {
     return (i >= 0 && i < g_ngpus) ? i : -1;
 }
 
+/* Reference-counted like the real library: only the 0 -> 1 init is a cold one (driver attach, tens of ms on a real
+ * box) and only the 1 -> 0 shutdown detaches.  fake_nvml_cold_inits() lets a test count the cold ones. */
+static unsigned g_cold_inits;
+unsigned fake_nvml_cold_inits(void) { return g_cold_inits; }
+
 nvmlReturn_t nvmlInit_v2(void) {
     load_config();
     MAYBE_FAIL("nvmlInit_v2");
-    g_inited = 1;
+    if (g_inited++ == 0) ++g_cold_inits;
     return NVML_SUCCESS;
 }
 
 nvmlReturn_t nvmlShutdown(void) {
     if (!g_inited) return NVML_ERROR_UNINITIALIZED;
-    g_inited = 0;
+    --g_inited;
     return NVML_SUCCESS;
 }
 

@@ -145,7 +145,15 @@ def test_batched_mount_and_unmount_of_eight_gpus(fake_nvml):
         assert a.nodes() == b.nodes() == [f"nvidia{i}" for i in range(8)]
         assert [a.node(i) for i in range(8)] == [b.node(i) for i in range(8)] == [(195, i, 0o666) for i in range(8)]
         assert a.read("devices.allow") == b.read("devices.allow")  # the last line written wins in a plain file
+        # the busy check asks NVML once per GPU (ref: util.go:100-109, nvidia.go:58-63: init .. shutdown each time);
+        # batched, the eight queries share one driver attach
+        import ctypes
+        from tests.conftest import FAKE_NVML
+        cold = ctypes.CDLL(FAKE_NVML).fake_nvml_cold_inits
+        cold.restype = ctypes.c_uint
+        before = cold()
         assert util.UnmountGPUs(product_pod(), gpus, False, env_of(a)) == 8
+        assert cold() - before == 1
         assert a.nodes() == []
         # a failure part-way reports how far it got and leaves earlier GPUs mounted (no rollback, as in the reference)
         util.MountGPU(product_pod(), gpus[2], env_of(a))

@@ -60,7 +60,36 @@ def open_fds():
     return len(os.listdir("/proc/self/fd"))
 
 
-def bench_reference(t, gpus, iters):
+def reference_running_processes(uuid):
+    """GetRunningProcess as the reference does it (ref: pkg/device/nvidia.go:58-87 over nvml_dl.go:29-53): dlopen, nvmlInit_v2,
+    handle by UUID, graphics then compute processes (1024 entries each), nvmlShutdown, dlclose - once per GPU.  Only used on a
+    box with a real driver, so that the reference arm of the unmount timing pays the same NVML busy check the native arm does."""
+    import ctypes
+    import _ctypes
+
+    class ProcessInfo(ctypes.Structure):  # nvmlProcessInfo_t (v3): pid, usedGpuMemory, gpuInstanceId, computeInstanceId
+        _fields_ = [("pid", ctypes.c_uint), ("mem", ctypes.c_ulonglong), ("gi", ctypes.c_uint), ("ci", ctypes.c_uint)]
+
+    h = _ctypes.dlopen("libnvidia-ml.so.1", os.RTLD_LAZY | os.RTLD_LOCAL)
+    try:
+        lib = ctypes.CDLL("libnvidia-ml.so.1", handle=h)
+        assert lib.nvmlInit_v2() == 0
+        try:
+            dev = ctypes.c_void_p()
+            assert lib.nvmlDeviceGetHandleByUUID(uuid.encode(), ctypes.byref(dev)) == 0
+            pids = []
+            for fn in (lib.nvmlDeviceGetGraphicsRunningProcesses_v3, lib.nvmlDeviceGetComputeRunningProcesses_v3):
+                buf, n = (ProcessInfo * 1024)(), ctypes.c_uint(1024)
+                assert fn(dev, ctypes.byref(n), buf) == 0
+                pids += [buf[i].pid for i in range(n.value)]
+            return pids
+        finally:
+            lib.nvmlShutdown()
+    finally:
+        _ctypes.dlclose(h)
+
+
+def bench_reference(t, gpus, iters, nvml_busy_check=False):
     """The oracle's fork/exec restatement: the timed CPU baseline (1 thread)."""
     from oracle import gmo_ref_ctypes as ref  # the checker doubles as the timed reference arm, nothing else
 
@@ -73,8 +102,8 @@ def bench_reference(t, gpus, iters):
         for r in recs:  # serial, as server.go:80-95
             ref.mount_gpu(pod, r, **kw)
         t1 = time.perf_counter()
-        for r in recs:  # server.go:155-168
-            ref.unmount_gpu(pod, r, False, [], **kw)
+        for (u, _), r in zip(gpus, recs):  # server.go:155-168
+            ref.unmount_gpu(pod, r, False, reference_running_processes(u) if nvml_busy_check else [], **kw)
         t2 = time.perf_counter()
         mount_s.append(t1 - t0)
         unmount_s.append(t2 - t1)
@@ -266,7 +295,8 @@ def main():
         os.environ["GMP_FAKE_NVML_CONFIG"] = cfg
     else:
         os.environ.pop("GPUMOUNTER_NVML_LIB", None)
-    out = {"host_cores": os.cpu_count(), "threads_used": 1, "iters": args.iters, "mount": {}, "unmount": {}}
+    out = {"host_cores": os.cpu_count(), "threads_used": 1, "iters": args.iters, "mount": {}, "unmount": {},
+           "unmount_nvml_busy_check": "real NVML, both arms" if have_gpu else "fake NVML in the native arm, none in the reference arm"}
     # On a GPU box the unmount path's NVML query names a UUID: use real UUIDs where they exist, made-up ones beyond
     real = []
     if have_gpu:
@@ -278,7 +308,7 @@ def main():
             # NVML only answers for real UUIDs; repeat them with distinct minors to model G GPUs' worth of work
             gpus = [(real[i % len(real)][0], 100 + i) for i in range(g)]
         with harness.Target() as t:
-            ref_m, ref_u = bench_reference(t, gpus, args.iters)
+            ref_m, ref_u = bench_reference(t, gpus, args.iters, nvml_busy_check=have_gpu)
         with harness.Target() as t:
             nat_m, nat_u = bench_native(t, gpus, args.iters, batched=True)
         with harness.Target() as t:
