@@ -240,15 +240,17 @@ struct ProbeResources {
     void* b = nullptr;
     unsigned long long* acc = nullptr;
     void* pinned = nullptr;
+    void* touch = nullptr;  // first-touch scratch, normally freed before the large buffers are allocated
     void release() {
         if (pinned) cudaFreeHost(pinned);
+        if (touch) cudaFree(touch);
         if (acc) cudaFree(acc);
         if (b) cudaFree(b);
         if (a) cudaFree(a);
         for (auto& e : ev)
             if (e) cudaEventDestroy(e);
         if (stream) cudaStreamDestroy(stream);
-        pinned = a = b = nullptr;
+        pinned = touch = a = b = nullptr;
         acc = nullptr;
         ev[0] = ev[1] = nullptr;
         stream = nullptr;
@@ -316,25 +318,25 @@ int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeReso
     GMP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ordinal));
     out->sm_count = (uint32_t)sms;
 
-    t0 = now_ns();
     GMP_CUDA(cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking));
     GMP_CUDA(cudaEventCreate(&r.ev[0]));
     GMP_CUDA(cudaEventCreate(&r.ev[1]));
-    GMP_CUDA(cudaMalloc(&r.a, o.bytes));
     const bool want_copy = !(o.flags & GMP_HBM_F_SKIP_COPY);
-    if (want_copy) GMP_CUDA(cudaMalloc(&r.b, o.bytes));
-    GMP_CUDA(cudaMalloc(&r.acc, 4 * sizeof(unsigned long long)));
-    out->ns_alloc = now_ns() - t0;
     out->d2h_bytes = 0;
     out->h2d_bytes = 0;
 
-    // Untimed first touch on a small prefix: loads the three kernels (lazy module loading makes the first
-    // launch of each cost milliseconds) and yields the earliest possible "a kernel ran on this GPU and its
-    // result verified" milestone, which is what mount-to-usable latency waits for.
+    // Untimed first touch, in a small allocation of its own and BEFORE the large buffers exist: it loads the three
+    // kernels (lazy module loading makes the first launch of each cost milliseconds) and yields the earliest possible
+    // "a kernel ran on this GPU and its result verified" milestone, which is what mount-to-usable latency waits for.
+    // cudaMalloc of the large buffers costs ~30 ms per GiB and serialises across the GPUs of one process (8 x 2 GiB:
+    // 0.47 s, profiles/r01_8gpu/mount_latency_resident_8gpu.json), so it must not sit in front of that milestone.
     {
         const uint64_t tf = now_ns();
         const size_t wb = (size_t)std::min<uint64_t>(o.bytes, 4ull << 20);
-        PassCtx c{&r, r.a, nullptr, wb, GMP_PAT_SPLITMIX, o.seed ^ 0xA5A5A5A5ull};
+        const size_t second = (wb + 255) & ~(size_t)255;  // copy destination, 256-byte aligned like a cudaMalloc result
+        GMP_CUDA(cudaMalloc(&r.touch, want_copy ? second + wb : wb));
+        GMP_CUDA(cudaMalloc(&r.acc, 4 * sizeof(unsigned long long)));
+        PassCtx c{&r, r.touch, nullptr, wb, GMP_PAT_SPLITMIX, o.seed ^ 0xA5A5A5A5ull};
         GMP_CUDA(do_write(&c));
         GMP_CUDA(do_verify(&c));
         gmp_verify_result v;
@@ -343,13 +345,20 @@ int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeReso
         out->d2h_bytes += 32;
         note_verify(out, v, GMP_PAT_SPLITMIX);
         if (want_copy) {
-            PassCtx cc{&r, r.b, r.a, wb, GMP_PAT_SPLITMIX, 0};
+            PassCtx cc{&r, static_cast<char*>(r.touch) + second, r.touch, wb, GMP_PAT_SPLITMIX, 0};
             GMP_CUDA(do_copy(&cc));
             GMP_CUDA(cudaStreamSynchronize(r.stream));
         }
         out->ns_first_kernel = now_ns() - tf;
         if (v.mismatch_lanes == 0) out->mono_first_verified_ns = now_ns();
+        GMP_CUDA(cudaFree(r.touch));
+        r.touch = nullptr;
     }
+
+    t0 = now_ns();
+    GMP_CUDA(cudaMalloc(&r.a, o.bytes));
+    if (want_copy) GMP_CUDA(cudaMalloc(&r.b, o.bytes));
+    out->ns_alloc = now_ns() - t0;
 
     Series wr, rd, cp;
     const uint64_t tk0 = now_ns();

@@ -146,7 +146,12 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
         first_failure(out, out->nodes_status);
     }
     out->ns_nodes = now_ns() - t0;
-    if (out->status != GMP_OK) {
+    if (out->status != GMP_OK || (o.flags & GMP_PROBE_F_NODES_ONLY)) {
+        if (out->status == GMP_OK) {
+            out->n = n_expected;
+            for (int i = 0; i < n_expected; ++i) out->devices[i] = expected[i];
+            out->nvml_status = GMP_ERR_UNAVAILABLE;  // not consulted
+        }
         out->ns_total = now_ns() - t_begin;
         return out->status;
     }
@@ -203,7 +208,7 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
                 if (out->devices[i].pci_bus_id[0] == '\0') memcpy(out->devices[i].pci_bus_id, cuda[c].pci_bus_id, GMP_PCI_LEN);
             }
         }
-        if (out->device_set_status == GMP_OK && n_cuda != n_expected) {
+        if (out->device_set_status == GMP_OK && n_cuda != n_expected && !(o.flags & GMP_PROBE_F_HOST_VIEW)) {
             set_error("CUDA sees %d devices, %d were mounted", n_cuda, n_expected);
             out->device_set_status = GMP_ERR_DEVICE_SET;
         }
@@ -365,6 +370,7 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
     j.raw("[");
     for (int i = 0; i < n; ++i) {
         const gmp_hbm_result& h = r->hbm[i];
+        if (h.uuid[0] == '\0' && h.status == GMP_OK) continue;  // step skipped (SKIP_HBM, NODES_ONLY): no entry
         j.sep();
         j.raw("{");
         j.kstr("uuid", h.uuid);
@@ -399,6 +405,7 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
     j.raw("[");
     for (int i = 0; i < n; ++i) {
         const gmp_gpu_health& h = r->health[i];
+        if (r->ns_cuda_init == 0) break;  // never got as far as sampling (NODES_ONLY, or a failed node check)
         auto opt32 = [](uint32_t v) { return v == UINT32_MAX ? -1ll : (long long)v; };
         auto opt64 = [](uint64_t v) { return v == UINT64_MAX ? -1ll : (long long)v; };
         j.sep();

@@ -138,6 +138,8 @@ void usage() {
             "       gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
             "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
             "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only] [--lib-baselines]\n"
+            "         [--nodes-only]  (device nodes + driver library only: no CUDA, a few ms)\n"
+            "         [--host-view]   (run from the host: CUDA may see more GPUs than the listed ones)\n"
             "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n"
             "Defaults may come from GPUMOUNTER_PROBE_BYTES / _ITERS / _PATTERNS / _SEED / _DMA_BYTES / _P2P_BYTES / _SKIP_P2P.\n");
 }
@@ -203,6 +205,8 @@ int main(int argc, char** argv) {
         else if (a == "--skip-hbm") o.flags |= GMP_PROBE_F_SKIP_HBM;
         else if (a == "--skip-p2p") o.flags |= GMP_PROBE_F_SKIP_P2P;
         else if (a == "--skip-nvml") o.flags |= GMP_PROBE_F_SKIP_NVML;
+        else if (a == "--nodes-only") o.flags |= GMP_PROBE_F_NODES_ONLY;
+        else if (a == "--host-view") o.flags |= GMP_PROBE_F_HOST_VIEW;
         else if (a == "--skip-copy") o.hbm.flags |= GMP_HBM_F_SKIP_COPY;
         else if (a == "--lib-baselines") o.hbm.flags |= GMP_HBM_F_LIB_BASELINES;
         else if (a == "--matrix-only") o.p2p.flags |= GMP_P2P_F_MATRIX_ONLY;

@@ -267,6 +267,7 @@ def probe_hbm(uuid: Optional[str] = None, *, nbytes: int = 0, iters: int = 0, pa
 GMP_P2P_CELLS = GMP_MAX_DEVICES * GMP_MAX_DEVICES
 P2P_F_KEEP_DEVICE, P2P_F_SKIP_BIDIR, P2P_F_SKIP_ALLTOALL, P2P_F_MATRIX_ONLY = 1, 2, 4, 8
 PROBE_F_SKIP_NODES, PROBE_F_SKIP_HBM, PROBE_F_SKIP_P2P, PROBE_F_SKIP_NVML, PROBE_F_KEEP_DEVICE = 1, 2, 4, 8, 16
+PROBE_F_NODES_ONLY, PROBE_F_HOST_VIEW = 32, 64
 
 
 class gmp_p2p_opts(ctypes.Structure):

@@ -434,7 +434,14 @@ enum {
     GMP_PROBE_F_SKIP_HBM   = 1u << 1,
     GMP_PROBE_F_SKIP_P2P   = 1u << 2,
     GMP_PROBE_F_SKIP_NVML  = 1u << 3,
-    GMP_PROBE_F_KEEP_DEVICE = 1u << 4
+    GMP_PROBE_F_KEEP_DEVICE = 1u << 4,
+    /* Stop after step 1 (device nodes + driver library): no CUDA, no NVML, a few ms.  What the worker runs INSIDE the
+     * pod when the kernels are run from its own resident process instead (GMP_PROBE_F_HOST_VIEW). */
+    GMP_PROBE_F_NODES_ONLY = 1u << 5,
+    /* The caller is not confined to the pod's device set - the worker itself, on the host, where CUDA sees every GPU
+     * of the node: each expected UUID must be visible to CUDA, but CUDA seeing MORE devices than expected is not an
+     * error.  With GMP_PROBE_F_KEEP_DEVICE in a long-lived process, cuInit and the primary contexts are paid once. */
+    GMP_PROBE_F_HOST_VIEW = 1u << 6
 };
 
 typedef struct gmp_report {

@@ -55,6 +55,24 @@ def test_missing_nodes_have_distinct_codes(tmp_path):
         assert rc in (-_lib.GMP_ERR_DRIVER_LIB, -_lib.GMP_ERR_UNAVAILABLE, -_lib.GMP_ERR_DEVICE_SET, 0) or HAS_GPU
 
 
+def test_nodes_only_stops_before_cuda(tmp_path):
+    """--nodes-only is the in-pod half of the two-stage hook (nodes checked in the pod, kernels run from the worker's
+    resident process): it never initialises CUDA, so its verdict does not depend on a driver being present."""
+    d = tmp_path / "dev"
+    d.mkdir()
+    for name in ("nvidiactl", "nvidia-uvm", "nvidia3"):
+        (d / name).write_text("")
+    rc, j, _ = run("--dev-dir", str(d), "--uuid", "GPU-x:3", "--uuid", "GPU-y:4", "--nodes-only")
+    assert rc == -_lib.GMP_ERR_NODE_GPU and j["nodes_status"] == _lib.GMP_ERR_NODE_GPU and "nvidia4" in j["detail"]
+    (d / "nvidia4").write_text("")
+    rc, j, _ = run("--dev-dir", str(d), "--uuid", "GPU-x:3", "--uuid", "GPU-y:4", "--nodes-only")
+    if rc == -_lib.GMP_ERR_DRIVER_LIB:  # no libcuda.so.1 on this machine: reported as such, still without CUDA
+        assert j["nodes_status"] == _lib.GMP_ERR_DRIVER_LIB and "libcuda.so.1" in j["detail"]
+    else:
+        assert rc == 0 and j["status"] == 0 and j["nodes_status"] == 0
+        assert [x["uuid"] for x in j["devices"]] == ["GPU-x", "GPU-y"] and j["hbm"] == [] and j["ms_cuda_init"] == 0
+
+
 @pytest.mark.skipif(HAS_GPU, reason="box has a GPU")
 def test_no_driver_is_reported_not_faked(tmp_path):
     rc, j, _ = run("--skip-nodes")

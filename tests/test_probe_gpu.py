@@ -167,6 +167,36 @@ def test_probe_all_rejects_a_wrong_device_set():
     assert l2.split()[:2] == [str(_lib.GMP_ERR_DEVICE_SET)] * 2 and "NVML says" in l2
 
 
+def test_host_view_accepts_a_subset_and_a_resident_process_gets_warm():
+    """The worker on the host sees every GPU of the node.  HOST_VIEW: probing a subset is fine, an unknown UUID is still
+    refused; with KEEP_DEVICE the second probe of a resident process pays neither cuInit nor a context."""
+    code = (
+        "import json,sys; sys.path.insert(0, %r)\n"
+        "from gpumounter_b200 import probe\n"
+        "nv = {d.uuid: d for d in probe.enumerate_nvml()}\n"
+        "cu = probe.enumerate_cuda()\n"
+        "one = [probe.Device(cu[0].uuid, nv[cu[0].uuid].minor, '', -1, -1)]\n"
+        "F = probe.PROBE_F_HOST_VIEW | probe.PROBE_F_SKIP_NODES | probe.PROBE_F_KEEP_DEVICE\n"
+        "out = []\n"
+        "for i in range(3):\n"
+        "    r = probe.probe_all(one, hbm_bytes=256<<20, hbm_iters=1, dma_bytes=1<<20, flags=F, raise_on_error=False)\n"
+        "    j = json.loads(probe.report_json(r))\n"
+        "    out.append([r.status, j['n_gpus'], j['ms_to_usable'], j['hbm'][0]['ms_context'], j['hbm'][0]['mismatch_lanes']])\n"
+        "bad = one + [probe.Device('GPU-00000000-0000-0000-0000-000000000000', None, '', -1, -1)]\n"
+        "r = probe.probe_all(bad, hbm_bytes=1<<20, flags=F, raise_on_error=False)\n"
+        "strict = probe.probe_all(one, hbm_bytes=1<<20, raise_on_error=False, flags=probe.PROBE_F_SKIP_NODES)\n"
+        "print(json.dumps({'runs': out, 'n_cuda': len(cu), 'bad': r.status, 'strict': strict.status}))\n" % ROOT
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    j = json.loads(out.stdout.strip().splitlines()[-1])
+    assert all(r[0] == 0 and r[1] == 1 and r[4] == 0 for r in j["runs"]), j
+    assert j["runs"][2][2] < 100 and j["runs"][2][3] < 20, j   # warm: ms to usable, ms for the context
+    assert j["bad"] == _lib.GMP_ERR_DEVICE_SET
+    # without HOST_VIEW a subset is a device-set mismatch (the in-pod rule); with one visible GPU the sets are equal
+    assert j["strict"] == (0 if j["n_cuda"] == 1 else _lib.GMP_ERR_DEVICE_SET)
+
+
 def test_probe_executable_on_the_box():
     exe = probe.probe_executable()
     p = subprocess.run([exe, "--bytes", "1G", "--iters", "1", "--p2p-bytes", "128M"], capture_output=True, text=True, timeout=600)

@@ -227,6 +227,53 @@ def to_usable(iters, hbm_bytes, n_gpus):
     return out
 
 
+def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts):
+    """Two-stage hook with a resident worker (this process stands in for it: on the host, sees every GPU, cuInit paid once at
+    start-up): native mount -> `gpumounter-probe --nodes-only` fexecve'd in the pod (device cgroup + mount namespace: the nodes
+    open there; no CUDA) -> gmp_probe_all(HOST_VIEW) in-process on the mounted GPUs.  keep_contexts: the worker retains the
+    primary contexts between calls (KEEP_DEVICE) or releases them (cudaDeviceReset) after each probe.
+    What this does NOT time is the tenant's own CUDA start-up in the pod - that is to_usable()."""
+    nv = {d.uuid: d for d in probe.enumerate_nvml()}
+    cu = probe.enumerate_cuda()[:n_gpus]  # cuInit happens here at the latest
+    gpus = [(d.uuid, nv[d.uuid].minor) for d in cu]
+    expected = [probe.Device(u, m, "", -1, -1) for u, m in gpus]
+    flags = probe.PROBE_F_HOST_VIEW | probe.PROBE_F_SKIP_NODES | (probe.PROBE_F_KEEP_DEVICE if keep_contexts else 0)
+    lat, phases = [], []
+    for it in range(iters + 1):  # iteration 0 warms the worker (first contexts, module load); not counted
+        with harness.Target() as t:
+            for name in ("nvidiactl", "nvidia-uvm"):
+                mknod_like(f"/dev/{name}", f"/proc/{t.pid}/root{t.devdir}/{name}")
+            recs = [device.New(m, u) for u, m in gpus]
+            pod, env = product_pod(), env_of(t)
+            t0 = time.monotonic_ns()
+            util.MountGPUs(pod, recs, env)
+            t_mounted = time.monotonic_ns()
+            rc, nodes = util.ProbeInPod(pod, recs, ["--dev-dir", t.devdir, "--nodes-only"], env, raise_on_error=False)
+            t_nodes = time.monotonic_ns()
+            assert rc == 0 and nodes.get("status") == 0 and nodes.get("nodes_status") == 0, nodes
+            r = probe.probe_all(expected, hbm_bytes=hbm_bytes, hbm_iters=1, dma_bytes=16 << 20, p2p_bytes=256 << 20, p2p_iters=1,
+                                flags=flags, raise_on_error=False)
+            t_done = time.monotonic_ns()
+            assert r.status == 0, r.detail
+            rep = json.loads(probe.report_json(r))
+            util.UnmountGPUs(pod, recs, False, env)
+            if it == 0:
+                continue
+            lat.append((rep["mono_usable_ns"] - t0) / 1e9)
+            phases.append({"mount_ms": (t_mounted - t0) / 1e6, "nodes_only_in_pod_ms": (t_nodes - t_mounted) / 1e6,
+                           "probe_start_to_usable_ms": rep["ms_to_usable"], "context_ms": max(h["ms_context"] for h in rep["hbm"]),
+                           "alloc_ms": max(h["ms_alloc"] for h in rep["hbm"]),
+                           "first_kernel_ms": max(h["ms_first_kernel"] for h in rep["hbm"]),
+                           "full_probe_ms": (t_done - t_nodes) / 1e6})
+    if keep_contexts:
+        # hand the contexts back: one last probe without KEEP_DEVICE resets every device it touched
+        probe.probe_all(expected, hbm_bytes=1 << 20, hbm_iters=1, dma_bytes=0,
+                        flags=probe.PROBE_F_HOST_VIEW | probe.PROBE_F_SKIP_NODES | probe.PROBE_F_SKIP_P2P, raise_on_error=False)
+    return {"gpus": len(gpus), "hbm_bytes_per_gpu": hbm_bytes, "iters": iters, "contexts_retained": keep_contexts,
+            "p50_s": statistics.median(lat), "p99_s": pct(lat, 0.99), "min_s": min(lat), "max_s": max(lat),
+            "median_phases_ms": {k: statistics.median(p[k] for p in phases) for k in phases[0]}}
+
+
 def churn_real(rounds, hbm_bytes=256 << 20):
     """Config 5 on real GPUs: 1 -> N -> 1 mounted GPUs, `rounds` times.  Every step: native mount, in-pod probe (HBM only),
     native unmount, in-pod check that the nodes are gone, and NVML's process list of every touched GPU back to its
@@ -276,9 +323,14 @@ def main():
     ap.add_argument("--churn-rounds", type=int, default=100)
     ap.add_argument("--usable-iters", type=int, default=0, help="> 0 only on a box with real GPUs")
     ap.add_argument("--usable-bytes", type=int, default=1 << 30)
+    ap.add_argument("--resident-iters", type=int, default=0,
+                    help="> 0 only on a box with real GPUs: two-stage hook, kernels run from this (resident) process")
     ap.add_argument("--churn-real-rounds", type=int, default=0, help="> 0 only on a box with real GPUs")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
+    # same context-size setting gpumounter-probe gives itself (probe_main.cpp); must precede this process's cuInit
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "1")
+    os.environ.setdefault("CUDA_DEVICE_MAX_COPY_CONNECTIONS", "1")
     why = harness.can_run()
     if why:
         print(json.dumps({"unavailable": why}))
@@ -326,6 +378,12 @@ def main():
         n_vis = len(probe.enumerate_cuda())
         out["mount_to_usable"] = {str(n): to_usable(args.usable_iters, args.usable_bytes, n)
                                   for n in (1, 2, 4, 8) if n <= n_vis}
+    if args.resident_iters > 0 and have_gpu:
+        n_vis = len(probe.enumerate_cuda())
+        out["mount_to_usable_resident_worker"] = {
+            mode: {str(n): to_usable_resident(args.resident_iters, args.usable_bytes, n, keep)
+                   for n in (1, 2, 4, 8) if n <= n_vis}
+            for mode, keep in (("contexts_released", False), ("contexts_retained", True))}
     if args.churn_real_rounds > 0 and have_gpu:
         out["churn_real"] = churn_real(args.churn_real_rounds)
     text = json.dumps(out)
