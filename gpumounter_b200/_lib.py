@@ -34,6 +34,7 @@ GMP_ERR_NODE_GPU = -20
 GMP_ERR_NODE_DENIED = -21
 GMP_ERR_DRIVER_LIB = -22
 GMP_ERR_STILL_MOUNTED = -23
+GMP_ERR_UNSUPPORTED = -24
 
 
 class ProbeError(RuntimeError):

@@ -28,7 +28,11 @@ class gmp_pod(ctypes.Structure):
 
 class gmp_mount_env(ctypes.Structure):
     _fields_ = [("devices_root", ctypes.c_char_p), ("dev_prefix", ctypes.c_char_p),
-                ("cgroup_driver", ctypes.c_char_p), ("proc_root", ctypes.c_char_p)]
+                ("cgroup_driver", ctypes.c_char_p), ("proc_root", ctypes.c_char_p),
+                ("cgroup2_root", ctypes.c_char_p), ("extensions", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
+
+
+EXT_CRI_RUNTIMES, EXT_CGROUP_V2 = 1, 2  # GMP_EXT_*: off by default (section 7 of the header)
 
 
 class gmp_ns_config(ctypes.Structure):
@@ -108,9 +112,12 @@ class MountEnv:
     dev_prefix: Optional[str] = None
     cgroup_driver: Optional[str] = None
     proc_root: Optional[str] = None
+    cgroup2_root: Optional[str] = None
+    extensions: int = 0
 
     def to_c(self):
-        return gmp_mount_env(enc(self.devices_root), enc(self.dev_prefix), enc(self.cgroup_driver), enc(self.proc_root))
+        return gmp_mount_env(enc(self.devices_root), enc(self.dev_prefix), enc(self.cgroup_driver), enc(self.proc_root),
+                             enc(self.cgroup2_root), self.extensions, 0)
 
 
 def env_ptr(env: Optional[MountEnv]):

@@ -53,6 +53,14 @@ def GetCgroupName(cgroupDriver: str, pod: Pod, containerID: str) -> str:  # ref:
     return buf.value.decode()
 
 
+def GetCgroupNameOfPod(pod: Pod, env: Optional[MountEnv] = None) -> str:
+    """ref: util.go:21-34: strip "docker://", read the driver, GetCgroupName - what MountGPU resolves first."""
+    buf = ctypes.create_string_buffer(4096)
+    c = pod.to_c()
+    check(lib().gmp_get_pod_cgroup_path(env_ptr(env), ctypes.byref(c), buf, 4096), "gmp_get_pod_cgroup_path")
+    return buf.value.decode()
+
+
 def GetDeviceGroupPath(cgroupPath: str, env: Optional[MountEnv] = None) -> str:  # ref: cgroup.go:115-118
     buf = ctypes.create_string_buffer(8192)
     check(lib().gmp_get_device_group_path(env_ptr(env), cgroupPath.encode(), buf, 8192), "GetDeviceGroupPath")

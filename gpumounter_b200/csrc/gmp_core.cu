@@ -151,6 +151,7 @@ extern "C" const char* gmp_strerror(int code) {
         case GMP_ERR_NODE_DENIED: return "GPU device node not openable (device cgroup)";
         case GMP_ERR_DRIVER_LIB: return "libcuda.so.1 not found";
         case GMP_ERR_STILL_MOUNTED: return "device node still present after unmount";
+        case GMP_ERR_UNSUPPORTED: return "cgroup device program is not in the canonical block form";
         default: return "unknown error";
     }
 }

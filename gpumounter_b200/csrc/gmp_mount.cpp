@@ -69,7 +69,14 @@ void put(char (&dst)[N], const std::string& s) {
 
 const char* or_default(const char* v, const char* d) { return (v != nullptr && v[0] != '\0') ? v : d; }
 
-std::string devices_root(const gmp_mount_env* env) { return or_default(env ? env->devices_root : nullptr, kDevicesRoot); }
+bool extension_on(const gmp_mount_env* env, uint32_t bit) { return env != nullptr && (env->extensions & bit) != 0; }
+
+// Where the pod's cgroup directory lives: the v1 `devices` hierarchy (ref: cgroup.go:116), or, with GMP_EXT_CGROUP_V2
+// (section 7 of the header, no reference counterpart), the unified hierarchy.
+std::string devices_root(const gmp_mount_env* env) {
+    if (extension_on(env, GMP_EXT_CGROUP_V2)) return or_default(env->cgroup2_root, "/sys/fs/cgroup");
+    return or_default(env ? env->devices_root : nullptr, kDevicesRoot);
+}
 std::string dev_prefix(const gmp_mount_env* env) { return or_default(env ? env->dev_prefix : nullptr, kDevPrefix); }
 std::string proc_root(const gmp_mount_env* env) { return or_default(env ? env->proc_root : nullptr, "/proc"); }
 
@@ -268,7 +275,8 @@ int cgroup_driver(const gmp_mount_env* env, std::string* out) {
     return GMP_OK;
 }
 
-int cgroup_name(const std::string& driver, const gmp_pod* pod, const std::string& container_id, std::string* out) {
+int cgroup_name(const std::string& driver, const gmp_pod* pod, const std::string& container_id, std::string* out,
+                const char* scope_prefix = "docker-", const char* cgroupfs_prefix = "") {
     int qos = 0;
     int rc = pod_qos(pod, &qos);
     if (rc != GMP_OK) return rc;
@@ -285,11 +293,11 @@ int cgroup_name(const std::string& driver, const gmp_pod* pod, const std::string
         std::string base;
         rc = to_systemd(parts, &base);
         if (rc != GMP_OK) return rc;
-        *out = base + "/docker-" + container_id + ".scope";  // ref: cgroup.go:106
+        *out = base + "/" + scope_prefix + container_id + ".scope";  // "docker-", ref: cgroup.go:106
         return GMP_OK;
     }
     if (driver == "cgroupfs") {
-        *out = to_cgroupfs(parts) + "/" + container_id;  // ref: cgroup.go:108
+        *out = to_cgroupfs(parts) + "/" + cgroupfs_prefix + container_id;  // ref: cgroup.go:108
         return GMP_OK;
     }
     set_error("unsupported cgroup driver");  // ref: cgroup.go:112
@@ -311,6 +319,19 @@ int pod_cgroup_path(const gmp_mount_env* env, const gmp_pod* pod, std::string* o
     std::string driver;
     int rc = cgroup_driver(env, &driver);  // ref: util.go:25-29
     if (rc != GMP_OK) return rc;
+    if (extension_on(env, GMP_EXT_CRI_RUNTIMES)) {
+        // kubelet reports "<runtime>://<id>"; the reference only knows dockershim.  Leaf names as the runtimes create
+        // them: containerd "cri-containerd-<id>.scope" / "<id>", CRI-O "crio-<id>.scope" / "crio-<id>".
+        const std::string id = pod->container_id;
+        const struct {
+            const char* scheme;
+            const char* scope_prefix;
+            const char* cgroupfs_prefix;
+        } runtimes[] = {{"containerd://", "cri-containerd-", ""}, {"cri-o://", "crio-", "crio-"}};
+        for (const auto& r : runtimes)
+            if (id.compare(0, strlen(r.scheme), r.scheme) == 0)
+                return cgroup_name(driver, pod, id.substr(strlen(r.scheme)), out, r.scope_prefix, r.cgroupfs_prefix);
+    }
     return cgroup_name(driver, pod, strip_docker_scheme(pod->container_id), out);  // ref: util.go:30-34
 }
 
@@ -335,6 +356,17 @@ int read_cgroup_pids(const gmp_mount_env* env, const std::string& cgroup_path, s
 }
 
 int write_permission(const gmp_mount_env* env, const std::string& cgroup_path, int minor, const char* file_name) {
+    if (extension_on(env, GMP_EXT_CGROUP_V2)) {
+        // no devices.allow / devices.deny on the unified hierarchy: edit the device program(s) attached to the cgroup
+        gmp_dev_rule rule;
+        rule.type = GMP_DEV_CHAR;
+        rule.major = GMP_NVIDIA_MAJOR;
+        rule.minor = minor;
+        rule.access = GMP_DEV_ACC_READ | GMP_DEV_ACC_WRITE;  // "rw", ref: nvidia.go:38
+        rule.allow = 1;
+        const std::string dir = devices_root(env) + cgroup_path;
+        return gmp_cgroup2_update_devices(dir.c_str(), &rule, 1, strcmp(file_name, "devices.allow") == 0, nullptr);
+    }
     const std::string file = devices_root(env) + cgroup_path + "/" + file_name;
     // what `echo '...' > file` does: O_WRONLY|O_CREAT|O_TRUNC and a trailing newline
     const int fd = open(file.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0666);
@@ -786,6 +818,14 @@ extern "C" int gmp_get_cgroup_name(const char* driver, const gmp_pod* pod, const
         REQUIRE(driver != nullptr && pod != nullptr && container_id != nullptr);
         std::string s;
         int rc = cgroup_name(driver, pod, container_id, &s);
+        return rc != GMP_OK ? rc : emit(s, out, cap);
+    });
+}
+
+extern "C" int gmp_get_pod_cgroup_path(const gmp_mount_env* env, const gmp_pod* pod, char* out, size_t cap) {
+    return guarded([&]() -> int {
+        std::string s;
+        int rc = pod_cgroup_path(env, pod, &s);
         return rc != GMP_OK ? rc : emit(s, out, cap);
     });
 }

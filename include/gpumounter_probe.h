@@ -73,7 +73,8 @@ enum {
     GMP_ERR_NODE_GPU         = -20, /* /dev/nvidiaN missing */
     GMP_ERR_NODE_DENIED      = -21, /* /dev/nvidiaN exists but open() is refused (device cgroup) */
     GMP_ERR_DRIVER_LIB       = -22, /* libcuda.so.1 not resolvable from the probing context */
-    GMP_ERR_STILL_MOUNTED    = -23  /* after an unmount: the device node is still there (or still opens) in the pod */
+    GMP_ERR_STILL_MOUNTED    = -23, /* after an unmount: the device node is still there (or still opens) in the pod */
+    GMP_ERR_UNSUPPORTED      = -24  /* section 7: a cgroup-v2 device program that is not in the canonical block form */
 };
 
 GMP_API int         gmp_abi_version(void);
@@ -552,8 +553,15 @@ typedef struct gmp_mount_env {
     const char* dev_prefix;     /* "/dev/nvidia", ref: nvidia.go:40 */
     const char* cgroup_driver;  /* overrides $CGROUP_DRIVER when not NULL */
     const char* proc_root;      /* "/proc": where <pid>/ns/mnt is looked up */
+    const char* cgroup2_root;   /* "/sys/fs/cgroup": the unified hierarchy, used with GMP_EXT_CGROUP_V2 (section 7) */
+    uint32_t    extensions;     /* GMP_EXT_* bits (section 7); 0 = exactly the reference's behaviour */
+    uint32_t    reserved;
 } gmp_mount_env;
 
+/* ref: util.go:21-34 (the first steps of MountGPU / UnmountGPU): container id of ContainerStatuses[0] with
+ * "docker://" removed, $CGROUP_DRIVER, then GetCgroupName.  The one place where gmp_mount_env.extensions
+ * (GMP_EXT_CRI_RUNTIMES, section 7) changes the answer. */
+GMP_API int gmp_get_pod_cgroup_path(const gmp_mount_env* env, const gmp_pod* pod, char* out, size_t cap);
 /* ref: cgroup.go:115-118 GetDeviceGroupPath */
 GMP_API int gmp_get_device_group_path(const gmp_mount_env* env, const char* cgroup_path, char* out, size_t cap);
 /* ref: cgroup.go:120-141 GetCgroupPIDs: the lines of cgroup.procs that end in '\n' (a last
@@ -647,6 +655,77 @@ GMP_API int gmp_get_remove_gpu(const gmp_gpu* list, int n, const char* owner_nam
                                const char* const* uuids, int n_uuids, int32_t* indices, int* count);
 /* ref: allocator.go:191-199: "<owner>-slave-pod-<6 hex>" from three random bytes */
 GMP_API int gmp_slave_pod_name(const char* owner, const unsigned char rand3[3], char* out, size_t cap);
+
+/* ---- 7. Extensions beyond the reference -----------------------------------
+ *
+ * Nothing in this section has a reference counterpart: the reference only knows dockershim container ids and the
+ * cgroup-v1 `devices` controller (ref: pkg/util/cgroup/cgroup.go:104-108,115-118,143-169), so on a node with
+ * containerd / CRI-O or the unified cgroup hierarchy its mount path resolves a directory that does not exist.
+ * Everything here is OFF unless asked for through gmp_mount_env.extensions; with extensions == 0 the mount path
+ * behaves exactly as the reference does (including for container ids it does not understand).
+ */
+enum {
+    /* "containerd://<id>" and "cri-o://<id>" container ids: scheme stripped like "docker://"; systemd scope
+     * "cri-containerd-<id>.scope" / "crio-<id>.scope", cgroupfs leaf "<id>" / "crio-<id>". */
+    GMP_EXT_CRI_RUNTIMES = 1u << 0,
+    /* Unified hierarchy: the pod's cgroup lives under gmp_mount_env.cgroup2_root ("/sys/fs/cgroup") and device
+     * access is decided by BPF_PROG_TYPE_CGROUP_DEVICE programs, not devices.allow / devices.deny files. */
+    GMP_EXT_CGROUP_V2    = 1u << 1
+};
+
+/* One rule of a cgroup device filter; the values are the kernel's (BPF_DEVCG_DEV_*, BPF_DEVCG_ACC_*). */
+enum { GMP_DEV_BLOCK = 1, GMP_DEV_CHAR = 2 };
+enum { GMP_DEV_ACC_MKNOD = 1, GMP_DEV_ACC_READ = 2, GMP_DEV_ACC_WRITE = 4, GMP_DEV_ACC_ALL = 7 };
+typedef struct gmp_dev_rule {
+    int32_t  type;    /* GMP_DEV_CHAR or GMP_DEV_BLOCK */
+    int32_t  major;   /* -1 = any */
+    int32_t  minor;   /* -1 = any */
+    uint32_t access;  /* GMP_DEV_ACC_* bits this rule covers; a request matches when all of ITS bits are covered */
+    int32_t  allow;   /* 1 = allow, 0 = deny */
+} gmp_dev_rule;
+
+/* struct bpf_insn, spelled out so that callers need no kernel header: regs = dst_reg | src_reg << 4. */
+typedef struct gmp_bpf_insn { uint8_t code; uint8_t regs; int16_t off; int32_t imm; } gmp_bpf_insn;
+
+/*
+ * Rules -> program, in the block form runc emits (opencontainers/runc libcontainer/cgroups/devices/devicefilter.go,
+ * v1.0.0-rc93 and later; third-party, not in the reference tree): a 6-instruction prologue loads type, access,
+ * major and minor into r2..r5; then one block per rule, LAST rule first (so the last matching rule of the list
+ * wins), each block comparing only what the rule restricts and ending in "r0 = allow; exit"; finally
+ * "r0 = default_allow; exit".  GMP_ERR_INVALID for a rule with an unknown type or no access bits,
+ * GMP_ERR_BUFFER_TOO_SMALL with *n_insns = the size needed.
+ */
+GMP_API int gmp_devfilter_build(const gmp_dev_rule* rules, int n_rules, int default_allow,
+                                gmp_bpf_insn* insns, int cap, int* n_insns);
+/* Program -> rules (in list order, i.e. the reverse of block order).  GMP_ERR_UNSUPPORTED for anything that is
+ * not exactly the block form above (for example a program written by crun). */
+GMP_API int gmp_devfilter_decode(const gmp_bpf_insn* insns, int n_insns, gmp_dev_rule* rules, int cap,
+                                 int* n_rules, int* default_allow);
+/* Runs a device program on one request the way the kernel would (ALU, ALU64, JMP, JMP32, LDX from the 12-byte
+ * context; no calls, no maps; at most 65536 steps).  *allowed = r0 != 0.  GMP_ERR_UNSUPPORTED for any other
+ * instruction, GMP_ERR_INVALID for a jump or load out of range. */
+GMP_API int gmp_devfilter_eval(const gmp_bpf_insn* insns, int n_insns, int type, uint32_t access,
+                               uint32_t major, uint32_t minor, int* allowed);
+
+/* The device programs attached to one cgroup-v2 directory (BPF_PROG_QUERY, not the effective set of its
+ * ancestors).  *attach_flags receives the kernel's flags for that attachment (BPF_F_ALLOW_MULTI = 2 for runc). */
+GMP_API int gmp_cgroup2_device_programs(const char* cgroup_dir, uint32_t* prog_ids, int cap, int* n,
+                                        uint32_t* attach_flags);
+/* The instructions of a loaded program, by id (BPF_OBJ_GET_INFO_BY_FD, translated form: identical to what was
+ * loaded for programs of this type, which use no maps and no calls). */
+GMP_API int gmp_cgroup2_read_program(uint32_t prog_id, gmp_bpf_insn* insns, int cap, int* n_insns);
+/* Attach a program built from `rules` to a cgroup that has none (what a runtime does at container start; used by
+ * the tests and the harness to play the runtime's part). */
+GMP_API int gmp_cgroup2_attach_rules(const char* cgroup_dir, const gmp_dev_rule* rules, int n_rules, int default_allow);
+/*
+ * The v2 counterpart of writing devices.allow / devices.deny: every device program attached to `cgroup_dir` is
+ * decoded, edited and atomically replaced (BPF_F_REPLACE).  grant != 0: append "allow" rules (earlier rules they
+ * shadow are dropped).  grant == 0: remove exactly the allow rules a previous grant appended; where there is none
+ * (the runtime itself had granted the device) append a deny rule instead.  A cgroup with no device program is
+ * unrestricted at that level: nothing to do, *programs = 0.  GMP_ERR_UNSUPPORTED leaves everything untouched.
+ */
+GMP_API int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_rule* rules, int n_rules, int grant,
+                                       int* programs);
 
 #ifdef __cplusplus
 }

@@ -3,7 +3,9 @@
 A `Target` is a process in its OWN mount namespace with a private tmpfs mounted on a scratch "dev" directory, so a
 device node created for it is visible only through /proc/<pid>/root — the same situation as a container whose /dev
 the host cannot see.  Its device cgroup is either a scratch directory tree with a hand-written cgroup.procs (always
-available) or a real cgroup-v1 `devices` group (when /sys/fs/cgroup/devices is writable).
+available), a real cgroup-v1 `devices` group (when /sys/fs/cgroup/devices is writable), or - `cgroup2=True` - a real
+cgroup-v2 directory with the device program a container runtime would have attached at start (runc's default allow
+list, built and attached by oracle/gmo_devfilter.py, not by the library under test).
 """
 
 from __future__ import annotations
@@ -31,8 +33,14 @@ def can_run() -> Optional[str]:
     return None
 
 
+def can_run_cgroup2() -> Optional[str]:
+    from oracle import gmo_devfilter
+
+    return can_run() or (gmo_devfilter.kernel_available() or None)
+
+
 class Target:
-    def __init__(self, real_cgroup: bool = False, qos_dir: str = "besteffort"):
+    def __init__(self, real_cgroup: bool = False, qos_dir: str = "besteffort", cgroup2: bool = False, runtime_rules=None):
         self.base = tempfile.mkdtemp(prefix="gmp_target_")
         self.devdir = os.path.join(self.base, "dev")
         os.mkdir(self.devdir)
@@ -40,7 +48,14 @@ class Target:
         self.cgroup_path = f"/kubepods/{qos_dir}/pod{UID}/{CID}" if qos_dir else f"/kubepods/pod{UID}/{CID}"
         self.proc = None
         self.extra: List[subprocess.Popen] = []
-        if real_cgroup:
+        self.cgroup2 = cgroup2
+        self.runtime_rules = runtime_rules
+        if cgroup2:
+            from oracle import gmo_devfilter
+
+            self.real_cgroup = True
+            self.devices_root = f"{gmo_devfilter.cgroup2_mount()}/gmp-{uuidlib.uuid4().hex[:8]}"
+        elif real_cgroup:
             self.devices_root = f"/sys/fs/cgroup/devices/gmp-{uuidlib.uuid4().hex[:8]}"
         else:
             self.devices_root = os.path.join(self.base, "cgroup_devices")
@@ -49,6 +64,11 @@ class Target:
     # ---- lifecycle ------------------------------------------------------------------------------------------
     def start(self) -> "Target":
         os.makedirs(self.cgroup_dir)
+        if self.cgroup2:
+            from oracle import gmo_devfilter
+
+            rules = gmo_devfilter.RUNC_DEFAULT_RULES if self.runtime_rules is None else self.runtime_rules
+            gmo_devfilter.kernel_attach_rules(self.cgroup_dir, rules)
         script = f"mount -t tmpfs -o mode=755 tmpfs {self.devdir} && echo ready && exec sleep 600"
         self.proc = subprocess.Popen(["unshare", "-m", "--propagation", "private", "sh", "-c", script],
                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
@@ -124,6 +144,18 @@ class Target:
 
     def nodes(self) -> List[str]:
         return sorted(os.listdir(f"/proc/{self.pid}/root{self.devdir}"))
+
+    def try_open(self, minor: int, flags: int = os.O_RDWR) -> int:
+        """errno of open(2) on the target's node for `minor`, attempted by a fresh process that first joins the target's
+        cgroup (so the cgroup's device filter judges it): 0 = opened, EPERM = the filter refused, ENXIO/ENODEV = the
+        filter let it through and no driver answered (this box has none), ENOENT = no node."""
+        code = (f"import os\nopen({os.path.join(self.cgroup_dir, 'cgroup.procs')!r}, 'w').write(str(os.getpid()))\n"
+                f"try:\n    os.close(os.open({self.node_path_in_target(minor)!r}, {flags}))\n    print(0)\n"
+                f"except OSError as e:\n    print(e.errno)\n")
+        import sys
+
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=30)
+        return int(out.stdout.strip())
 
     def host_sees(self) -> List[str]:
         return sorted(os.listdir(self.devdir))

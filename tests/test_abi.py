@@ -100,11 +100,12 @@ def test_python_struct_mirrors_match_the_compiled_sizes(tmp_path):
     """ctypes mirrors in probe.py / _model.py against sizeof() as the C compiler sees the header."""
     import subprocess
 
-    from gpumounter_b200 import _model
+    from gpumounter_b200 import _model, cgroup2
 
     names = ["gmp_device", "gmp_verify_result", "gmp_hbm_opts", "gmp_hbm_result", "gmp_p2p_opts", "gmp_p2p_result",
              "gmp_probe_opts", "gmp_report", "gmp_gpu", "gmp_pod", "gmp_container_resources", "gmp_mount_env", "gmp_ns_config",
-             "gmp_process_info", "gmp_gpu_health", "gmp_container_devices", "gmp_container_entry", "gmp_pod_resources"]
+             "gmp_process_info", "gmp_gpu_health", "gmp_container_devices", "gmp_container_entry", "gmp_pod_resources",
+             "gmp_dev_rule", "gmp_bpf_insn"]
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include "gpumounter_probe.h"\nint main(void) {\n' +
                    "".join(f'  printf("{n} %zu\\n", sizeof({n}));\n' for n in names) + "  return 0;\n}\n")
@@ -112,5 +113,5 @@ def test_python_struct_mirrors_match_the_compiled_sizes(tmp_path):
     subprocess.run(["gcc", f"-I{ROOT}/include", str(src), "-o", str(exe)], check=True)
     sizes = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
     for n in names:
-        mirror = getattr(probe, n, None) or getattr(_model, n)
+        mirror = getattr(probe, n, None) or getattr(_model, n, None) or getattr(cgroup2, n)
         assert ctypes.sizeof(mirror) == int(sizes[n]), (n, ctypes.sizeof(mirror), sizes[n])

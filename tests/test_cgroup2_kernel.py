@@ -1,0 +1,187 @@
+"""cgroup-v2 extension against the real kernel (header section 7; no reference counterpart): device programs are loaded,
+attached, read back, edited and ENFORCED on a scratch cgroup of this machine's unified hierarchy.  Skipped where there
+is no writable cgroup2 mount or bpf(2) is refused.  The "runtime's" program is always attached by the independent
+Python side (oracle/gmo_devfilter.py), the library under test only ever edits it."""
+
+import errno
+import os
+
+import pytest
+
+from gpumounter_b200 import ProbeError, _lib, cgroup2 as c, device, util
+from gpumounter_b200._model import EXT_CGROUP_V2, EXT_CRI_RUNTIMES, MountEnv, Pod
+from oracle import gmo_devfilter as o
+from tests import harness
+from tests.conftest import FAKE_UUIDS
+
+why = harness.can_run_cgroup2()
+pytestmark = pytest.mark.skipif(why is not None, reason=f"cgroup2 kernel path not testable here: {why}")
+
+NO_DRIVER = (errno.ENXIO, errno.ENODEV)  # open() got past the device filter and found no driver behind the node
+
+
+def env_of(t, ext=EXT_CGROUP_V2):
+    return MountEnv(cgroup2_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs", extensions=ext)
+
+
+def product_pod(cid="docker://" + harness.CID):
+    return Pod("gpu-pod", uid=harness.UID, container_id=cid)
+
+
+def attached(t):
+    ids, flags = c.device_programs(t.cgroup_dir)
+    return [c.read_program(i) for i in ids], flags
+
+
+def test_runtime_program_reads_back_exactly_and_decodes(fake_nvml):
+    with harness.Target(cgroup2=True) as t:
+        progs, flags = attached(t)
+        assert flags == 2 and len(progs) == 1                      # BPF_F_ALLOW_MULTI, as runc attaches
+        assert progs[0] == o.runc_program(o.RUNC_DEFAULT_RULES)    # translated form == loaded form for this program type
+        rules, default = c.decode(progs[0])
+        assert [(r.type, r.major, r.minor, r.access, r.allow) for r in rules] == o.RUNC_DEFAULT_RULES and default is False
+
+
+def test_mount_and_unmount_on_the_unified_hierarchy_are_enforced_by_the_kernel(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        env, pod = env_of(t), product_pod()
+        baseline, _ = attached(t)
+        gpus = [device.New(m, u) for u, m, _ in gpus_cfg]
+        # a node alone is not access: made by hand (the runtime's wildcard 'm' rule allows mknod), open is refused
+        os.mknod(t.node_path_in_target(3), 0o666 | 0o020000, os.makedev(195, 3))
+        assert t.try_open(3) == errno.EPERM
+        os.unlink(t.node_path_in_target(3))
+        assert util.MountGPUs(pod, gpus[:2], env) == 2
+        m0, m1 = gpus[0].MinorNumber, gpus[1].MinorNumber
+        assert t.node(m0) == (195, m0, 0o666) and t.node(m1) == (195, m1, 0o666)
+        assert t.try_open(m0) in NO_DRIVER and t.try_open(m1) in NO_DRIVER       # the filter lets them through now
+        other = gpus[2].MinorNumber
+        os.mknod(t.node_path_in_target(other), 0o666 | 0o020000, os.makedev(195, other))
+        assert t.try_open(other) == errno.EPERM                                  # ... and only them
+        os.unlink(t.node_path_in_target(other))
+        assert t.try_open(3 if 3 not in (m0, m1) else 4) == errno.ENOENT
+        progs, flags = attached(t)
+        assert flags == 2 and len(progs) == 1
+        rules, _ = c.decode(progs[0])
+        assert rules[-2:] == [c.gpu_rule(m0), c.gpu_rule(m1)] and len(rules) == len(o.RUNC_DEFAULT_RULES) + 2
+        # unmount one: its node goes, its rule goes, the other GPU keeps working
+        assert util.UnmountGPUs(pod, gpus[:1], False, env) == 1
+        assert t.node(m0) is None and t.try_open(m1) in NO_DRIVER
+        os.mknod(t.node_path_in_target(m0), 0o666 | 0o020000, os.makedev(195, m0))
+        assert t.try_open(m0) == errno.EPERM
+        os.unlink(t.node_path_in_target(m0))
+        # unmount the other: the program is byte for byte what the runtime attached ("devices.list back to baseline")
+        assert util.UnmountGPUs(pod, gpus[1:2], False, env) == 1
+        assert attached(t)[0] == baseline and t.nodes() == []
+
+
+def test_churn_does_not_grow_the_program(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        env, pod = env_of(t), product_pod()
+        gpus = [device.New(m, u) for u, m, _ in gpus_cfg]
+        baseline, _ = attached(t)
+        fds0 = len(os.listdir("/proc/self/fd"))
+        for k in list(range(1, 9)) + list(range(7, 0, -1)):
+            util.MountGPUs(pod, gpus[:k], env)
+            assert len(c.decode(attached(t)[0][0])[0]) == len(o.RUNC_DEFAULT_RULES) + k
+            util.UnmountGPUs(pod, gpus[:k], False, env)
+            assert attached(t)[0] == baseline
+        assert len(os.listdir("/proc/self/fd")) == fds0
+
+
+def test_grant_twice_is_idempotent_and_revoke_of_a_runtime_granted_device_denies(fake_nvml):
+    fake_nvml()
+    runtime = o.RUNC_DEFAULT_RULES + [(o.DEV_CHAR, 195, 5, o.ACC_ALL, True)]   # the pod was STARTED with GPU 5
+    with harness.Target(cgroup2=True, runtime_rules=runtime) as t:
+        os.mknod(t.node_path_in_target(5), 0o666 | 0o020000, os.makedev(195, 5))
+        assert t.try_open(5) in NO_DRIVER
+        before = attached(t)[0]
+        assert c.update_devices(t.cgroup_dir, [c.gpu_rule(7)], True) == 1
+        once = attached(t)[0]
+        assert c.update_devices(t.cgroup_dir, [c.gpu_rule(7)], True) == 1
+        assert attached(t)[0] == once != before
+        assert c.update_devices(t.cgroup_dir, [c.gpu_rule(7)], False) == 1
+        assert attached(t)[0] == before
+        # revoking what the runtime itself granted cannot be done by removing a rule of ours: a deny rule goes on top
+        assert c.update_devices(t.cgroup_dir, [c.gpu_rule(5)], False) == 1
+        rules, _ = c.decode(attached(t)[0][0])
+        assert rules[-1] == c.Rule(c.DEV_CHAR, 195, 5, c.ACC_READ | c.ACC_WRITE, False)
+        assert t.try_open(5) == errno.EPERM and t.try_open(5, os.O_RDONLY) == errno.EPERM
+        # and granting it again takes the deny rule away instead of stacking another allow on it
+        assert c.update_devices(t.cgroup_dir, [c.gpu_rule(5)], True) == 1
+        rules, _ = c.decode(attached(t)[0][0])
+        assert rules[-1] == c.gpu_rule(5) and len(rules) == len(runtime) + 1
+        assert t.try_open(5) in NO_DRIVER
+
+
+def test_foreign_program_is_left_alone(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        # a second program in a layout the decoder does not know (what crun or systemd would attach): "r0 = 1; exit"
+        fd = o.kernel_load([(0xB7, 0, 0, 0, 1), (0x95, 0, 0, 0, 0)])
+        o.kernel_attach(t.cgroup_dir, fd)
+        os.close(fd)
+        before = attached(t)
+        assert len(before[0]) == 2
+        u, m, _ = gpus_cfg[0]
+        with pytest.raises(ProbeError) as e:
+            util.MountGPU(product_pod(), device.New(m, u), env_of(t))
+        assert e.value.code == _lib.GMP_ERR_UNSUPPORTED and "canonical block form" in e.value.detail
+        assert attached(t) == before and t.nodes() == []          # nothing half done: no rule edited, no node made
+
+
+def test_cgroup_without_a_device_program_is_unrestricted(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        bare = os.path.join(t.devices_root, "bare")
+        os.mkdir(bare)
+        try:
+            assert c.device_programs(bare) == ([], 0)
+            assert c.update_devices(bare, [c.gpu_rule(0)], True) == 0
+            assert c.device_programs(bare) == ([], 0)
+        finally:
+            os.rmdir(bare)
+        with pytest.raises(ProbeError) as e:
+            c.device_programs(os.path.join(t.devices_root, "missing"))
+        assert e.value.code == _lib.GMP_ERR_SYS
+
+
+def test_in_pod_probe_joins_the_v2_cgroup(fake_nvml, tmp_path):
+    """gmp_probe_in_pod writes the child into <cgroup2_root><path>/cgroup.procs before it execs the probe: the script
+    below stands in for gpumounter-probe and reports which v2 cgroup it runs in and what open() says."""
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        env, pod = env_of(t), product_pod()
+        u, m, _ = gpus_cfg[0]
+        gpu = device.New(m, u)
+        util.MountGPU(pod, gpu, env)
+        script = tmp_path / "fake-probe"
+        script.write_text("#!/bin/sh\n"
+                          "cg=$(grep '^0::' /proc/self/cgroup | cut -d: -f3)\n"
+                          f"if sh -c ': <> {t.devdir}/nvidia{m}' 2>/dev/null; then r=opened; else r=refused; fi\n"
+                          "printf '{\"status\":0,\"cgroup\":\"%s\",\"open\":\"%s\"}\\n' \"$cg\" \"$r\"\n")
+        script.chmod(0o755)
+        rc, rep = util.ProbeInPod(pod, [gpu], [], env, probe_exe=str(script), raise_on_error=False)
+        assert rc == 0 and rep["cgroup"].endswith(t.cgroup_path), rep
+
+
+@pytest.mark.parametrize("cid, driver, leaf", [
+    ("containerd://" + harness.CID, "cgroupfs", harness.CID),
+    ("containerd://" + harness.CID, "systemd", f"cri-containerd-{harness.CID}.scope"),
+    ("cri-o://" + harness.CID, "cgroupfs", f"crio-{harness.CID}"),
+    ("cri-o://" + harness.CID, "systemd", f"crio-{harness.CID}.scope"),
+    ("docker://" + harness.CID, "systemd", f"docker-{harness.CID}.scope"),
+])
+def test_cri_runtime_container_ids(cid, driver, leaf):
+    from gpumounter_b200 import cgroup
+
+    pod = product_pod(cid)
+    on = cgroup.GetCgroupNameOfPod(pod, MountEnv(cgroup_driver=driver, extensions=EXT_CRI_RUNTIMES))
+    assert on.rsplit("/", 1)[1] == leaf
+    off = cgroup.GetCgroupNameOfPod(pod, MountEnv(cgroup_driver=driver))
+    # without the extension: the reference's behaviour, which only knows how to strip "docker://" (ref: util.go:23)
+    ref_id = cid.replace("docker://", "", 1)
+    assert off.endswith("/" + ref_id if driver == "cgroupfs" else f"/docker-{ref_id}.scope")
+    assert on.rsplit("/", 1)[0] == off[:len(on.rsplit("/", 1)[0])]   # same pod-level directory either way

@@ -10,7 +10,7 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "gpumounter_b200", "csrc")
 SRCS = [os.path.join(ROOT, "tests", "native", "host_sanitize.cpp"), os.path.join(CSRC, "gmp_mount.cpp"),
-        os.path.join(CSRC, "gmp_nvml.cpp")]
+        os.path.join(CSRC, "gmp_nvml.cpp"), os.path.join(CSRC, "gmp_devfilter.cpp")]
 CXX = shutil.which("g++") or "g++"
 
 
