@@ -386,6 +386,28 @@ int write_permission(const gmp_mount_env* env, const std::string& cgroup_path, i
     return GMP_OK;
 }
 
+// All G GPUs of one request.  v1: one file write per GPU, as the reference's loop does (ref: server.go:80-95 ->
+// cgroup.go:143-169).  v2: ONE program replacement carrying all G rules (each replacement costs a verifier run).
+int write_permissions(const gmp_mount_env* env, const std::string& cgroup_path, const gmp_gpu* gpus, int n, const char* file_name) {
+    if (extension_on(env, GMP_EXT_CGROUP_V2) && n > 1) {
+        std::vector<gmp_dev_rule> rules((size_t)n);
+        for (int i = 0; i < n; ++i) {
+            rules[(size_t)i].type = GMP_DEV_CHAR;
+            rules[(size_t)i].major = GMP_NVIDIA_MAJOR;
+            rules[(size_t)i].minor = gpus[i].minor_number;
+            rules[(size_t)i].access = GMP_DEV_ACC_READ | GMP_DEV_ACC_WRITE;
+            rules[(size_t)i].allow = 1;
+        }
+        const std::string dir = devices_root(env) + cgroup_path;
+        return gmp_cgroup2_update_devices(dir.c_str(), rules.data(), n, strcmp(file_name, "devices.allow") == 0, nullptr);
+    }
+    for (int i = 0; i < n; ++i) {
+        const int rc = write_permission(env, cgroup_path, gpus[i].minor_number, file_name);
+        if (rc != GMP_OK) return rc;
+    }
+    return GMP_OK;
+}
+
 // ---- namespace work in a forked child ---------------------------------------------------------------
 enum class NodeOp { kCreate, kRemove };
 
@@ -595,10 +617,8 @@ int mount_many(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus
     std::string cgroup_path;
     int rc = pod_cgroup_path(env, pod, &cgroup_path);
     if (rc != GMP_OK) return rc;
-    for (int i = 0; i < n; ++i) {  // ref: util.go:37-40
-        rc = write_permission(env, cgroup_path, gpus[i].minor_number, "devices.allow");
-        if (rc != GMP_OK) return rc;
-    }
+    rc = write_permissions(env, cgroup_path, gpus, n, "devices.allow");  // ref: util.go:37-40
+    if (rc != GMP_OK) return rc;
     std::vector<std::string> pids;  // ref: util.go:44-55
     rc = read_cgroup_pids(env, cgroup_path, &pids);
     if (rc != GMP_OK) return rc;
@@ -638,10 +658,8 @@ int unmount_many(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gp
         for (const std::string& b : busy)
             if (std::find(victims.begin(), victims.end(), b) == victims.end()) victims.push_back(b);
     }
-    for (int i = 0; i < n; ++i) {  // ref: util.go:112-115
-        rc = write_permission(env, cgroup_path, gpus[i].minor_number, "devices.deny");
-        if (rc != GMP_OK) return rc;
-    }
+    rc = write_permissions(env, cgroup_path, gpus, n, "devices.deny");  // ref: util.go:112-115
+    if (rc != GMP_OK) return rc;
     int pid = 0;  // ref: util.go:118-124
     rc = first_pid(pids, &pid);
     if (rc != GMP_OK) return rc;

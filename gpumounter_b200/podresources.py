@@ -26,32 +26,47 @@ LIST_METHOD = "/v1alpha1.PodResourcesLister/List"
 _F = descriptor_pb2.FieldDescriptorProto
 
 
-def _file() -> descriptor_pb2.FileDescriptorProto:
-    fd = descriptor_pb2.FileDescriptorProto(name="podresources_v1alpha1.proto", package="v1alpha1", syntax="proto3")
+def _file(package: str) -> descriptor_pb2.FileDescriptorProto:
+    fd = descriptor_pb2.FileDescriptorProto(name=f"podresources_{package}.proto", package=package, syntax="proto3")
 
     def msg(name, fields):
         m = fd.message_type.add(name=name)
         for fname, num, ftype, label, tname in fields:
             f = m.field.add(name=fname, number=num, type=ftype, label=label)
             if tname:
-                f.type_name = ".v1alpha1." + tname
+                f.type_name = f".{package}." + tname
 
     opt, rep = _F.LABEL_OPTIONAL, _F.LABEL_REPEATED
     msg("ListPodResourcesRequest", [])
     msg("ListPodResourcesResponse", [("pod_resources", 1, _F.TYPE_MESSAGE, rep, "PodResources")])
     msg("PodResources", [("name", 1, _F.TYPE_STRING, opt, None), ("namespace", 2, _F.TYPE_STRING, opt, None),
                          ("containers", 3, _F.TYPE_MESSAGE, rep, "ContainerResources")])
-    msg("ContainerResources", [("name", 1, _F.TYPE_STRING, opt, None), ("devices", 2, _F.TYPE_MESSAGE, rep, "ContainerDevices")])
-    msg("ContainerDevices", [("resource_name", 1, _F.TYPE_STRING, opt, None), ("device_ids", 2, _F.TYPE_STRING, rep, None)])
+    container = [("name", 1, _F.TYPE_STRING, opt, None), ("devices", 2, _F.TYPE_MESSAGE, rep, "ContainerDevices")]
+    devices = [("resource_name", 1, _F.TYPE_STRING, opt, None), ("device_ids", 2, _F.TYPE_STRING, rep, None)]
+    if package == "v1":
+        # what v1 adds that matters here: the NUMA node of each device; cpu_ids (3), memory (4) and
+        # dynamic_resources (5) of ContainerResources are left undeclared and skipped as unknown fields
+        container.append(("cpu_ids", 3, _F.TYPE_INT64, rep, None))
+        devices.append(("topology", 3, _F.TYPE_MESSAGE, opt, "TopologyInfo"))
+        msg("TopologyInfo", [("nodes", 1, _F.TYPE_MESSAGE, rep, "NUMANode")])
+        msg("NUMANode", [("ID", 1, _F.TYPE_INT64, opt, None)])
+    msg("ContainerResources", container)
+    msg("ContainerDevices", devices)
     s = fd.service.add(name="PodResourcesLister")
-    s.method.add(name="List", input_type=".v1alpha1.ListPodResourcesRequest", output_type=".v1alpha1.ListPodResourcesResponse")
+    s.method.add(name="List", input_type=f".{package}.ListPodResourcesRequest", output_type=f".{package}.ListPodResourcesResponse")
     return fd
 
 
 _pool = descriptor_pool.DescriptorPool()
-_pool.Add(_file())
+_pool.Add(_file("v1alpha1"))
+_pool.Add(_file("v1"))
 ListPodResourcesRequest = message_factory.GetMessageClass(_pool.FindMessageTypeByName("v1alpha1.ListPodResourcesRequest"))
 ListPodResourcesResponse = message_factory.GetMessageClass(_pool.FindMessageTypeByName("v1alpha1.ListPodResourcesResponse"))
+# Extension, no reference counterpart: the v1 API that replaced v1alpha1 (GA in Kubernetes 1.20,
+# package "v1", same socket).  Same field numbers for everything UpdateGPUStatus reads.
+V1_LIST_METHOD = "/v1.PodResourcesLister/List"
+V1ListPodResourcesRequest = message_factory.GetMessageClass(_pool.FindMessageTypeByName("v1.ListPodResourcesRequest"))
+V1ListPodResourcesResponse = message_factory.GetMessageClass(_pool.FindMessageTypeByName("v1.ListPodResourcesResponse"))
 
 Listing = List[Tuple[str, str, List[Tuple[str, List[Tuple[str, List[str]]]]]]]
 
@@ -62,10 +77,27 @@ def to_listing(resp) -> Listing:
             for p in resp.pod_resources]
 
 
-def ListPods(socket_path: str = SocketPath, timeout: float = ConnectionTimeout) -> Listing:
-    """ref: collector.go:92-111 (stat the socket), :165-180 (blocking dial over unix, 10 s), :182-194 (List, 10 s)."""
+def numa_nodes(resp) -> dict:
+    """v1 only: device id -> NUMA node ids, for the devices that report a topology."""
+    out = {}
+    for p in resp.pod_resources:
+        for c in p.containers:
+            for d in c.devices:
+                if d.HasField("topology"):
+                    for dev in d.device_ids:
+                        out[dev] = [n.ID for n in d.topology.nodes]
+    return out
+
+
+def ListPods(socket_path: str = SocketPath, timeout: float = ConnectionTimeout, api: str = "v1alpha1") -> Listing:
+    """ref: collector.go:92-111 (stat the socket), :165-180 (blocking dial over unix, 10 s), :182-194 (List, 10 s).
+
+    api: "v1alpha1" (the reference's, default), "v1" (extension), or "auto" (v1, falling back to v1alpha1 when the
+    kubelet answers UNIMPLEMENTED)."""
     import grpc
 
+    if api not in ("v1alpha1", "v1", "auto"):
+        raise ValueError(f"unknown PodResources API version {api!r}")
     if not os.path.exists(socket_path):
         raise FileNotFoundError(f"Can not found {socket_path}")  # collector.go:93-97
     channel = grpc.insecure_channel("unix://" + socket_path)
@@ -74,11 +106,19 @@ def ListPods(socket_path: str = SocketPath, timeout: float = ConnectionTimeout) 
             grpc.channel_ready_future(channel).result(timeout=timeout)  # grpc.WithBlock()
         except grpc.FutureTimeoutError:
             raise ConnectionError(f"failure connecting to {socket_path}: context deadline exceeded")
-        call = channel.unary_unary(LIST_METHOD, request_serializer=lambda m: m.SerializeToString(),
-                                   response_deserializer=ListPodResourcesResponse.FromString)
-        try:
-            return to_listing(call(ListPodResourcesRequest(), timeout=timeout))
-        except grpc.RpcError as e:
-            raise ConnectionError(f"failure getting pod resources {e.code().name}: {e.details()}")
+        versions = {"v1alpha1": [(LIST_METHOD, ListPodResourcesRequest, ListPodResourcesResponse)],
+                    "v1": [(V1_LIST_METHOD, V1ListPodResourcesRequest, V1ListPodResourcesResponse)]}
+        versions["auto"] = versions["v1"] + versions["v1alpha1"]
+        last = None
+        for method, request, response in versions[api]:
+            call = channel.unary_unary(method, request_serializer=lambda m: m.SerializeToString(),
+                                       response_deserializer=response.FromString)
+            try:
+                return to_listing(call(request(), timeout=timeout))
+            except grpc.RpcError as e:
+                last = e
+                if e.code() != grpc.StatusCode.UNIMPLEMENTED:
+                    break
+        raise ConnectionError(f"failure getting pod resources {last.code().name}: {last.details()}")
     finally:
         channel.close()

@@ -1,4 +1,4 @@
-// Sanitizer driver for the host-only half of the library (gmp_mount.cpp + gmp_nvml.cpp): built once with
+// Sanitizer driver for the host-only half of the library (gmp_mount.cpp + gmp_nvml.cpp + gmp_devfilter.cpp): built once with
 // -fsanitize=address,undefined and once with -fsanitize=thread by tests/test_host_sanitizers.py.
 // Exercises the string/path/QoS/selection logic with hostile inputs, the nsenter argv builder, and — from eight
 // threads at once — the entry points the header declares thread-safe.
@@ -104,6 +104,39 @@ static void logic_round(int salt) {
     const unsigned char r3[3] = {1, 2, 3};
     CHECK(gmp_slave_pod_name("owner", r3, buf, sizeof(buf)) == GMP_OK && strcmp(buf, "owner-slave-pod-010203") == 0);
     CHECK(gmp_slave_pod_name("owner", r3, buf, 5) == GMP_ERR_BUFFER_TOO_SMALL);
+    // device filter (header section 7): build, decode, evaluate; truncated and garbled programs must fail cleanly
+    {
+        gmp_dev_rule rules[3] = {{GMP_DEV_CHAR, -1, -1, GMP_DEV_ACC_MKNOD, 1}, {GMP_DEV_CHAR, 1, 3, GMP_DEV_ACC_ALL, 1},
+                                 {GMP_DEV_CHAR, 195, salt, GMP_DEV_ACC_READ | GMP_DEV_ACC_WRITE, 1}};
+        gmp_bpf_insn prog[64];
+        int n_insns = 0, n_rules = 0, def = -1, allowed = -1;
+        CHECK(gmp_devfilter_build(rules, 3, 0, prog, 64, &n_insns) == GMP_OK && n_insns == 6 + 6 + 5 + 8 + 2);
+        CHECK(gmp_devfilter_build(rules, 3, 0, prog, 5, &n_insns) == GMP_ERR_BUFFER_TOO_SMALL && n_insns == 27);
+        gmp_dev_rule back[8];
+        CHECK(gmp_devfilter_decode(prog, n_insns, back, 8, &n_rules, &def) == GMP_OK && n_rules == 3 && def == 0);
+        CHECK(memcmp(back, rules, sizeof(rules)) == 0);
+        CHECK(gmp_devfilter_decode(prog, n_insns, back, 2, &n_rules, &def) == GMP_ERR_BUFFER_TOO_SMALL && n_rules == 3);
+        CHECK(gmp_devfilter_eval(prog, n_insns, GMP_DEV_CHAR, GMP_DEV_ACC_READ, 195, (uint32_t)salt, &allowed) == GMP_OK && allowed == 1);
+        CHECK(gmp_devfilter_eval(prog, n_insns, GMP_DEV_CHAR, GMP_DEV_ACC_READ, 195, 77, &allowed) == GMP_OK && allowed == 0);
+        for (int cut = 1; cut < n_insns; ++cut) {  // every truncation: an error code, never a read past the end
+            CHECK(gmp_devfilter_decode(prog, cut, back, 8, &n_rules, &def) == GMP_ERR_UNSUPPORTED);
+            const int rc = gmp_devfilter_eval(prog, cut, GMP_DEV_CHAR, GMP_DEV_ACC_READ, 9, 9, &allowed);
+            CHECK(rc == GMP_OK || rc == GMP_ERR_INVALID);
+        }
+        for (int at = 0; at < n_insns; ++at) {     // every single-instruction corruption
+            gmp_bpf_insn bad[64];
+            memcpy(bad, prog, sizeof(gmp_bpf_insn) * (size_t)n_insns);
+            bad[at].off = (int16_t)(bad[at].off + 1000 * (salt + 1));
+            bad[at].regs = (uint8_t)(bad[at].regs ^ 0xFF);
+            (void)gmp_devfilter_decode(bad, n_insns, back, 8, &n_rules, &def);
+            (void)gmp_devfilter_eval(bad, n_insns, GMP_DEV_CHAR, GMP_DEV_ACC_READ, 1, 3, &allowed);
+        }
+        gmp_dev_rule hostile = {7, -5, 1 << 30, 0xFFFF, 2};
+        CHECK(gmp_devfilter_build(&hostile, 1, 0, prog, 64, &n_insns) == GMP_ERR_INVALID);
+        uint32_t ids[4];
+        int n_ids = -1;
+        CHECK(gmp_cgroup2_device_programs("/nonexistent/cgroup", ids, 4, &n_ids, nullptr) == GMP_ERR_SYS);
+    }
     // NVML absent: a clean error, not a crash
     gmp_device devs[2];
     int n = -1;

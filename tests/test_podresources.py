@@ -10,16 +10,17 @@ from gpumounter_b200 import collector, device, podresources
 from tests.conftest import FAKE_UUIDS
 
 
-def serve_fake_kubelet(sock, response=None, fail=False):
+def serve_fake_kubelet(sock, response=None, fail=False, services=("v1alpha1",)):
     def handler(raw, context):
         if fail:
             context.abort(grpc.StatusCode.UNAVAILABLE, "kubelet restarting")
         return response
 
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=2))
-    server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler("v1alpha1.PodResourcesLister", {
-        "List": grpc.unary_unary_rpc_method_handler(handler, request_deserializer=podresources.ListPodResourcesRequest.FromString,
-                                                    response_serializer=lambda m: m.SerializeToString())}),))
+    for package in services:
+        server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler(f"{package}.PodResourcesLister", {
+            "List": grpc.unary_unary_rpc_method_handler(handler, request_deserializer=lambda b: b,
+                                                        response_serializer=lambda m: m.SerializeToString())}),))
     server.add_insecure_port("unix://" + sock)
     server.start()
     return server
@@ -74,3 +75,42 @@ def test_errors_are_reported_like_the_reference(tmp_path):
     dead.write_text("")  # exists, nobody listens
     with pytest.raises(ConnectionError, match="failure connecting to"):
         podresources.ListPods(str(dead), timeout=0.5)
+
+
+def v1_response():
+    r = podresources.V1ListPodResourcesResponse()
+    c = r.pod_resources.add(name="gpu-pod", namespace="default").containers.add(name="main", cpu_ids=[0, 1, 64, 65])
+    d = c.devices.add(resource_name="nvidia.com/gpu", device_ids=[FAKE_UUIDS[0]])
+    d.topology.nodes.add(ID=1)
+    c.devices.add(resource_name="nvidia.com/gpu", device_ids=[FAKE_UUIDS[3]])
+    return r
+
+
+def test_v1_api_is_an_opt_in_extension(tmp_path):
+    """Kubernetes 1.20+ serves v1 (and from 1.27 on only v1); the reference asks for v1alpha1.  Same listing either way,
+    plus the NUMA node v1 reports for a device."""
+    resp = v1_response()
+    assert podresources.numa_nodes(resp) == {FAKE_UUIDS[0]: [1]}
+    # a v1alpha1 client reading v1 bytes sees the same pods/containers/devices: topology and cpu_ids are unknown fields
+    old = podresources.ListPodResourcesResponse.FromString(resp.SerializeToString())
+    assert podresources.to_listing(old) == podresources.to_listing(resp)
+    sock = str(tmp_path / "kubelet.sock")
+    srv = serve_fake_kubelet(sock, resp, services=("v1",))  # a modern kubelet: no v1alpha1 any more
+    try:
+        want = [("gpu-pod", "default", [("main", [("nvidia.com/gpu", [FAKE_UUIDS[0]]), ("nvidia.com/gpu", [FAKE_UUIDS[3]])])])]
+        assert podresources.ListPods(sock, timeout=5, api="v1") == want
+        assert podresources.ListPods(sock, timeout=5, api="auto") == want
+        with pytest.raises(ConnectionError, match="UNIMPLEMENTED"):   # the reference's call against that kubelet
+            podresources.ListPods(sock, timeout=5)
+    finally:
+        srv.stop(0)
+    sock2 = str(tmp_path / "old.sock")
+    srv = serve_fake_kubelet(sock2, sample_response(), services=("v1alpha1",))  # a 1.18 kubelet
+    try:
+        assert podresources.ListPods(sock2, timeout=5, api="auto") == podresources.ListPods(sock2, timeout=5)
+        with pytest.raises(ConnectionError, match="UNIMPLEMENTED"):
+            podresources.ListPods(sock2, timeout=5, api="v1")
+    finally:
+        srv.stop(0)
+    with pytest.raises(ValueError):
+        podresources.ListPods(sock2, api="v2")
