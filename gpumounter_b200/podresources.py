@@ -9,6 +9,10 @@ unpinned — there is no kubelet in this environment; tests run against a stand-
     PodResources            { string name = 1; string namespace = 2; repeated ContainerResources containers = 3 }
     ContainerResources      { string name = 1; repeated ContainerDevices devices = 2 }
     ContainerDevices        { string resource_name = 1; repeated string device_ids = 2 }
+
+Extension (no reference counterpart): the same service in package `v1` (Kubernetes >= 1.20, the only
+one served from 1.27 on), which adds `TopologyInfo topology = 3 { repeated NUMANode nodes = 1 { int64 ID = 1 } }` to
+ContainerDevices and `repeated int64 cpu_ids = 3` to ContainerResources; `ListPods(api="v1" | "auto")`.
 """
 
 from __future__ import annotations
