@@ -72,6 +72,14 @@ def evaluate(insns: Sequence[Insn], type: int, access: int, major: int, minor: i
     return bool(ok.value)
 
 
+def plan(insns: Sequence[Insn], rules: Sequence[Rule], grant: bool) -> List[Insn]:
+    """The program gmp_cgroup2_update_devices would put in place of `insns` (no kernel involved)."""
+    arr, n = (gmp_bpf_insn * 16384)(), ctypes.c_int()
+    check(lib().gmp_devfilter_plan(_c_insns(insns), len(insns), _c_rules(rules), len(rules), int(grant), arr, 16384, ctypes.byref(n)),
+          "gmp_devfilter_plan")
+    return _py_insns(arr, n.value)
+
+
 def device_programs(cgroup_dir: str) -> Tuple[List[int], int]:
     ids, n, flags = (ctypes.c_uint32 * 64)(), ctypes.c_int(), ctypes.c_uint32()
     check(lib().gmp_cgroup2_device_programs(cgroup_dir.encode(), ids, 64, ctypes.byref(n), ctypes.byref(flags)), "gmp_cgroup2_device_programs")

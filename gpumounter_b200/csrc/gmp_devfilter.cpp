@@ -107,16 +107,18 @@ void emit_prologue(std::vector<gmp_bpf_insn>* p) {
     p->push_back(insn(kLdxW, 5, 1, 8, 0));
 }
 
-void emit_block(const gmp_dev_rule& r, std::vector<gmp_bpf_insn>* p) {
+// `tmp` is the scratch register of the access test: r1 in runc's layout (the context pointer is dead after the prologue),
+// r6 in the prefix put in front of a foreign program, which still needs r1.
+void emit_block(const gmp_dev_rule& r, std::vector<gmp_bpf_insn>* p, int tmp = 1) {
     int left = block_length(r);  // a jump's offset counts from the instruction after it to the next block
     auto jump_off = [&left]() { return --left; };
     p->push_back(insn(kJneK, 2, 0, jump_off(), r.type));
     if (r.access != GMP_DEV_ACC_ALL) {
-        p->push_back(insn(kMov32X, 1, 3, 0, 0));
+        p->push_back(insn(kMov32X, tmp, 3, 0, 0));
         --left;
-        p->push_back(insn(kAnd32K, 1, 0, 0, (int32_t)r.access));
+        p->push_back(insn(kAnd32K, tmp, 0, 0, (int32_t)r.access));
         --left;
-        p->push_back(insn(kJneX, 1, 3, jump_off(), 0));
+        p->push_back(insn(kJneX, tmp, 3, jump_off(), 0));
     }
     if (r.major >= 0) p->push_back(insn(kJneK, 4, 0, jump_off(), r.major));
     if (r.minor >= 0) p->push_back(insn(kJneK, 5, 0, jump_off(), r.minor));
@@ -140,6 +142,47 @@ int unsupported(const char* why, int at) {
     return GMP_ERR_UNSUPPORTED;
 }
 
+// One rule block starting at p[*at]; advances *at past it.
+int parse_block(const gmp_bpf_insn* p, int n, int* at_io, int tmp, gmp_dev_rule* out) {
+    int at = *at_io;
+    gmp_dev_rule r;
+    r.major = r.minor = -1;
+    r.access = GMP_DEV_ACC_ALL;
+    const int begin = at;
+    if (at >= n || p[at].code != kJneK || dst_of(p[at]) != 2) return unsupported("block does not start with the type test", at);
+    r.type = p[at].imm;
+    if (r.type != GMP_DEV_CHAR && r.type != GMP_DEV_BLOCK) return unsupported("unknown device type", at);
+    std::vector<int> jumps = {at};
+    ++at;
+    if (at + 3 <= n && p[at].code == kMov32X && dst_of(p[at]) == tmp && src_of(p[at]) == 3 && p[at + 1].code == kAnd32K &&
+        dst_of(p[at + 1]) == tmp && p[at + 2].code == kJneX && dst_of(p[at + 2]) == tmp && src_of(p[at + 2]) == 3) {
+        r.access = (uint32_t)p[at + 1].imm;
+        if (r.access == 0 || (r.access & ~(uint32_t)GMP_DEV_ACC_ALL) != 0) return unsupported("access mask", at + 1);
+        jumps.push_back(at + 2);
+        at += 3;
+    }
+    if (at < n && p[at].code == kJneK && dst_of(p[at]) == 4) {
+        if (p[at].imm < 0) return unsupported("major", at);
+        r.major = p[at].imm;
+        jumps.push_back(at++);
+    }
+    if (at < n && p[at].code == kJneK && dst_of(p[at]) == 5) {
+        if (p[at].imm < 0) return unsupported("minor", at);
+        r.minor = p[at].imm;
+        jumps.push_back(at++);
+    }
+    if (at + 2 > n || p[at].code != kMov32K || dst_of(p[at]) != 0 || (p[at].imm != 0 && p[at].imm != 1) || p[at + 1].code != kExit)
+        return unsupported("block does not end in 'w0 = 0|1; exit'", at);
+    r.allow = p[at].imm;
+    at += 2;
+    for (int j : jumps)
+        if (j + 1 + p[j].off != at) return unsupported("jump does not target the next block", j);
+    if (at - begin != block_length(r)) return unsupported("block length", begin);
+    *out = r;
+    *at_io = at;
+    return GMP_OK;
+}
+
 // Blocks in program order; the caller reverses them into list order.
 int decode(const gmp_bpf_insn* p, int n, std::vector<gmp_dev_rule>* rules, int* default_allow) {
     std::vector<gmp_bpf_insn> pro;
@@ -159,41 +202,67 @@ int decode(const gmp_bpf_insn* p, int n, std::vector<gmp_dev_rule>* rules, int* 
             return GMP_OK;
         }
         gmp_dev_rule r;
-        r.major = r.minor = -1;
-        r.access = GMP_DEV_ACC_ALL;
-        const int begin = at;
-        if (p[at].code != kJneK || dst_of(p[at]) != 2) return unsupported("block does not start with the type test", at);
-        r.type = p[at].imm;
-        if (r.type != GMP_DEV_CHAR && r.type != GMP_DEV_BLOCK) return unsupported("unknown device type", at);
-        std::vector<int> jumps = {at};
-        ++at;
-        if (at + 3 <= n && p[at].code == kMov32X && dst_of(p[at]) == 1 && src_of(p[at]) == 3 && p[at + 1].code == kAnd32K &&
-            dst_of(p[at + 1]) == 1 && p[at + 2].code == kJneX && dst_of(p[at + 2]) == 1 && src_of(p[at + 2]) == 3) {
-            r.access = (uint32_t)p[at + 1].imm;
-            if (r.access == 0 || (r.access & ~(uint32_t)GMP_DEV_ACC_ALL) != 0) return unsupported("access mask", at + 1);
-            jumps.push_back(at + 2);
-            at += 3;
-        }
-        if (at < n && p[at].code == kJneK && dst_of(p[at]) == 4) {
-            if (p[at].imm < 0) return unsupported("major", at);
-            r.major = p[at].imm;
-            jumps.push_back(at++);
-        }
-        if (at < n && p[at].code == kJneK && dst_of(p[at]) == 5) {
-            if (p[at].imm < 0) return unsupported("minor", at);
-            r.minor = p[at].imm;
-            jumps.push_back(at++);
-        }
-        if (at + 2 > n || p[at].code != kMov32K || dst_of(p[at]) != 0 || (p[at].imm != 0 && p[at].imm != 1) ||
-            p[at + 1].code != kExit)
-            return unsupported("block does not end in 'w0 = 0|1; exit'", at);
-        r.allow = p[at].imm;
-        at += 2;
-        for (int j : jumps)
-            if (j + 1 + p[j].off != at) return unsupported("jump does not target the next block", j);
-        if (at - begin != block_length(r)) return unsupported("block length", begin);
+        const int rc = parse_block(p, n, &at, 1, &r);
+        if (rc != GMP_OK) return rc;
         rules->push_back(r);
     }
+}
+
+// ---- prefix in front of a program in some other layout (crun, systemd, hand-written) -------------------------------
+// The foreign program is kept verbatim (its jumps are relative, so it can be moved); in front of it go
+//     w0 = kWrapMagic; w0 = <number of rules>          two dead stores that mark and size the prefix
+//     the six prologue loads                             (r1, the context pointer, is left alone)
+//     one block per rule, LAST rule first, scratch r6    a match returns; no match falls through into the original
+// Every verifiable program initialises r2..r5 itself before reading them, so leaving them loaded is harmless.
+constexpr int32_t kWrapMagic = 0x474D5046;  // "GMPF"
+constexpr int kWrapTmp = 6;
+
+bool relocatable(const gmp_bpf_insn* p, int n, int* at) {
+    for (int i = 0; i < n; ++i) {
+        const uint8_t cls = BPF_CLASS(p[i].code);
+        const bool call = (cls == BPF_JMP || cls == BPF_JMP32) && BPF_OP(p[i].code) == BPF_CALL;  // helper ids are rewritten
+        const bool wide_imm = p[i].code == (BPF_LD | BPF_IMM | BPF_DW);                           // map references likewise
+        if (call || wide_imm) {
+            *at = i;
+            return false;
+        }
+    }
+    return true;
+}
+
+void wrap(const std::vector<gmp_dev_rule>& ours, const gmp_bpf_insn* original, int n, std::vector<gmp_bpf_insn>* out) {
+    out->clear();
+    if (!ours.empty()) {
+        out->push_back(insn(kMov32K, 0, 0, 0, kWrapMagic));
+        out->push_back(insn(kMov32K, 0, 0, 0, (int32_t)ours.size()));
+        emit_prologue(out);
+        for (size_t i = ours.size(); i-- > 0;) emit_block(ours[i], out, kWrapTmp);
+    }
+    out->insert(out->end(), original, original + n);
+}
+
+// Splits a program into (our prefix rules in list order, where the original starts).  No prefix: empty, 0.
+int unwrap(const gmp_bpf_insn* p, int n, std::vector<gmp_dev_rule>* ours, int* original_at) {
+    ours->clear();
+    *original_at = 0;
+    if (n < 2 || p[0].code != kMov32K || dst_of(p[0]) != 0 || p[0].imm != kWrapMagic) return GMP_OK;
+    if (p[1].code != kMov32K || dst_of(p[1]) != 0 || p[1].imm <= 0 || p[1].imm > 4096) return unsupported("prefix header", 1);
+    std::vector<gmp_bpf_insn> pro;
+    emit_prologue(&pro);
+    if (n < 2 + kPrologue) return unsupported("prefix too short", 2);
+    for (int i = 0; i < kPrologue; ++i)
+        if (!same(p[2 + i], pro[(size_t)i])) return unsupported("prefix prologue differs", 2 + i);
+    int at = 2 + kPrologue;
+    for (int k = 0; k < p[1].imm; ++k) {
+        gmp_dev_rule r;
+        const int rc = parse_block(p, n, &at, kWrapTmp, &r);
+        if (rc != GMP_OK) return rc;
+        ours->push_back(r);
+    }
+    std::reverse(ours->begin(), ours->end());
+    if (at >= n) return unsupported("prefix with nothing behind it", at);
+    *original_at = at;
+    return GMP_OK;
 }
 
 }  // namespace
@@ -487,6 +556,14 @@ bool same_rule(const gmp_dev_rule& a, const gmp_dev_rule& b) {
 // Appends `r` (the last matching rule wins).  Earlier rules on the same device whose access set is covered by r's can
 // never be the last match again and are dropped, so mount/unmount cycles do not grow the program.
 void append_rule(std::vector<gmp_dev_rule>* list, const gmp_dev_rule& r) {
+    // already there, with nothing after it that speaks about this device: appending would only reorder
+    for (size_t k = list->size(); k-- > 0;) {
+        const gmp_dev_rule& o = (*list)[k];
+        if (same_rule(o, r)) return;
+        if (o.type == r.type && (o.major == -1 || r.major == -1 || o.major == r.major) &&
+            (o.minor == -1 || r.minor == -1 || o.minor == r.minor))
+            break;
+    }
     list->erase(std::remove_if(list->begin(), list->end(),
                                [&r](const gmp_dev_rule& o) { return same_device(o, r) && (o.access & ~r.access) == 0; }),
                 list->end());
@@ -550,24 +627,93 @@ int guarded(F&& body) {  // no C++ exception crosses the C ABI
     }
 }
 
+// Prefix rules in front of a foreign program: same editing as edit_rules(), except that "is the device still reachable"
+// is answered by RUNNING the foreign program (its rules are not known), and that an answer it cannot give counts as yes.
+void edit_prefix(std::vector<gmp_dev_rule>* ours, const gmp_bpf_insn* original, int n_original, const gmp_dev_rule* rules, int n,
+                 bool grant) {
+    for (int i = 0; i < n; ++i) {
+        gmp_dev_rule r = rules[i];
+        r.allow = 1;
+        if (grant) {
+            append_rule(ours, r);
+            continue;
+        }
+        for (size_t k = ours->size(); k-- > 0;) {
+            if (!same_device((*ours)[k], r)) continue;
+            if (same_rule((*ours)[k], r)) ours->erase(ours->begin() + (long)k);
+            break;
+        }
+        bool reachable = r.major < 0 || r.minor < 0;
+        for (uint32_t q = 1; q <= GMP_DEV_ACC_ALL && !reachable; ++q) {
+            if ((q & ~r.access) != 0) continue;
+            bool by_prefix = false, decided = false;
+            for (size_t k = ours->size(); k-- > 0 && !decided;) {
+                const gmp_dev_rule& o = (*ours)[k];
+                if (o.type == r.type && (o.major == -1 || o.major == r.major) && (o.minor == -1 || o.minor == r.minor) &&
+                    (q & ~o.access) == 0) {
+                    by_prefix = o.allow != 0;
+                    decided = true;
+                }
+            }
+            if (decided) {
+                reachable = by_prefix;
+                continue;
+            }
+            int allowed = 1;
+            if (eval(original, n_original, r.type, q, (uint32_t)r.major, (uint32_t)r.minor, &allowed) != GMP_OK) allowed = 1;
+            reachable = allowed != 0;
+        }
+        if (reachable) {
+            r.allow = 0;
+            append_rule(ours, r);
+        }
+    }
+}
+
+// What one attached program has to become.  *changed = false: it already says what is asked.
+int plan_replacement(const std::vector<gmp_bpf_insn>& insns, const gmp_dev_rule* rules, int n, bool grant,
+                     std::vector<gmp_bpf_insn>* fresh, bool* changed) {
+    *changed = false;
+    std::vector<gmp_dev_rule> ours;
+    int original_at = 0;
+    int rc = unwrap(insns.data(), (int)insns.size(), &ours, &original_at);
+    if (rc != GMP_OK) return rc;
+    if (original_at == 0) {  // no prefix of ours: runc's layout is edited in place, rule list to rule list
+        std::vector<gmp_dev_rule> blocks;
+        int default_allow = 0;
+        if (decode(insns.data(), (int)insns.size(), &blocks, &default_allow) == GMP_OK) {
+            std::vector<gmp_dev_rule> list(blocks.rbegin(), blocks.rend());
+            const std::vector<gmp_dev_rule> before = list;
+            edit_rules(&list, default_allow != 0, rules, n, grant);
+            if (list.size() == before.size() && std::equal(list.begin(), list.end(), before.begin(), same_rule)) return GMP_OK;
+            *changed = true;
+            return build(list.data(), (int)list.size(), default_allow, fresh);
+        }
+        clear_error();
+    }
+    const gmp_bpf_insn* original = insns.data() + original_at;
+    const int n_original = (int)insns.size() - original_at;
+    int at = 0;
+    if (!relocatable(original, n_original, &at)) {
+        set_error("device program calls a helper or references a map (instruction %d): it cannot be read back and re-loaded", at);
+        return GMP_ERR_UNSUPPORTED;
+    }
+    edit_prefix(&ours, original, n_original, rules, n, grant);
+    wrap(ours, original, n_original, fresh);
+    *changed = fresh->size() != insns.size() || !std::equal(fresh->begin(), fresh->end(), insns.begin(), same);
+    return GMP_OK;
+}
+
 int replace_one(int cgroup_fd, uint32_t prog_id, uint32_t attach_flags, const gmp_dev_rule* rules, int n, bool grant) {
     Fd old_fd;
     int rc = program_fd_by_id(prog_id, &old_fd);
     if (rc != GMP_OK) return rc;
-    std::vector<gmp_bpf_insn> insns;
+    std::vector<gmp_bpf_insn> insns, fresh;
     rc = read_program(old_fd.fd, &insns);
     if (rc != GMP_OK) return rc;
-    std::vector<gmp_dev_rule> blocks;
-    int default_allow = 0;
-    rc = decode(insns.data(), (int)insns.size(), &blocks, &default_allow);
-    if (rc != GMP_OK) return rc;
-    std::vector<gmp_dev_rule> list(blocks.rbegin(), blocks.rend());
-    const std::vector<gmp_dev_rule> before = list;
-    edit_rules(&list, default_allow != 0, rules, n, grant);
-    if (list.size() == before.size() && std::equal(list.begin(), list.end(), before.begin(), same_rule)) return GMP_OK;
-    std::vector<gmp_bpf_insn> fresh;
-    rc = build(list.data(), (int)list.size(), default_allow, &fresh);
-    if (rc != GMP_OK) return rc;
+    bool changed = false;
+    rc = plan_replacement(insns, rules, n, grant, &fresh, &changed);
+    if (rc != GMP_OK || !changed) return rc;
     Fd new_fd;
     rc = load_program(fresh, &new_fd);
     if (rc != GMP_OK) return rc;
@@ -626,6 +772,32 @@ extern "C" int gmp_devfilter_eval(const gmp_bpf_insn* insns, int n_insns, int ty
             return (int)GMP_ERR_INVALID;
         }
         return eval(insns, n_insns, type, access, major, minor, allowed);
+    });
+}
+
+extern "C" int gmp_devfilter_plan(const gmp_bpf_insn* insns, int n_insns, const gmp_dev_rule* rules, int n_rules, int grant,
+                                  gmp_bpf_insn* out, int cap, int* n_out) {
+    return guarded([&]() {
+        if (insns == nullptr || n_insns <= 0 || n_out == nullptr || n_rules < 0 || (n_rules > 0 && rules == nullptr) || cap < 0 ||
+            (cap > 0 && out == nullptr)) {
+            set_error("bad argument");
+            return (int)GMP_ERR_INVALID;
+        }
+        for (int i = 0; i < n_rules; ++i)
+            if (!rule_ok(rules[i])) return (int)GMP_ERR_INVALID;
+        const std::vector<gmp_bpf_insn> current(insns, insns + n_insns);
+        std::vector<gmp_bpf_insn> fresh;
+        bool changed = false;
+        const int rc = plan_replacement(current, rules, n_rules, grant != 0, &fresh, &changed);
+        if (rc != GMP_OK) return rc;
+        const std::vector<gmp_bpf_insn>& result = changed ? fresh : current;
+        *n_out = (int)result.size();
+        if ((int)result.size() > cap) {
+            set_error("%zu instructions, capacity %d", result.size(), cap);
+            return (int)GMP_ERR_BUFFER_TOO_SMALL;
+        }
+        memcpy(out, result.data(), result.size() * sizeof(gmp_bpf_insn));
+        return (int)GMP_OK;
     });
 }
 
@@ -708,17 +880,16 @@ extern "C" int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_
         uint32_t flags = 0;
         rc = query_programs(cg.fd, &ids, &flags);
         if (rc != GMP_OK) return rc;
-        // decode everything first: a program we cannot read must leave the cgroup untouched
+        // plan everything first: a program that cannot be edited must leave the cgroup untouched
         for (uint32_t id : ids) {
             Fd fd;
             rc = program_fd_by_id(id, &fd);
             if (rc != GMP_OK) return rc;
-            std::vector<gmp_bpf_insn> insns;
+            std::vector<gmp_bpf_insn> insns, fresh;
             rc = read_program(fd.fd, &insns);
             if (rc != GMP_OK) return rc;
-            std::vector<gmp_dev_rule> blocks;
-            int def = 0;
-            rc = decode(insns.data(), (int)insns.size(), &blocks, &def);
+            bool changed = false;
+            rc = plan_replacement(insns, rules, n_rules, grant != 0, &fresh, &changed);
             if (rc != GMP_OK) return rc;
         }
         for (uint32_t id : ids) {

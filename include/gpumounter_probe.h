@@ -74,7 +74,7 @@ enum {
     GMP_ERR_NODE_DENIED      = -21, /* /dev/nvidiaN exists but open() is refused (device cgroup) */
     GMP_ERR_DRIVER_LIB       = -22, /* libcuda.so.1 not resolvable from the probing context */
     GMP_ERR_STILL_MOUNTED    = -23, /* after an unmount: the device node is still there (or still opens) in the pod */
-    GMP_ERR_UNSUPPORTED      = -24  /* section 7: a cgroup-v2 device program that is not in the canonical block form */
+    GMP_ERR_UNSUPPORTED      = -24  /* section 7: a cgroup-v2 device program that can be neither decoded nor re-loaded */
 };
 
 GMP_API int         gmp_abi_version(void);
@@ -707,6 +707,20 @@ GMP_API int gmp_devfilter_decode(const gmp_bpf_insn* insns, int n_insns, gmp_dev
 GMP_API int gmp_devfilter_eval(const gmp_bpf_insn* insns, int n_insns, int type, uint32_t access,
                                uint32_t major, uint32_t minor, int* allowed);
 
+/*
+ * What gmp_cgroup2_update_devices would replace one attached program with, without touching the kernel.
+ *  - a program in the block form above is edited rule list to rule list (see gmp_cgroup2_update_devices);
+ *  - any other program (crun, systemd, hand-written) is kept verbatim behind a PREFIX: two marker instructions
+ *    ("w0 = 0x474D5046; w0 = <n>"), the prologue, and one block per rule of ours (scratch register r6, so that r1
+ *    still holds the context for the program behind).  A request that matches a prefix rule is decided there, every
+ *    other request falls through into the original.  Revoking the last prefix rule gives the original back byte for
+ *    byte.  Whether a device must be DENIED on revoke (it is reachable without our rule) is found by running the
+ *    original with gmp_devfilter_eval;
+ *  - a program that calls helpers or references maps cannot be read back in loadable form: GMP_ERR_UNSUPPORTED.
+ */
+GMP_API int gmp_devfilter_plan(const gmp_bpf_insn* insns, int n_insns, const gmp_dev_rule* rules, int n_rules, int grant,
+                               gmp_bpf_insn* out, int cap, int* n_out);
+
 /* The device programs attached to one cgroup-v2 directory (BPF_PROG_QUERY, not the effective set of its
  * ancestors).  *attach_flags receives the kernel's flags for that attachment (BPF_F_ALLOW_MULTI = 2 for runc). */
 GMP_API int gmp_cgroup2_device_programs(const char* cgroup_dir, uint32_t* prog_ids, int cap, int* n,
@@ -722,7 +736,8 @@ GMP_API int gmp_cgroup2_attach_rules(const char* cgroup_dir, const gmp_dev_rule*
  * decoded, edited and atomically replaced (BPF_F_REPLACE).  grant != 0: append "allow" rules (earlier rules they
  * shadow are dropped).  grant == 0: remove exactly the allow rules a previous grant appended; where there is none
  * (the runtime itself had granted the device) append a deny rule instead.  A cgroup with no device program is
- * unrestricted at that level: nothing to do, *programs = 0.  GMP_ERR_UNSUPPORTED leaves everything untouched.
+ * unrestricted at that level: nothing to do, *programs = 0.  Programs in other layouts are handled as gmp_devfilter_plan
+ * describes.  Any error leaves every program of the cgroup untouched.
  */
 GMP_API int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_rule* rules, int n_rules, int grant,
                                        int* programs);

@@ -234,3 +234,38 @@ def kernel_available() -> str:
     except OSError as e:
         return f"bpf(BPF_PROG_LOAD) refused: {e}"
     return ""
+
+
+# ---- programs in OTHER layouts, to stand in for runtimes that are not runc ----------------------------------------------
+def first_match_program(rules: Sequence[Rule], default_allow: bool = False) -> List[Insn]:
+    """A device filter in the style crun and systemd use (both derive from systemd's bpf-devices.c): the same six loads,
+    then one block per rule in LIST order (the FIRST matching rule wins), 64-bit moves for the verdict, the access test
+    written as "(access & ~rule) != 0 -> next" with JSET.  Not a transcription of either project's emitter - the point is
+    a valid, enforceable program whose layout gmp_devfilter_decode does not recognise."""
+    MOV64_K, JSET_K = 0xB7, 0x45
+    prog: List[Insn] = [
+        (LDX_W, 2, 1, 0, 0), (AND32_K, 2, 0, 0, 0xFFFF), (LDX_W, 3, 1, 0, 0), (RSH32_K, 3, 0, 0, 16),
+        (LDX_W, 4, 1, 4, 0), (LDX_W, 5, 1, 8, 0),
+    ]
+    for t, ma, mi, acc, allow in rules:
+        block: List[List[int]] = [[JNE_K, 2, 0, None, t]]
+        if acc != ACC_ALL:
+            block.append([JSET_K, 3, 0, None, (~acc) & ACC_ALL])
+        if ma >= 0:
+            block.append([JNE_K, 4, 0, None, ma])
+        if mi >= 0:
+            block.append([JNE_K, 5, 0, None, mi])
+        block += [[MOV64_K, 0, 0, 0, 1 if allow else 0], [EXIT, 0, 0, 0, 0]]
+        for k, ins in enumerate(block):
+            if ins[3] is None:
+                ins[3] = len(block) - (k + 1)
+        prog += [tuple(i) for i in block]
+    prog += [(MOV64_K, 0, 0, 0, 1 if default_allow else 0), (EXIT, 0, 0, 0, 0)]
+    return prog
+
+
+def decide_first_match(rules: Sequence[Rule], default_allow: bool, type_: int, access: int, major: int, minor: int) -> bool:
+    for t, ma, mi, acc, allow in rules:
+        if t == type_ and ma in (-1, major) and mi in (-1, minor) and (access & ~acc) == 0:
+            return allow
+    return default_allow

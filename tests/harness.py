@@ -40,7 +40,8 @@ def can_run_cgroup2() -> Optional[str]:
 
 
 class Target:
-    def __init__(self, real_cgroup: bool = False, qos_dir: str = "besteffort", cgroup2: bool = False, runtime_rules=None):
+    def __init__(self, real_cgroup: bool = False, qos_dir: str = "besteffort", cgroup2: bool = False, runtime_rules=None,
+                 runtime_program=None):
         self.base = tempfile.mkdtemp(prefix="gmp_target_")
         self.devdir = os.path.join(self.base, "dev")
         os.mkdir(self.devdir)
@@ -50,6 +51,7 @@ class Target:
         self.extra: List[subprocess.Popen] = []
         self.cgroup2 = cgroup2
         self.runtime_rules = runtime_rules
+        self.runtime_program = runtime_program  # explicit instructions instead of runc's layout of runtime_rules
         if cgroup2:
             from oracle import gmo_devfilter
 
@@ -68,7 +70,14 @@ class Target:
             from oracle import gmo_devfilter
 
             rules = gmo_devfilter.RUNC_DEFAULT_RULES if self.runtime_rules is None else self.runtime_rules
-            gmo_devfilter.kernel_attach_rules(self.cgroup_dir, rules)
+            if self.runtime_program is not None:
+                fd = gmo_devfilter.kernel_load(self.runtime_program)
+                try:
+                    gmo_devfilter.kernel_attach(self.cgroup_dir, fd)
+                finally:
+                    os.close(fd)
+            else:
+                gmo_devfilter.kernel_attach_rules(self.cgroup_dir, rules)
         script = f"mount -t tmpfs -o mode=755 tmpfs {self.devdir} && echo ready && exec sleep 600"
         self.proc = subprocess.Popen(["unshare", "-m", "--propagation", "private", "sh", "-c", script],
                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)

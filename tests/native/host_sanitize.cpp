@@ -131,6 +131,23 @@ static void logic_round(int salt) {
             (void)gmp_devfilter_decode(bad, n_insns, back, 8, &n_rules, &def);
             (void)gmp_devfilter_eval(bad, n_insns, GMP_DEV_CHAR, GMP_DEV_ACC_READ, 1, 3, &allowed);
         }
+        {   // planner: runc layout edited in place, a foreign program wrapped and unwrapped, garbage refused or wrapped
+            gmp_bpf_insn planned[128], again[128];
+            int n_planned = 0, n_again = 0;
+            gmp_dev_rule gpu = {GMP_DEV_CHAR, 195, 40 + salt, GMP_DEV_ACC_READ | GMP_DEV_ACC_WRITE, 1};
+            CHECK(gmp_devfilter_build(rules, 3, 0, prog, 64, &n_insns) == GMP_OK);
+            CHECK(gmp_devfilter_plan(prog, n_insns, &gpu, 1, 1, planned, 128, &n_planned) == GMP_OK && n_planned == n_insns + 8);
+            CHECK(gmp_devfilter_plan(planned, n_planned, &gpu, 1, 0, again, 128, &n_again) == GMP_OK && n_again == n_insns);
+            CHECK(memcmp(again, prog, sizeof(gmp_bpf_insn) * (size_t)n_insns) == 0);
+            gmp_bpf_insn foreign[2] = {{0xB7, 0, 0, 1}, {0x95, 0, 0, 0}};  // r0 = 1; exit
+            CHECK(gmp_devfilter_plan(foreign, 2, &gpu, 1, 1, planned, 128, &n_planned) == GMP_OK && n_planned == 2 + 6 + 8 + 2);
+            CHECK(gmp_devfilter_plan(planned, n_planned, &gpu, 1, 0, again, 128, &n_again) == GMP_OK);
+            CHECK(n_again == 2 + 6 + 8 + 2);  // "allow everything" still reaches the GPU: the allow became a deny
+            CHECK(gmp_devfilter_eval(again, n_again, GMP_DEV_CHAR, GMP_DEV_ACC_READ, 195, (uint32_t)(40 + salt), &allowed) == GMP_OK && !allowed);
+            for (int cut = 1; cut < n_planned; ++cut)  // truncated prefixes: an error or a wrap, never a crash
+                (void)gmp_devfilter_plan(planned, cut, &gpu, 1, 0, again, 128, &n_again);
+            CHECK(gmp_devfilter_plan(planned, n_planned, &gpu, 1, 1, again, 4, &n_again) == GMP_ERR_BUFFER_TOO_SMALL);
+        }
         gmp_dev_rule hostile = {7, -5, 1 << 30, 0xFFFF, 2};
         CHECK(gmp_devfilter_build(&hostile, 1, 0, prog, 64, &n_insns) == GMP_ERR_INVALID);
         uint32_t ids[4];

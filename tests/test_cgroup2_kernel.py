@@ -116,11 +116,55 @@ def test_grant_twice_is_idempotent_and_revoke_of_a_runtime_granted_device_denies
         assert t.try_open(5) in NO_DRIVER
 
 
-def test_foreign_program_is_left_alone(fake_nvml):
+def test_program_in_another_layout_is_wrapped_not_rewritten(fake_nvml):
+    """A runtime that is not runc (crun, systemd: first match wins, 64-bit moves, JSET access test).  The library cannot
+    turn it into a rule list; it keeps it verbatim and puts its own rules in front.  Same kernel-enforced behaviour."""
+    gpus_cfg = fake_nvml()
+    original = o.first_match_program(o.RUNC_DEFAULT_RULES)
+    with harness.Target(cgroup2=True, runtime_program=original) as t:
+        env, pod = env_of(t), product_pod()
+        gpus = [device.New(m, u) for u, m, _ in gpus_cfg]
+        assert attached(t)[0] == [original]
+        with pytest.raises(ProbeError):
+            c.decode(original)
+        assert util.MountGPUs(pod, gpus[:3], env) == 3
+        now = attached(t)[0][0]
+        assert now[0] == (0xB4, 0, 0, 0, 0x474D5046) and now[1] == (0xB4, 0, 0, 0, 3) and now[-len(original):] == original
+        for g in gpus[:3]:
+            assert t.try_open(g.MinorNumber) in NO_DRIVER
+        other = gpus[3].MinorNumber
+        os.mknod(t.node_path_in_target(other), 0o666 | 0o020000, os.makedev(195, other))
+        assert t.try_open(other) == errno.EPERM
+        os.unlink(t.node_path_in_target(other))
+        assert util.UnmountGPUs(pod, gpus[:2], False, env) == 2
+        assert t.try_open(gpus[2].MinorNumber) in NO_DRIVER and attached(t)[0][0][1] == (0xB4, 0, 0, 0, 1)
+        assert util.UnmountGPUs(pod, gpus[2:3], False, env) == 1
+        assert attached(t)[0] == [original] and t.nodes() == []
+
+
+def test_two_programs_on_one_cgroup_are_both_edited(fake_nvml):
+    """BPF_F_ALLOW_MULTI: every attached program must say yes.  runc's program plus a second one in another layout."""
     gpus_cfg = fake_nvml()
     with harness.Target(cgroup2=True) as t:
-        # a second program in a layout the decoder does not know (what crun or systemd would attach): "r0 = 1; exit"
-        fd = o.kernel_load([(0xB7, 0, 0, 0, 1), (0x95, 0, 0, 0, 0)])
+        second = o.first_match_program(o.RUNC_DEFAULT_RULES)
+        fd = o.kernel_load(second)
+        o.kernel_attach(t.cgroup_dir, fd)
+        os.close(fd)
+        before = attached(t)
+        assert len(before[0]) == 2
+        u, m, _ = gpus_cfg[0]
+        gpu = device.New(m, u)
+        util.MountGPU(product_pod(), gpu, env_of(t))
+        assert t.try_open(m) in NO_DRIVER and len(attached(t)[0]) == 2
+        util.UnmountGPU(product_pod(), gpu, False, env_of(t))
+        assert sorted(attached(t)[0]) == sorted(before[0]) and t.nodes() == []
+
+
+def test_program_that_cannot_be_reloaded_leaves_everything_untouched(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        # a second program that calls a helper (bpf_get_current_uid_gid = 15): its translated form is not loadable
+        fd = o.kernel_load([(0x85, 0, 0, 0, 15), (0xB7, 0, 0, 0, 1), (0x95, 0, 0, 0, 0)])
         o.kernel_attach(t.cgroup_dir, fd)
         os.close(fd)
         before = attached(t)
@@ -128,7 +172,7 @@ def test_foreign_program_is_left_alone(fake_nvml):
         u, m, _ = gpus_cfg[0]
         with pytest.raises(ProbeError) as e:
             util.MountGPU(product_pod(), device.New(m, u), env_of(t))
-        assert e.value.code == _lib.GMP_ERR_UNSUPPORTED and "canonical block form" in e.value.detail
+        assert e.value.code == _lib.GMP_ERR_UNSUPPORTED and "re-loaded" in e.value.detail
         assert attached(t) == before and t.nodes() == []          # nothing half done: no rule edited, no node made
 
 

@@ -152,3 +152,75 @@ def test_interpreter_handles_general_programs_and_refuses_what_it_cannot_run():
         with pytest.raises(ProbeError) as e:
             c.evaluate(bad, 2, 2, 1, 3)
         assert e.value.code == code, bad
+
+
+# ---- programs in a layout the decoder does not know: kept verbatim behind a prefix ----------------------------------
+GPU_RW = c.ACC_READ | c.ACC_WRITE
+
+
+def requests(extra=()):
+    for type_ in (1, 2):
+        for access in range(1, 8):
+            for major, minor in [(1, 3), (1, 5), (195, 0), (195, 3), (195, 4), (136, 9), (8, 0), *extra]:
+                yield type_, access, major, minor
+
+
+def test_foreign_program_gets_a_prefix_and_comes_back_byte_for_byte():
+    original = o.first_match_program(o.RUNC_DEFAULT_RULES)
+    with pytest.raises(ProbeError):
+        c.decode(original)                                      # not runc's layout
+    granted = c.plan(original, [c.gpu_rule(3), c.gpu_rule(4)], True)
+    assert granted[0] == (0xB4, 0, 0, 0, 0x474D5046) and granted[1] == (0xB4, 0, 0, 0, 2)   # marker, two rules
+    assert granted[-len(original):] == original                 # the runtime's program, untouched, behind the prefix
+    for type_, access, major, minor in requests():
+        before = o.interpret(original, type_, access, major, minor)
+        mine = type_ == c.DEV_CHAR and major == 195 and minor in (3, 4) and (access & ~GPU_RW) == 0
+        assert c.evaluate(granted, type_, access, major, minor) == (mine or before) == o.interpret(granted, type_, access, major, minor)
+    assert c.plan(granted, [c.gpu_rule(3)], True) == granted    # idempotent
+    one = c.plan(granted, [c.gpu_rule(3)], False)
+    assert one[1] == (0xB4, 0, 0, 0, 1) and not c.evaluate(one, c.DEV_CHAR, GPU_RW, 195, 3) and c.evaluate(one, c.DEV_CHAR, GPU_RW, 195, 4)
+    assert c.plan(one, [c.gpu_rule(4)], False) == original      # last rule gone: the original, byte for byte
+    assert c.plan(original, [c.gpu_rule(9)], False) == original # revoking what nobody granted changes nothing
+
+
+def test_revoking_a_device_the_foreign_program_grants_puts_a_deny_in_the_prefix():
+    original = o.first_match_program(o.RUNC_DEFAULT_RULES + [(o.DEV_CHAR, 195, -1, o.ACC_ALL, True)])   # all GPUs allowed
+    assert o.interpret(original, c.DEV_CHAR, GPU_RW, 195, 2)
+    denied = c.plan(original, [c.gpu_rule(2)], False)
+    assert denied[1] == (0xB4, 0, 0, 0, 1) and denied[-len(original):] == original
+    for access in range(1, 8):
+        want = o.interpret(original, c.DEV_CHAR, access, 195, 2) and (access & ~GPU_RW) != 0    # rw requests denied, 'm' untouched
+        assert c.evaluate(denied, c.DEV_CHAR, access, 195, 2) == want
+        assert c.evaluate(denied, c.DEV_CHAR, access, 195, 3) == o.interpret(original, c.DEV_CHAR, access, 195, 3)
+    assert c.plan(denied, [c.gpu_rule(2)], True)[-len(original) - 8:] == c.plan(original, [c.gpu_rule(2)], True)[-len(original) - 8:]
+
+
+def test_programs_that_cannot_be_reloaded_are_refused():
+    with_call = [(0x85, 0, 0, 0, 6), (0xB7, 0, 0, 0, 1), (0x95, 0, 0, 0, 0)]          # call bpf_trace_printk
+    with_map = [(0x18, 1, 1, 0, 5), (0, 0, 0, 0, 0), (0xB7, 0, 0, 0, 1), (0x95, 0, 0, 0, 0)]   # ld_imm64 r1, map fd
+    for prog in (with_call, with_map):
+        with pytest.raises(ProbeError) as e:
+            c.plan(prog, [c.gpu_rule(0)], True)
+        assert e.value.code == _lib.GMP_ERR_UNSUPPORTED and "re-loaded" in e.value.detail
+
+
+@settings(max_examples=150, deadline=None)
+@given(st.lists(rule_st, max_size=8), st.booleans(), st.booleans(),
+       st.lists(st.tuples(st.sampled_from([0, 3, 7, 255]), st.booleans()), min_size=1, max_size=6))
+def test_random_grant_revoke_sequences_on_both_layouts(rules, default_allow, foreign, steps):
+    """Any sequence of grants and revokes of GPU rules, on a runc-layout or a foreign program: after every step the
+    planned program allows rw on exactly the granted GPUs (plus whatever the runtime's own rules allow for requests the
+    GPU rules do not speak about), and once everything is revoked a device the runtime does not grant is closed."""
+    prog = o.first_match_program(rules, default_allow) if foreign else o.runc_program(rules, default_allow)
+    base = (lambda *a: o.decide_first_match(rules, default_allow, *a)) if foreign else (lambda *a: o.decide(rules, default_allow, *a))
+    state = {}  # minor -> True (granted) / False (revoked)
+    for minor, grant in steps:
+        prog = c.plan(prog, [c.gpu_rule(minor)], grant)
+        state[minor] = grant
+        for m, g in state.items():
+            for q in (c.ACC_READ, c.ACC_WRITE, GPU_RW):
+                assert c.evaluate(prog, c.DEV_CHAR, q, 195, m) == g == o.interpret(prog, c.DEV_CHAR, q, 195, m)
+        for type_, access, major, minor2 in requests(extra=[(195, 255), (195, 7)]):
+            touched = type_ == c.DEV_CHAR and major == 195 and minor2 in state and (access & ~GPU_RW) == 0
+            if not touched and not (type_ == c.DEV_CHAR and major == 195 and minor2 in state):
+                assert c.evaluate(prog, type_, access, major, minor2) == base(type_, access, major, minor2)
