@@ -203,3 +203,32 @@ def test_over_the_wire_on_the_reference_method_paths(world):
         ch.close()
     finally:
         srv.stop(0)
+
+
+@pytest.mark.skipif(harness.can_run_cgroup2() is not None, reason="no writable cgroup2 mount / bpf(2) here")
+def test_add_and_remove_on_a_containerd_pod_on_the_unified_hierarchy(fake_nvml):
+    """The same handlers with the two mount-path extensions on (header section 7): a containerd container id and a real
+    cgroup-v2 directory whose device program the kernel enforces."""
+    import errno
+
+    from gpumounter_b200 import cgroup2
+    from gpumounter_b200._model import EXT_CGROUP_V2, EXT_CRI_RUNTIMES
+
+    cfg = fake_nvml()
+    gpus = [device.New(m, u) for u, m, _ in cfg]
+    pod = Pod("gpu-pod", "default", uid=harness.UID, node_name="node-1", container_id="containerd://" + harness.CID)
+    with harness.Target(cgroup2=True) as t:
+        cluster = FakeCluster([pod], [u for u, _, _ in cfg])
+        env = MountEnv(cgroup2_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs",
+                       extensions=EXT_CGROUP_V2 | EXT_CRI_RUNTIMES)
+        impl = server.GPUMountImpl(cluster, gpus=gpus, env=env, probe_hook=lambda p, m: (0, {"n_gpus": len(m)}))
+        baseline = [cgroup2.read_program(i) for i in cgroup2.device_programs(t.cgroup_dir)[0]]
+        assert impl.AddGPU(add(n=2)).add_gpu_result == api.AddGPUResult_Success
+        assert t.nodes() == ["nvidia2", "nvidia3"]
+        assert t.try_open(2) in (errno.ENXIO, errno.ENODEV) and t.try_open(3) in (errno.ENXIO, errno.ENODEV)
+        member = t.spawn_member()
+        fake_nvml(procs=[(FAKE_UUIDS[0], member.pid, 1 << 20, "compute")])
+        assert impl.RemoveGPU(remove([FAKE_UUIDS[0]])).remove_gpu_result == api.RemoveGPUResult_GPUBusy
+        assert impl.RemoveGPU(remove([FAKE_UUIDS[0], FAKE_UUIDS[1]], force=True)).remove_gpu_result == api.RemoveGPUResult_Success
+        assert member.wait(timeout=5) == -15 and t.nodes() == [] and not cluster.alloc
+        assert [cgroup2.read_program(i) for i in cgroup2.device_programs(t.cgroup_dir)[0]] == baseline
