@@ -49,6 +49,9 @@ def product_pod():
 
 
 def env_of(t):
+    if getattr(t, "cgroup2", False):  # extension (header section 7): the unified hierarchy, eBPF device program
+        from gpumounter_b200._model import EXT_CGROUP_V2
+        return MountEnv(cgroup2_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs", extensions=EXT_CGROUP_V2)
     return MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
 
 
@@ -347,6 +350,7 @@ def main():
         os.environ["GMP_FAKE_NVML_CONFIG"] = cfg
     else:
         os.environ.pop("GPUMOUNTER_NVML_LIB", None)
+    v2_ok = harness.can_run_cgroup2() is None
     out = {"host_cores": os.cpu_count(), "threads_used": 1, "iters": args.iters, "mount": {}, "unmount": {},
            "unmount_nvml_busy_check": "real NVML, both arms" if have_gpu else "fake NVML in the native arm, none in the reference arm"}
     # On a GPU box the unmount path's NVML query names a UUID: use real UUIDs where they exist, made-up ones beyond
@@ -367,11 +371,20 @@ def main():
             ser_m, ser_u = bench_native(t, gpus, args.iters, batched=False)
         out["mount"][str(g)] = {"reference_fork_exec": ref_m, "native_batched": nat_m, "native_serial": ser_m,
                                 "speedup_p50": ref_m["p50_ms"] / nat_m["p50_ms"]}
+        if v2_ok:
+            # no reference arm: on the unified hierarchy the reference's path resolves a directory that does not exist
+            with harness.Target(cgroup2=True) as t:
+                v2_m, v2_u = bench_native(t, gpus, args.iters, batched=True)
+            out["mount"][str(g)]["native_batched_cgroup2"] = v2_m
+            out.setdefault("unmount_cgroup2", {})[str(g)] = v2_u
         out["unmount"][str(g)] = {"reference_fork_exec": ref_u, "native_batched": nat_u, "native_serial": ser_u,
                                   "speedup_p50": ref_u["p50_ms"] / nat_u["p50_ms"]}
     if args.churn_rounds and not have_gpu:
         with harness.Target() as t:
             out["churn_1_8_1"] = churn(t, args.churn_rounds)
+        if v2_ok:
+            with harness.Target(cgroup2=True) as t:
+                out["churn_1_8_1_cgroup2"] = churn(t, args.churn_rounds)
     elif args.churn_rounds:
         out["churn_1_8_1"] = {"skipped": "churn uses made-up UUIDs, which a real NVML refuses; run on a driver-less box"}
     if args.usable_iters > 0 and have_gpu:
