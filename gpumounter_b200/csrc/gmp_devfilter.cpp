@@ -704,23 +704,6 @@ int plan_replacement(const std::vector<gmp_bpf_insn>& insns, const gmp_dev_rule*
     return GMP_OK;
 }
 
-int replace_one(int cgroup_fd, uint32_t prog_id, uint32_t attach_flags, const gmp_dev_rule* rules, int n, bool grant) {
-    Fd old_fd;
-    int rc = program_fd_by_id(prog_id, &old_fd);
-    if (rc != GMP_OK) return rc;
-    std::vector<gmp_bpf_insn> insns, fresh;
-    rc = read_program(old_fd.fd, &insns);
-    if (rc != GMP_OK) return rc;
-    bool changed = false;
-    rc = plan_replacement(insns, rules, n, grant, &fresh, &changed);
-    if (rc != GMP_OK || !changed) return rc;
-    Fd new_fd;
-    rc = load_program(fresh, &new_fd);
-    if (rc != GMP_OK) return rc;
-    if (attach_flags & BPF_F_ALLOW_MULTI) return attach_program(cgroup_fd, new_fd.fd, BPF_F_ALLOW_MULTI, old_fd.fd);
-    return attach_program(cgroup_fd, new_fd.fd, attach_flags, -1);  // single-program attachment: attaching replaces
-}
-
 }  // namespace
 
 extern "C" int gmp_devfilter_build(const gmp_dev_rule* rules, int n_rules, int default_allow, gmp_bpf_insn* insns, int cap,
@@ -880,21 +863,40 @@ extern "C" int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_
         uint32_t flags = 0;
         rc = query_programs(cg.fd, &ids, &flags);
         if (rc != GMP_OK) return rc;
-        // plan everything first: a program that cannot be edited must leave the cgroup untouched
-        for (uint32_t id : ids) {
-            Fd fd;
-            rc = program_fd_by_id(id, &fd);
+        // 1. plan and 2. load every replacement before 3. attaching any: a program that cannot be edited, or a
+        //    replacement the verifier refuses, leaves the cgroup untouched
+        struct Step {
+            Fd old_fd, new_fd;
+            bool changed = false;
+        };
+        std::vector<Step> steps(ids.size());
+        for (size_t k = 0; k < ids.size(); ++k) {
+            rc = program_fd_by_id(ids[k], &steps[k].old_fd);
             if (rc != GMP_OK) return rc;
             std::vector<gmp_bpf_insn> insns, fresh;
-            rc = read_program(fd.fd, &insns);
+            rc = read_program(steps[k].old_fd.fd, &insns);
             if (rc != GMP_OK) return rc;
-            bool changed = false;
-            rc = plan_replacement(insns, rules, n_rules, grant != 0, &fresh, &changed);
+            rc = plan_replacement(insns, rules, n_rules, grant != 0, &fresh, &steps[k].changed);
+            if (rc != GMP_OK) return rc;
+            if (!steps[k].changed) continue;
+            rc = load_program(fresh, &steps[k].new_fd);
             if (rc != GMP_OK) return rc;
         }
-        for (uint32_t id : ids) {
-            rc = replace_one(cg.fd, id, flags, rules, n_rules, grant != 0);
-            if (rc != GMP_OK) return rc;
+        const bool multi = (flags & BPF_F_ALLOW_MULTI) != 0;
+        for (size_t k = 0; k < steps.size(); ++k) {
+            if (!steps[k].changed) continue;
+            rc = multi ? attach_program(cg.fd, steps[k].new_fd.fd, BPF_F_ALLOW_MULTI, steps[k].old_fd.fd)
+                       : attach_program(cg.fd, steps[k].new_fd.fd, flags, -1);  // single-program attachment: attaching replaces
+            if (rc == GMP_OK) continue;
+            // an attach failed half way (not expected once the loads succeeded): put the earlier programs back
+            const std::string why = gmp_last_error();
+            for (size_t j = 0; j < k; ++j) {
+                if (!steps[j].changed) continue;
+                if (multi) (void)attach_program(cg.fd, steps[j].old_fd.fd, BPF_F_ALLOW_MULTI, steps[j].new_fd.fd);
+                else (void)attach_program(cg.fd, steps[j].old_fd.fd, flags, -1);
+            }
+            set_error("%s (earlier replacements rolled back)", why.c_str());
+            return rc;
         }
         if (programs) *programs = (int)ids.size();
         return (int)GMP_OK;

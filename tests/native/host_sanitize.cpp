@@ -13,7 +13,7 @@
 
 #include "gpumounter_probe.h"
 
-// the two error-plumbing functions normally come from gmp_core.cu (a CUDA translation unit)
+// the error-plumbing functions normally come from gmp_core.cu (a CUDA translation unit)
 namespace gmp {
 static thread_local char g_err[512];
 void set_error(const char* fmt, ...) {
@@ -24,6 +24,7 @@ void set_error(const char* fmt, ...) {
 }
 void clear_error() { g_err[0] = '\0'; }
 }  // namespace gmp
+extern "C" const char* gmp_last_error(void) { return gmp::g_err; }
 
 #define CHECK(cond)                                                         \
     do {                                                                    \
