@@ -27,6 +27,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <sys/file.h>
 #include <sys/syscall.h>
 #include <unistd.h>
 
@@ -528,7 +529,10 @@ int load_program(const std::vector<gmp_bpf_insn>& insns, Fd* out) {
     return GMP_OK;
 }
 
-int attach_program(int cgroup_fd, int prog_fd, uint32_t flags, int replace_fd) {
+// BPF_F_REPLACE names the program it expects to find: if another writer has swapped it out since it was read, the
+// kernel answers ENOENT and nothing is attached - a compare-and-swap.  *lost_race tells that case apart.
+int attach_program(int cgroup_fd, int prog_fd, uint32_t flags, int replace_fd, bool* lost_race = nullptr) {
+    if (lost_race) *lost_race = false;
     union bpf_attr a;
     memset(&a, 0, sizeof(a));
     a.target_fd = (uint32_t)cgroup_fd;
@@ -540,6 +544,7 @@ int attach_program(int cgroup_fd, int prog_fd, uint32_t flags, int replace_fd) {
         a.replace_bpf_fd = (uint32_t)replace_fd;
     }
     if (sys_bpf(BPF_PROG_ATTACH, &a) != 0) {
+        if (lost_race && replace_fd >= 0 && errno == ENOENT) *lost_race = true;
         set_error("bpf(BPF_PROG_ATTACH, flags 0x%x): %s", a.attach_flags, strerror(errno));
         return GMP_ERR_SYS;
     }
@@ -859,44 +864,55 @@ extern "C" int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_
         Fd cg;
         int rc = open_cgroup(cgroup_dir, &cg);
         if (rc != GMP_OK) return rc;
-        std::vector<uint32_t> ids;
-        uint32_t flags = 0;
-        rc = query_programs(cg.fd, &ids, &flags);
-        if (rc != GMP_OK) return rc;
-        // 1. plan and 2. load every replacement before 3. attaching any: a program that cannot be edited, or a
-        //    replacement the verifier refuses, leaves the cgroup untouched
-        struct Step {
-            Fd old_fd, new_fd;
-            bool changed = false;
-        };
-        std::vector<Step> steps(ids.size());
-        for (size_t k = 0; k < ids.size(); ++k) {
-            rc = program_fd_by_id(ids[k], &steps[k].old_fd);
-            if (rc != GMP_OK) return rc;
-            std::vector<gmp_bpf_insn> insns, fresh;
-            rc = read_program(steps[k].old_fd.fd, &insns);
-            if (rc != GMP_OK) return rc;
-            rc = plan_replacement(insns, rules, n_rules, grant != 0, &fresh, &steps[k].changed);
-            if (rc != GMP_OK) return rc;
-            if (!steps[k].changed) continue;
-            rc = load_program(fresh, &steps[k].new_fd);
-            if (rc != GMP_OK) return rc;
+        // Editors of this library take turns (advisory lock on the directory, dropped when cg closes); a writer that does
+        // not know about the lock - the container runtime - is caught by the compare-and-swap below instead.
+        if (flock(cg.fd, LOCK_EX) != 0) {
+            set_error("flock %s: %s", cgroup_dir, strerror(errno));
+            return (int)GMP_ERR_SYS;
         }
-        const bool multi = (flags & BPF_F_ALLOW_MULTI) != 0;
-        for (size_t k = 0; k < steps.size(); ++k) {
-            if (!steps[k].changed) continue;
-            rc = multi ? attach_program(cg.fd, steps[k].new_fd.fd, BPF_F_ALLOW_MULTI, steps[k].old_fd.fd)
-                       : attach_program(cg.fd, steps[k].new_fd.fd, flags, -1);  // single-program attachment: attaching replaces
-            if (rc == GMP_OK) continue;
-            // an attach failed half way (not expected once the loads succeeded): put the earlier programs back
-            const std::string why = gmp_last_error();
-            for (size_t j = 0; j < k; ++j) {
-                if (!steps[j].changed) continue;
-                if (multi) (void)attach_program(cg.fd, steps[j].old_fd.fd, BPF_F_ALLOW_MULTI, steps[j].new_fd.fd);
-                else (void)attach_program(cg.fd, steps[j].old_fd.fd, flags, -1);
+        std::vector<uint32_t> ids;
+        for (int attempt = 0;; ++attempt) {
+            uint32_t flags = 0;
+            bool lost_race = false;
+            rc = query_programs(cg.fd, &ids, &flags);
+            if (rc != GMP_OK) return rc;
+            // 1. plan and 2. load every replacement before 3. attaching any: a program that cannot be edited, or a
+            //    replacement the verifier refuses, leaves the cgroup untouched
+            struct Step {
+                Fd old_fd, new_fd;
+                bool changed = false;
+            };
+            std::vector<Step> steps(ids.size());
+            for (size_t k = 0; k < ids.size(); ++k) {
+                rc = program_fd_by_id(ids[k], &steps[k].old_fd);
+                if (rc != GMP_OK) return rc;
+                std::vector<gmp_bpf_insn> insns, fresh;
+                rc = read_program(steps[k].old_fd.fd, &insns);
+                if (rc != GMP_OK) return rc;
+                rc = plan_replacement(insns, rules, n_rules, grant != 0, &fresh, &steps[k].changed);
+                if (rc != GMP_OK) return rc;
+                if (!steps[k].changed) continue;
+                rc = load_program(fresh, &steps[k].new_fd);
+                if (rc != GMP_OK) return rc;
             }
-            set_error("%s (earlier replacements rolled back)", why.c_str());
-            return rc;
+            const bool multi = (flags & BPF_F_ALLOW_MULTI) != 0;
+            for (size_t k = 0; k < steps.size(); ++k) {
+                if (!steps[k].changed) continue;
+                rc = multi ? attach_program(cg.fd, steps[k].new_fd.fd, BPF_F_ALLOW_MULTI, steps[k].old_fd.fd, &lost_race)
+                           : attach_program(cg.fd, steps[k].new_fd.fd, flags, -1);  // single-program attachment: attaching replaces
+                if (rc == GMP_OK) continue;
+                // an attach failed half way (not expected once the loads succeeded): put the earlier programs back
+                const std::string why = gmp_last_error();
+                for (size_t j = 0; j < k; ++j) {
+                    if (!steps[j].changed) continue;
+                    if (multi) (void)attach_program(cg.fd, steps[j].old_fd.fd, BPF_F_ALLOW_MULTI, steps[j].new_fd.fd);
+                    else (void)attach_program(cg.fd, steps[j].old_fd.fd, flags, -1);
+                }
+                if (lost_race && attempt < 8) break;  // somebody else edited this cgroup in between: read it again
+                set_error("%s (earlier replacements rolled back)", why.c_str());
+                return rc;
+            }
+            if (!lost_race) break;
         }
         if (programs) *programs = (int)ids.size();
         return (int)GMP_OK;

@@ -229,3 +229,38 @@ def test_cri_runtime_container_ids(cid, driver, leaf):
     ref_id = cid.replace("docker://", "", 1)
     assert off.endswith("/" + ref_id if driver == "cgroupfs" else f"/docker-{ref_id}.scope")
     assert on.rsplit("/", 1)[0] == off[:len(on.rsplit("/", 1)[0])]   # same pod-level directory either way
+
+
+def test_concurrent_editors_of_one_cgroup_do_not_lose_updates(fake_nvml):
+    """Two workers (threads here) granting and revoking different GPUs on the same cgroup at once.  The replacement names
+    the program it read (BPF_F_REPLACE): whoever loses the race gets ENOENT from the kernel, re-reads and tries again,
+    so no grant is overwritten by a stale read-modify-write."""
+    import threading
+
+    fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        baseline = attached(t)[0]
+        errors = []
+
+        def editor(minors):
+            try:
+                for _ in range(40):
+                    for m in minors:
+                        c.update_devices(t.cgroup_dir, [c.gpu_rule(m)], True)
+                    for m in minors:
+                        c.update_devices(t.cgroup_dir, [c.gpu_rule(m)], False)
+                for m in minors:
+                    c.update_devices(t.cgroup_dir, [c.gpu_rule(m)], True)
+            except Exception as e:  # noqa: BLE001
+                errors.append(e)
+
+        threads = [threading.Thread(target=editor, args=(ms,)) for ms in ([0, 1], [2, 3], [4, 5], [6, 7])]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        assert errors == []
+        rules, _ = c.decode(attached(t)[0][0])
+        assert sorted(r.minor for r in rules if r.major == 195) == list(range(8))      # every editor's last grant is there
+        assert c.update_devices(t.cgroup_dir, [c.gpu_rule(m) for m in range(8)], False) == 1
+        assert attached(t)[0] == baseline
