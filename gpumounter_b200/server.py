@@ -74,6 +74,12 @@ class Cluster:
         """kubelet v1alpha1 PodResourcesLister/List (ref: collector.go:182-194)"""
         raise NotImplementedError
 
+    def wait_for_pod_event(self, namespace: str, names: Sequence[str], timeout_s: float) -> bool:
+        """Extension (the reference spins on Get, allocator.go:246,295): block until one of the pods
+        changes - a watch on the namespace - or `timeout_s` passes, and return True.  The default says "no watch here"
+        (False) and the caller sleeps between rounds instead."""
+        return False
+
 
 ProbeHook = Callable[[Pod, Sequence[device.NvidiaGPU]], "tuple[int, dict]"]
 
@@ -113,7 +119,7 @@ class GPUMountImpl:
         return self.allocator.GetRemoveGPU(ownerPod.name, ownerPod.namespace, list(uuids))
 
     # ---- slave pods (ref: allocator.go:40-99, 128-156, 236-317) ------------------------------------------------
-    def _poll(self, step: Callable[[], Optional[str]]) -> str:
+    def _poll(self, step: Callable[[], Optional[str]], podNames: Sequence[str] = ()) -> str:
         deadline = None if self.poll_timeout_s is None else time.monotonic() + self.poll_timeout_s
         delay = self.poll_interval_s
         while True:
@@ -122,8 +128,11 @@ class GPUMountImpl:
                 return verdict
             if deadline is not None and time.monotonic() > deadline:
                 return FailedCreated
-            time.sleep(delay)
-            delay = min(delay * 2, 0.25)
+            # a cluster with a watch wakes us on the next pod event (re-checked at least once a second);
+            # without one: sleep with back-off, where the reference spins
+            if not self.cluster.wait_for_pod_event(GPUPoolNamespace, podNames, 1.0):
+                time.sleep(delay)
+                delay = min(delay * 2, 0.25)
 
     def checkCreateState(self, podNames: Sequence[str]) -> str:  # ref: allocator.go:236-282
         def one_round() -> Optional[str]:
@@ -145,7 +154,7 @@ class GPUMountImpl:
                     flag = False
             return SuccessfullyCreated if flag else None
 
-        return self._poll(one_round)
+        return self._poll(one_round, podNames)
 
     def checkDeleteState(self, podNames: Sequence[str]) -> str:  # ref: allocator.go:284-317
         def one_round() -> Optional[str]:
@@ -160,7 +169,7 @@ class GPUMountImpl:
                 flag = False
             return SuccessfullyDeleted if flag else None
 
-        v = self._poll(one_round)
+        v = self._poll(one_round, podNames)
         return FailedDeleted if v == FailedCreated else v
 
     def GetAvailableGPU(self, ownerPod: Pod, totalGpuNum: int, gpuNumPerPod: int) -> List[device.NvidiaGPU]:

@@ -232,3 +232,55 @@ def test_add_and_remove_on_a_containerd_pod_on_the_unified_hierarchy(fake_nvml):
         assert impl.RemoveGPU(remove([FAKE_UUIDS[0], FAKE_UUIDS[1]], force=True)).remove_gpu_result == api.RemoveGPUResult_Success
         assert member.wait(timeout=5) == -15 and t.nodes() == [] and not cluster.alloc
         assert [cgroup2.read_program(i) for i in cgroup2.device_programs(t.cgroup_dir)[0]] == baseline
+
+
+def test_a_cluster_with_a_watch_is_woken_by_events_instead_of_polling(fake_nvml):
+    """Extension: where the reference spins on Get (allocator.go:246,295), a cluster that can watch
+    blocks the handler until a pod event arrives.  The slave pod here becomes Running 50 ms after creation; the handler
+    reads its status exactly twice (Pending, then Running after the one event) and never sleeps on its own."""
+    import threading
+    import time
+
+    cfg = fake_nvml()
+    gpus = [device.New(m, u) for u, m, _ in cfg]
+
+    class WatchingCluster(FakeCluster):
+        def __init__(self, *a):
+            super().__init__(*a, pending_polls=0)
+            self.event = threading.Event()
+            self.running = set()
+            self.status_reads = 0
+            self.waits = 0
+
+        def create_slave_pod(self, name, owner, gpu_num):
+            super().create_slave_pod(name, owner, gpu_num)
+
+            def start():
+                time.sleep(0.05)
+                self.running.add(name)
+                self.event.set()
+
+            threading.Thread(target=start, daemon=True).start()
+
+        def pod_status(self, namespace, name):
+            self.status_reads += 1
+            if name in self.alloc and name not in self.running:
+                return server.PodStatus("Pending", None)
+            return super().pod_status(namespace, name)
+
+        def wait_for_pod_event(self, namespace, names, timeout_s):
+            assert namespace == "gpu-pool" and len(names) == 1
+            self.waits += 1
+            self.event.wait(timeout_s)
+            self.event.clear()
+            return True
+
+    with harness.Target() as t:
+        cluster = WatchingCluster([target_pod()], [u for u, _, _ in cfg])
+        env = MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+        impl = server.GPUMountImpl(cluster, gpus=gpus, env=env, poll_interval_s=30.0)   # a sleep would blow the timing
+        t0 = time.monotonic()
+        assert impl.AddGPU(add(n=1)).add_gpu_result == api.AddGPUResult_Success
+        assert time.monotonic() - t0 < 5.0
+        assert cluster.waits == 1 and cluster.status_reads == 2
+        assert len(t.nodes()) == 1
