@@ -27,8 +27,8 @@ int check_node(const std::string& path, int missing_code, int denied_code) {
     }
     const int e = errno;
     set_error("%s: %s", path.c_str(), strerror(e));
-    if (e == ENOENT || e == ENOTDIR) return missing_code;
-    return denied_code;  // EPERM / EACCES: the device cgroup (or file mode) refuses the open
+    if (e == EPERM || e == EACCES) return denied_code;  // the device cgroup (v1 list or v2 program) or the file mode refuses
+    return missing_code;  // ENOENT / ENOTDIR: no node; ENXIO / ENODEV: a node with no device behind it (wrong minor, no driver)
 }
 
 int check_nodes(const gmp_device* expected, int n, const char* dev_dir) {

@@ -70,7 +70,7 @@ enum {
     GMP_ERR_BUSY             = -17, /* GPU has processes of the pod and force is off (ref: util.go:106-109) */
     GMP_ERR_NODE_CTL         = -18, /* /dev/nvidiactl missing or not openable from the probing context */
     GMP_ERR_NODE_UVM         = -19, /* /dev/nvidia-uvm missing or not openable */
-    GMP_ERR_NODE_GPU         = -20, /* /dev/nvidiaN missing */
+    GMP_ERR_NODE_GPU         = -20, /* /dev/nvidiaN missing, or present with no device behind it (ENXIO / ENODEV) */
     GMP_ERR_NODE_DENIED      = -21, /* /dev/nvidiaN exists but open() is refused (device cgroup) */
     GMP_ERR_DRIVER_LIB       = -22, /* libcuda.so.1 not resolvable from the probing context */
     GMP_ERR_STILL_MOUNTED    = -23, /* after an unmount: the device node is still there (or still opens) in the pod */

@@ -264,3 +264,28 @@ def test_concurrent_editors_of_one_cgroup_do_not_lose_updates(fake_nvml):
         assert sorted(r.minor for r in rules if r.major == 195) == list(range(8))      # every editor's last grant is there
         assert c.update_devices(t.cgroup_dir, [c.gpu_rule(m) for m in range(8)], False) == 1
         assert attached(t)[0] == baseline
+
+
+def test_real_probe_binary_sees_the_v2_verdict_from_inside_the_pod(fake_nvml):
+    """gpumounter-probe --nodes-only, fexecve'd inside the target (v2 cgroup joined, mount namespace entered): a node
+    whose device the filter refuses is GMP_ERR_NODE_DENIED; once mounted, the open gets past the filter (and finds no
+    driver on this box: GMP_ERR_NODE_GPU with ENXIO's text, where a GPU box would go on to CUDA)."""
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        env, pod = env_of(t), product_pod()
+        u, m, _ = gpus_cfg[0]
+        gpu = device.New(m, u)
+        for name in ("nvidiactl", "nvidia-uvm"):
+            open(f"/proc/{t.pid}/root{t.devdir}/{name}", "w").close()
+        os.mknod(t.node_path_in_target(m), 0o666 | 0o020000, os.makedev(195, m))   # a node, but no grant
+        rc, rep = util.ProbeInPod(pod, [gpu], ["--dev-dir", t.devdir, "--nodes-only"], env, raise_on_error=False)
+        assert rc == _lib.GMP_ERR_NODE_DENIED and rep["nodes_status"] == _lib.GMP_ERR_NODE_DENIED, rep
+        assert "Operation not permitted" in rep["detail"]
+        os.unlink(t.node_path_in_target(m))
+        util.MountGPU(pod, gpu, env)
+        rc, rep = util.ProbeInPod(pod, [gpu], ["--dev-dir", t.devdir, "--nodes-only"], env, raise_on_error=False)
+        assert rc in (_lib.GMP_ERR_NODE_GPU, _lib.GMP_ERR_DRIVER_LIB, 0), rep
+        assert "Operation not permitted" not in rep["detail"]
+        util.UnmountGPU(pod, gpu, False, env)
+        rc, gone = util.VerifyUnmountedInPod(pod, [gpu], env, dev_dir=t.devdir, raise_on_error=False)
+        assert rc == 0 and gone["status"] == 0
