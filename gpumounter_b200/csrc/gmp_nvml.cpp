@@ -130,6 +130,14 @@ NvmlHold::NvmlHold() : session_(nullptr) {
 
 NvmlHold::~NvmlHold() { delete static_cast<NvmlSession*>(session_); }
 
+namespace {
+std::mutex g_holds_mu;
+std::vector<NvmlSession*>& holds() {
+    static std::vector<NvmlSession*>* v = new std::vector<NvmlSession*>();
+    return *v;
+}
+}  // namespace
+
 }  // namespace gmp
 
 using namespace gmp;
@@ -139,6 +147,32 @@ using namespace gmp;
         nvmlReturn_t r__ = (call);                       \
         if (r__ != NVML_SUCCESS) return (sess).fail(r__, what); \
     } while (0)
+
+extern "C" int gmp_nvml_hold(int acquire) {
+    clear_error();
+    std::lock_guard<std::mutex> lock(g_holds_mu);
+    if (acquire) {
+        NvmlSession* s = new (std::nothrow) NvmlSession();
+        if (s == nullptr) {
+            set_error("out of memory");
+            return GMP_ERR_NOMEM;
+        }
+        const int rc = s->open();
+        if (rc != GMP_OK) {
+            delete s;
+            return rc;
+        }
+        holds().push_back(s);
+        return GMP_OK;
+    }
+    if (holds().empty()) {
+        set_error("gmp_nvml_hold(0) without a matching gmp_nvml_hold(1)");
+        return GMP_ERR_INVALID;
+    }
+    delete holds().back();
+    holds().pop_back();
+    return GMP_OK;
+}
 
 extern "C" int gmp_enumerate_nvml(gmp_device* out, int cap, int* n) {
     clear_error();

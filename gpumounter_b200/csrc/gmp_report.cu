@@ -3,6 +3,7 @@
 // cgroup and mount namespace, right after the mount loop (ref: pkg/server/gpu-mount/server.go:97-98).
 
 #include "gmp_internal.h"
+#include "gmp_nvml_hold.h"
 
 #include <dlfcn.h>
 #include <errno.h>
@@ -11,6 +12,8 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <memory>
+#include <new>
 #include <string>
 #include <thread>
 #include <vector>
@@ -162,12 +165,17 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
     gmp_device nvml[GMP_MAX_DEVICES];
     int n_nvml = 0;
     std::string nvml_error;
+    // One NVML attach for the whole probe: the enumeration, the per-GPU health samples and the P2P status matrices each
+    // bracket themselves with nvmlInit_v2/nvmlShutdown, and a cold attach costs 30-140 ms (8-GPU host: 140 ms, i.e. over a
+    // second for 8 health samples).  Taken on the NVML thread so that it overlaps cuInit; released when the probe returns.
+    std::unique_ptr<NvmlHold> nvml_hold;
     std::thread nvml_thread;
     if (o.flags & GMP_PROBE_F_SKIP_NVML) {
         out->nvml_status = GMP_ERR_UNAVAILABLE;
     } else {
         nvml_thread = std::thread([&]() {
             const uint64_t tn = now_ns();
+            nvml_hold.reset(new (std::nothrow) NvmlHold());
             out->nvml_status = gmp_enumerate_nvml(nvml, GMP_MAX_DEVICES, &n_nvml);
             if (out->nvml_status != GMP_OK) {
                 n_nvml = 0;  // reported, not fatal: a pod need not ship libnvidia-ml

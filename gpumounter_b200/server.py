@@ -255,20 +255,23 @@ class GPUMountImpl:
         if len(removeGPUs) == 0:
             return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_GPUNotFound)  # server.go:130-135
         slavePodNames = []
-        for g in removeGPUs:  # server.go:139-153
-            slavePodNames.append(g.PodName)
+        # the busy check asks NVML once per GPU here and once more inside the unmount (each init .. shutdown, as
+        # nvidia.go:58-63): one attach held across the handler makes those calls cheap (30-140 ms each otherwise)
+        with util.NvmlAttached():
+            for g in removeGPUs:  # server.go:139-153
+                slavePodNames.append(g.PodName)
+                try:
+                    procs = util.GetPodGPUProcesses(targetPod, g, self.env)
+                except ProbeError as e:
+                    raise RpcError(str(e))
+                if procs is not None and not request.force:
+                    return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_GPUBusy)
             try:
-                procs = util.GetPodGPUProcesses(targetPod, g, self.env)
+                util.UnmountGPUs(targetPod, removeGPUs, bool(request.force), self.env)  # server.go:155-168, batched
             except ProbeError as e:
+                if e.code == GMP_ERR_BUSY:  # the GPUBusy sentinel of util.go:108 / server.go:158
+                    return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_GPUBusy)
                 raise RpcError(str(e))
-            if procs is not None and not request.force:
-                return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_GPUBusy)
-        try:
-            util.UnmountGPUs(targetPod, removeGPUs, bool(request.force), self.env)  # server.go:155-168, batched
-        except ProbeError as e:
-            if e.code == GMP_ERR_BUSY:  # the GPUBusy sentinel of util.go:108 / server.go:158
-                return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_GPUBusy)
-            raise RpcError(str(e))
         self.DeleteSlavePods(slavePodNames)  # server.go:171-175
         return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_Success)
 

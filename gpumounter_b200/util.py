@@ -59,6 +59,21 @@ def CanMount(mountType: str, isEntireMount: bool) -> bool:  # ref: util.go:207-2
     return bool(lib().gmp_can_mount(MOUNT_TYPE_CODE[mountType], int(isEntireMount)))
 
 
+class NvmlAttached:
+    """`with NvmlAttached():` keeps NVML attached for the block (gmp_nvml_hold), so that the per-GPU process queries made
+    inside it do not each pay a cold nvmlInit_v2.  Best effort: where NVML cannot be attached the block runs anyway and
+    the queries report the error themselves, exactly as without the hold."""
+
+    def __enter__(self):
+        self.held = lib().gmp_nvml_hold(1) == 0
+        return self
+
+    def __exit__(self, *exc):
+        if self.held:
+            lib().gmp_nvml_hold(0)
+        return False
+
+
 def ProbeInPod(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = (), env: Optional[MountEnv] = None,
                probe_exe: Optional[str] = None, raise_on_error: bool = True):
     """Run gpumounter-probe inside the pod (device cgroup + mount namespace) and return (status, report dict).

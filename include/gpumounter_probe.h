@@ -122,6 +122,16 @@ GMP_API int gmp_device_sets_equal(const gmp_device* a, int na, const gmp_device*
 /* Driver and NVML version strings (ref: pkg/util/gpu/collector/nvml/nvml.go:83-100; 80-byte buffers there). */
 GMP_API int gmp_nvml_versions(char* driver, size_t driver_cap, char* nvml, size_t nvml_cap);
 
+/*
+ * Keeps NVML attached between calls.  Every NVML-backed entry point brackets itself with nvmlInit_v2 / nvmlShutdown, as
+ * the reference does per query (ref: pkg/device/nvidia.go:58-63); NVML counts those references, and a cold attach costs
+ * 30-140 ms.  A caller about to make several such calls (RemoveGPU's busy check asks once per GPU, ref:
+ * server.go:139-153, then again inside UnmountGPU, util.go:100-109) takes one reference first - acquire != 0 - and gives
+ * it back - acquire == 0 - when done; the calls in between then cost microseconds.  No reference counterpart.
+ * GMP_ERR_NVML_NOT_FOUND / GMP_ERR_NVML when NVML cannot be attached, GMP_ERR_INVALID for an unmatched release.
+ */
+GMP_API int gmp_nvml_hold(int acquire);
+
 typedef struct gmp_process_info {
     uint32_t pid;              /* host PID (the worker runs with hostPID) */
     uint32_t reserved;

@@ -2,6 +2,7 @@
 P2P status, fault injection.  Mirrors what the reference's nvml_test.go / collector_test.go poke at by hand."""
 
 import ctypes
+import os
 
 import pytest
 
@@ -147,3 +148,34 @@ def test_sessions_reuse_one_library_image_and_leak_no_descriptors(fake_nvml):
         assert lib().gmp_nvml_versions(d, 80, n, 80) == 0
     assert len(os.listdir("/proc/self/fd")) == fds0
     assert _maps_count("libfake_nvml") == 1
+
+
+def test_hold_makes_nested_sessions_share_one_attach(fake_nvml):
+    fake_nvml()
+    cold = ctypes.CDLL(os.environ["GPUMOUNTER_NVML_LIB"]).fake_nvml_cold_inits
+    cold.restype = ctypes.c_uint
+    before = cold()
+    for _ in range(3):
+        probe.enumerate_nvml()
+    assert cold() - before == 3                      # as the reference: one attach per query
+    before = cold()
+    assert lib().gmp_nvml_hold(1) == 0
+    assert lib().gmp_nvml_hold(1) == 0               # holds nest
+    for _ in range(3):
+        probe.enumerate_nvml()
+    assert lib().gmp_nvml_hold(0) == 0
+    probe.enumerate_nvml()
+    assert lib().gmp_nvml_hold(0) == 0
+    assert cold() - before == 1
+    assert lib().gmp_nvml_hold(0) == _lib.GMP_ERR_INVALID     # unmatched release
+    probe.enumerate_nvml()
+    assert cold() - before == 2                      # released: the next query attaches again (fresh device list)
+
+
+def test_hold_without_nvml_is_an_error_and_changes_nothing(monkeypatch):
+    monkeypatch.setenv("GPUMOUNTER_NVML_LIB", "/nonexistent/libnvidia-ml.so.1")
+    assert lib().gmp_nvml_hold(1) == _lib.GMP_ERR_NVML_NOT_FOUND
+    assert lib().gmp_nvml_hold(0) == _lib.GMP_ERR_INVALID
+    from gpumounter_b200 import util
+    with util.NvmlAttached() as h:
+        assert h.held is False

@@ -284,3 +284,17 @@ def test_a_cluster_with_a_watch_is_woken_by_events_instead_of_polling(fake_nvml)
         assert time.monotonic() - t0 < 5.0
         assert cluster.waits == 1 and cluster.status_reads == 2
         assert len(t.nodes()) == 1
+
+
+def test_remove_gpu_attaches_nvml_once(world):
+    """RemoveGPU asks NVML about every GPU twice (server.go:139-153, then util.go:100-109).  One attach covers it all."""
+    import ctypes
+    import os
+
+    impl, cluster, t, fake_nvml, _ = world
+    assert impl.AddGPU(add(n=4)).add_gpu_result == api.AddGPUResult_Success
+    cold = ctypes.CDLL(os.environ["GPUMOUNTER_NVML_LIB"]).fake_nvml_cold_inits
+    cold.restype = ctypes.c_uint
+    before = cold()
+    assert impl.RemoveGPU(remove(FAKE_UUIDS[:4])).remove_gpu_result == api.RemoveGPUResult_Success
+    assert cold() - before == 1 and t.nodes() == []
