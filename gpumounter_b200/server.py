@@ -88,8 +88,12 @@ class GPUMountImpl:
     """ref: server.go:17-32"""
 
     def __init__(self, cluster: Cluster, gpus: Optional[Sequence[device.NvidiaGPU]] = None, env: Optional[MountEnv] = None,
-                 probe_hook: Optional[ProbeHook] = None, poll_interval_s: float = 0.002, poll_timeout_s: Optional[float] = None):
+                 probe_hook: Optional[ProbeHook] = None, poll_interval_s: float = 0.002, poll_timeout_s: Optional[float] = None,
+                 extended_response: bool = False):
         self.cluster = cluster
+        # additive wire surface (SURVEY.md 8f rank 3): answer AddGPU with the probe verdict in NEW field numbers (2..4);
+        # a peer built from the reference's api.proto skips them as unknown fields and sees the same enum in field 1
+        self.extended_response = extended_response
         self.env = env
         self.probe_hook = probe_hook
         self.poll_interval_s = poll_interval_s
@@ -236,9 +240,17 @@ class GPUMountImpl:
                 except (ClusterError, NotFound):
                     pass
             raise RpcError(ServiceInternalError)
+        status, report = None, None
         if self.probe_hook is not None:  # new: prove the mounted GPUs usable from inside the pod
             status, report = self.probe_hook(targetPod, gpuResources)
             self.last_probe_report = dict(report, status=status)
+        if self.extended_response:
+            import json as _json
+
+            return api.ExtendedAddGPUResponse(add_gpu_result=api.AddGPUResult_Success,
+                                              probe_status=0 if status is None else int(status),
+                                              probe_report="" if report is None else _json.dumps(report, separators=(",", ":")),
+                                              mounted_uuids=[g.UUID for g in gpuResources])
         return api.AddGPUResponse(add_gpu_result=api.AddGPUResult_Success)
 
     def RemoveGPU(self, request) -> "api.RemoveGPUResponse":  # ref: server.go:101-179
