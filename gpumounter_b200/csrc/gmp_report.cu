@@ -90,14 +90,33 @@ struct Json {
                 char esc[8];
                 snprintf(esc, sizeof(esc), "\\u%04x", (unsigned char)*c);
                 s += esc;
-            } else {
+            } else if ((unsigned char)*c < 0x80) {
                 s += *c;
+            } else {
+                // a well-formed UTF-8 sequence passes through; anything else (a path or message in another encoding)
+                // becomes U+FFFD so that the line is always valid JSON
+                const unsigned char b0 = (unsigned char)*c;
+                const int len = (b0 & 0xE0) == 0xC0 ? 2 : (b0 & 0xF0) == 0xE0 ? 3 : (b0 & 0xF8) == 0xF0 ? 4 : 0;
+                bool ok = len != 0 && b0 >= 0xC2 && b0 <= 0xF4;
+                for (int k = 1; ok && k < len; ++k) ok = ((unsigned char)c[k] & 0xC0) == 0x80;
+                if (ok && len == 3) ok = !(b0 == 0xE0 && (unsigned char)c[1] < 0xA0) && !(b0 == 0xED && (unsigned char)c[1] >= 0xA0);
+                if (ok && len == 4) ok = !(b0 == 0xF0 && (unsigned char)c[1] < 0x90) && !(b0 == 0xF4 && (unsigned char)c[1] >= 0x90);
+                if (ok) {
+                    s.append(c, (size_t)len);
+                    c += len - 1;
+                } else {
+                    s += "\\ufffd";
+                }
             }
         }
         s += '"';
     }
     void num(double v) {
-        char b[40];
+        if (!(v == v) || v > 1e300 || v < -1e300) {  // NaN / infinity have no JSON spelling
+            s += "null";
+            return;
+        }
+        char b[360];
         snprintf(b, sizeof(b), "%.3f", v);
         s += b;
     }

@@ -93,3 +93,30 @@ def test_bad_arguments():
     with pytest.raises(probe.ProbeError) as e:
         probe.probe_p2p(["GPU-a", ""])
     assert e.value.code == _lib.GMP_ERR_INVALID
+
+
+def test_report_json_is_always_valid_json():
+    """Whatever ends up in a report - non-finite rates, hostile strings, every counter at its maximum - the line parses."""
+    import ctypes
+    import math
+
+    r = probe.gmp_report()
+    ctypes.memset(ctypes.byref(r), 0xFF, ctypes.sizeof(r))           # every integer field at its extreme
+    r.status, r.n = -7, 2
+    r.detail = b'quote " backslash \\ newline \n tab \t bell \x07 <script> ' + "é€😀".encode() + b"\xff\xfe\xc3"
+    for i in range(2):
+        r.devices[i].uuid = b'GPU-"x"\\'
+        r.devices[i].pci_bus_id = b"0000:1B:00.0"
+        r.hbm[i].uuid = b"GPU-y"
+        r.hbm[i].write_gbs, r.hbm[i].read_gbs, r.hbm[i].copy_gbs = math.inf, -math.inf, math.nan
+        r.hbm[i].h2d_gbs = 1e308
+    r.p2p.n = 2
+    for k in range(4):
+        r.p2p.write_gbs[k] = math.nan
+    text = probe.report_json(r)
+    j = json.loads(text)
+    assert "\n" not in text and j["status"] == -7 and j["n_gpus"] == 2
+    assert j["hbm"][0]["write_gbs"] is None and j["hbm"][0]["read_gbs"] is None and j["hbm"][0]["copy_gbs"] is None
+    assert j["detail"].startswith('quote " backslash \\ newline \n tab \t bell \x07 <script>')
+    assert j["detail"].endswith("é€😀\ufffd\ufffd\ufffd")      # well-formed UTF-8 kept, stray bytes replaced
+    assert j["devices"][0]["uuid"] == 'GPU-"x"\\'
