@@ -697,7 +697,27 @@ std::string json_quote(const char* text) {
         else if (*c < 0x20 || *c == '<' || *c == '>' || *c == '&') {
             snprintf(esc, sizeof(esc), "\\u%04x", *c);
             out += esc;
-        } else out += (char)*c;
+        } else if (*c < 0x80) {
+            out += (char)*c;
+        } else {
+            // Go decodes a rune here: ill-formed UTF-8 is written as \ufffd, LINE/PARAGRAPH SEPARATOR are escaped
+            int need = (*c & 0xE0) == 0xC0 ? 1 : (*c & 0xF0) == 0xE0 ? 2 : (*c & 0xF8) == 0xF0 ? 3 : -1;
+            uint32_t rune = need == 1 ? (*c & 0x1Fu) : need == 2 ? (*c & 0x0Fu) : (*c & 0x07u);
+            for (int k = 1; need > 0 && k <= need; ++k) {
+                if ((c[k] & 0xC0) != 0x80) need = -1;
+                else rune = (rune << 6) | (c[k] & 0x3Fu);
+            }
+            static const uint32_t kMin[4] = {0, 0x80, 0x800, 0x10000};
+            if (need < 0 || rune < kMin[need] || rune > 0x10FFFF || (rune >= 0xD800 && rune <= 0xDFFF)) {
+                out += "\\ufffd";
+            } else if (rune == 0x2028 || rune == 0x2029) {
+                out += rune == 0x2028 ? "\\u2028" : "\\u2029";
+                c += need;
+            } else {
+                out.append(reinterpret_cast<const char*>(c), (size_t)need + 1);
+                c += need;
+            }
+        }
     }
     return out + "\"";
 }

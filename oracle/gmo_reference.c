@@ -75,6 +75,21 @@ void gmo_device_reset_state(gmo_gpu* g) { /* nvidia.go:52-56 */
     copy_str(g->state, sizeof(g->state), GMO_GPU_FREE_STATE);
 }
 
+/* Width of the UTF-8 sequence at c as Go's unicode/utf8 sees it, or 1 for an invalid one (table of RFC 3629: no
+ * overlong forms, no surrogates, nothing above U+10FFFF). */
+static int go_rune_width(const unsigned char* c) {
+    unsigned char lo = 0x80, hi = 0xBF;
+    int n;
+    if (c[0] >= 0xC2 && c[0] <= 0xDF) n = 2;
+    else if (c[0] >= 0xE0 && c[0] <= 0xEF) { n = 3; if (c[0] == 0xE0) lo = 0xA0; if (c[0] == 0xED) hi = 0x9F; }
+    else if (c[0] >= 0xF0 && c[0] <= 0xF4) { n = 4; if (c[0] == 0xF0) lo = 0x90; if (c[0] == 0xF4) hi = 0x8F; }
+    else return 1;
+    if (c[1] < lo || c[1] > hi) return 1;
+    for (int k = 2; k < n; ++k)
+        if (c[k] < 0x80 || c[k] > 0xBF) return 1;
+    return n;
+}
+
 /* encoding/json string escaping with the default HTML-safe mode that json.Marshal uses. */
 static void json_string(sb* s, const char* t) {
     sb_put(s, "\"");
@@ -94,8 +109,21 @@ static void json_string(sb* s, const char* t) {
                 if (*c < 0x20) {
                     snprintf(tmp, sizeof(tmp), "\\u%04x", *c);
                     sb_put(s, tmp);
-                } else {
+                } else if (*c < 0x80) {
                     sb_putn(s, (const char*)c, 1);
+                } else {
+                    /* utf8.DecodeRuneInString: RuneError with width 1 is written as \ufffd; U+2028 / U+2029 are
+                     * escaped (they break JavaScript); every other rune is copied (encoding/json encode.go, string()) */
+                    int w = go_rune_width(c);
+                    if (w == 1) {
+                        sb_put(s, "\\ufffd");
+                    } else if (w == 3 && c[0] == 0xE2 && c[1] == 0x80 && (c[2] == 0xA8 || c[2] == 0xA9)) {
+                        sb_put(s, c[2] == 0xA8 ? "\\u2028" : "\\u2029");
+                        c += 2;
+                    } else {
+                        sb_putn(s, (const char*)c, (size_t)w);
+                        c += w - 1;
+                    }
                 }
         }
     }

@@ -256,3 +256,40 @@ def test_random_ownership_selection_matches_oracle(owners, uuids, pod):
     assert a.GetMountType(pod, "default") == ref.mount_type_string(ref.get_mount_type(o_gpus, pod, "default"))
     assert [g.MinorNumber for g in a.GetPodGPUResources(pod, "default")] == ref.pod_gpu_resources(o_gpus, pod, "default")
     assert [g.MinorNumber for g in a.GetRemoveGPU(pod, "default", uuids)] == ref.get_remove_gpu(o_gpus, pod, "default", uuids)
+
+
+def test_device_string_follows_go_on_non_ascii_bytes():
+    """json.Marshal walks a string rune by rune (encoding/json encode.go): well-formed UTF-8 is copied, every byte of an
+    ill-formed sequence becomes \\ufffd, U+2028 / U+2029 are escaped, DEL is left alone.  Expected strings written out by
+    hand from those rules; oracle and library must both produce them."""
+    import ctypes
+
+    from gpumounter_b200 import lib
+    from gpumounter_b200._model import gmp_gpu
+    from oracle import gmo_ref_ctypes as ref
+
+    cases = [
+        (b"caf\xc3\xa9 \xe2\x82\xac \xf0\x9f\x98\x80", "café € 😀"),
+        (b"a\xe2\x80\xa8b\xe2\x80\xa9c", "a\\u2028b\\u2029c"),
+        (b"\xff", "\\ufffd"),
+        (b"\xed\xa0\x80", "\\ufffd\\ufffd\\ufffd"),            # a surrogate is not UTF-8
+        (b"\xc0\xaf", "\\ufffd\\ufffd"),                        # overlong '/'
+        (b"\xf4\x90\x80\x80", "\\ufffd\\ufffd\\ufffd\\ufffd"),  # above U+10FFFF
+        (b"x\xe2\x82", "x\\ufffd\\ufffd"),                      # cut off mid-rune
+        (b"\x7f\x1f", "\x7f\\u001f"),
+    ]
+    for raw, want in cases:
+        g = gmp_gpu()
+        assert lib().gmp_device_new(3, b"GPU-x", ctypes.byref(g)) == 0
+        g.pod_name = raw
+        buf = ctypes.create_string_buffer(4096)
+        assert lib().gmp_device_string(ctypes.byref(g), buf, 4096) == 0
+        expected = ('{"MinorNumber":3,"DeviceFilePath":"/dev/nvidia3","UUID":"GPU-x","State":"GPU_FREE_STATE","PodName":"'
+                    + want + '","Namespace":""}').encode()
+        assert buf.value == expected, (raw, buf.value)
+        og = ref.gmo_gpu()
+        ref._lib().gmo_device_new(3, b"GPU-x", ctypes.byref(og))
+        og.pod_name = raw
+        obuf = ctypes.create_string_buffer(4096)
+        assert ref._lib().gmo_device_string(ctypes.byref(og), obuf, 4096) >= 0
+        assert obuf.value == expected, (raw, obuf.value)
