@@ -61,6 +61,13 @@ def GetCgroupNameOfPod(pod: Pod, env: Optional[MountEnv] = None) -> str:
     return buf.value.decode()
 
 
+def DetectCgroupVersion(env: Optional[MountEnv] = None) -> int:
+    """1: the v1 `devices` controller is mounted (also on hybrid hosts); 2: unified hierarchy only.  Extension, header 7."""
+    v = ctypes.c_int()
+    check(lib().gmp_detect_cgroup_version(env_ptr(env), ctypes.byref(v)), "gmp_detect_cgroup_version")
+    return v.value
+
+
 def GetDeviceGroupPath(cgroupPath: str, env: Optional[MountEnv] = None) -> str:  # ref: cgroup.go:115-118
     buf = ctypes.create_string_buffer(8192)
     check(lib().gmp_get_device_group_path(env_ptr(env), cgroupPath.encode(), buf, 8192), "GetDeviceGroupPath")

@@ -19,6 +19,7 @@
 #include <string.h>
 #include <sys/stat.h>
 #include <sys/sysmacros.h>
+#include <sys/vfs.h>
 #include <sys/types.h>
 #include <sys/wait.h>
 #include <unistd.h>
@@ -857,6 +858,27 @@ extern "C" int gmp_get_cgroup_name(const char* driver, const gmp_pod* pod, const
         std::string s;
         int rc = cgroup_name(driver, pod, container_id, &s);
         return rc != GMP_OK ? rc : emit(s, out, cap);
+    });
+}
+
+extern "C" int gmp_detect_cgroup_version(const gmp_mount_env* env, int* version) {
+    return guarded([&]() -> int {
+        REQUIRE(version != nullptr);
+        *version = 0;
+        const std::string v1 = or_default(env ? env->devices_root : nullptr, kDevicesRoot);
+        struct stat st;
+        if (stat(v1.c_str(), &st) == 0 && S_ISDIR(st.st_mode)) {
+            *version = 1;
+            return GMP_OK;
+        }
+        const std::string v2 = or_default(env ? env->cgroup2_root : nullptr, "/sys/fs/cgroup");
+        struct statfs fs;
+        if (statfs(v2.c_str(), &fs) == 0 && (unsigned long)fs.f_type == 0x63677270ul /* CGROUP2_SUPER_MAGIC */) {
+            *version = 2;
+            return GMP_OK;
+        }
+        set_error("neither %s (cgroup v1 devices controller) nor a cgroup2 file system at %s", v1.c_str(), v2.c_str());
+        return GMP_ERR_UNAVAILABLE;
     });
 }
 

@@ -683,6 +683,12 @@ enum {
     GMP_EXT_CGROUP_V2    = 1u << 1
 };
 
+/* Which hierarchy decides device access on this node: *version = 1 when <devices_root> (default
+ * /sys/fs/cgroup/devices) is a directory - the v1 controller, which also wins on hybrid hosts - else 2 when
+ * <cgroup2_root> (default /sys/fs/cgroup) is a cgroup2 file system, else GMP_ERR_UNAVAILABLE.  What a worker
+ * consults once at start to decide whether to set GMP_EXT_CGROUP_V2. */
+GMP_API int gmp_detect_cgroup_version(const gmp_mount_env* env, int* version);
+
 /* One rule of a cgroup device filter; the values are the kernel's (BPF_DEVCG_DEV_*, BPF_DEVCG_ACC_*). */
 enum { GMP_DEV_BLOCK = 1, GMP_DEV_CHAR = 2 };
 enum { GMP_DEV_ACC_MKNOD = 1, GMP_DEV_ACC_READ = 2, GMP_DEV_ACC_WRITE = 4, GMP_DEV_ACC_ALL = 7 };

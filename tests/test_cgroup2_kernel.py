@@ -289,3 +289,16 @@ def test_real_probe_binary_sees_the_v2_verdict_from_inside_the_pod(fake_nvml):
         util.UnmountGPU(pod, gpu, False, env)
         rc, gone = util.VerifyUnmountedInPod(pod, [gpu], env, dev_dir=t.devdir, raise_on_error=False)
         assert rc == 0 and gone["status"] == 0
+
+
+def test_detect_cgroup_version(tmp_path):
+    from gpumounter_b200 import cgroup
+
+    assert cgroup.DetectCgroupVersion() in (1, 2)                       # this machine, whatever it is
+    (tmp_path / "devices").mkdir()
+    assert cgroup.DetectCgroupVersion(MountEnv(devices_root=str(tmp_path / "devices"))) == 1
+    v2 = o.cgroup2_mount()
+    assert cgroup.DetectCgroupVersion(MountEnv(devices_root=str(tmp_path / "absent"), cgroup2_root=v2)) == 2
+    with pytest.raises(ProbeError) as e:
+        cgroup.DetectCgroupVersion(MountEnv(devices_root=str(tmp_path / "absent"), cgroup2_root=str(tmp_path)))
+    assert e.value.code == _lib.GMP_ERR_UNAVAILABLE
