@@ -432,7 +432,8 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
     j.raw("[");
     for (int i = 0; i < n; ++i) {
         const gmp_gpu_health& h = r->health[i];
-        if (r->ns_cuda_init == 0) break;  // never got as far as sampling (NODES_ONLY, or a failed node check)
+        static const gmp_gpu_health never_sampled = {};  // the report starts zeroed; step 4 fills 0xFF or real values
+        if (memcmp(&h, &never_sampled, sizeof(h)) == 0) continue;  // NODES_ONLY, or a failed node check
         auto opt32 = [](uint32_t v) { return v == UINT32_MAX ? -1ll : (long long)v; };
         auto opt64 = [](uint64_t v) { return v == UINT64_MAX ? -1ll : (long long)v; };
         j.sep();
