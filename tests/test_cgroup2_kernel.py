@@ -12,7 +12,6 @@ from gpumounter_b200 import ProbeError, _lib, cgroup2 as c, device, util
 from gpumounter_b200._model import EXT_CGROUP_V2, EXT_CRI_RUNTIMES, MountEnv, Pod
 from oracle import gmo_devfilter as o
 from tests import harness
-from tests.conftest import FAKE_UUIDS
 
 why = harness.can_run_cgroup2()
 pytestmark = pytest.mark.skipif(why is not None, reason=f"cgroup2 kernel path not testable here: {why}")

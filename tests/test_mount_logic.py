@@ -8,7 +8,7 @@ import pytest
 from hypothesis import given, settings
 from hypothesis import strategies as st
 
-from gpumounter_b200 import ProbeError, _lib, allocator, cgroup, collector, device, namespace, util
+from gpumounter_b200 import ProbeError, _lib, allocator, cgroup, device, namespace, util
 from gpumounter_b200._model import ContainerResources, MountEnv, Pod
 from oracle import gmo_ref_ctypes as ref
 

@@ -3,7 +3,6 @@ the reference, on a cluster-less target (own mount namespace + private /dev tmpf
 CPU only; needs root, unshare and nsenter (skipped otherwise)."""
 
 import os
-import time
 
 import pytest
 
