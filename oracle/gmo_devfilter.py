@@ -15,7 +15,8 @@ Parity: runc is a third-party dependency of container runtimes, not of the refer
 machine: PARITY UNPINNED against runc itself.  What pins the restatement instead: (1) the block layout and instruction
 counts of runc's own devicefilter_test.go expectations as remembered (prologue 0-5, a wildcard-'m' block is 6
 instructions, a (c,1,3,rwm) block 5), (2) the Linux kernel on this box, which verifies, attaches and ENFORCES the
-programs in tests/test_cgroup2_kernel.py (open() of a denied device returns EPERM, of a granted one succeeds).
+programs in tests/test_cgroup2_kernel.py (open() of a denied device returns EPERM, of a granted one succeeds; and for
+120 random ALU/JMP/LDX programs the kernel's mknod(2) verdict equals `interpret` and the library's gmp_devfilter_eval).
 """
 
 from __future__ import annotations

@@ -301,3 +301,85 @@ def test_detect_cgroup_version(tmp_path):
     with pytest.raises(ProbeError) as e:
         cgroup.DetectCgroupVersion(MountEnv(devices_root=str(tmp_path / "absent"), cgroup2_root=str(tmp_path)))
     assert e.value.code == _lib.GMP_ERR_UNAVAILABLE
+
+
+def test_interpreters_compute_what_the_kernel_computes(tmp_path):
+    """Random ALU / JMP / LDX device programs are attached to a scratch cgroup; a child inside it calls mknod(2) for a
+    handful of (type, major, minor) and the kernel's verdict (success / EPERM) is compared with gmp_devfilter_eval and with
+    the Python interpreter.  Programs the verifier refuses are skipped.  This is what pins both interpreters."""
+    import json
+    import random
+    import subprocess
+    import sys
+    import uuid
+
+    rng = random.Random(20240611)
+    alu = [0x00, 0x10, 0x20, 0x40, 0x50, 0x60, 0x70, 0xA0, 0xB0, 0xC0]
+    jmp = [0x10, 0x20, 0x30, 0x40, 0x50, 0x60, 0x70, 0xA0, 0xB0, 0xC0, 0xD0]
+    imms = [0, 1, 2, 7, 16, 31, 195, 0xFFFF, 0x7FFFFFFF, -1, -2]
+
+    def program():
+        n = rng.randint(1, 16)
+        prog = [(0x61, 2, 1, 0, 0), (0x61, 3, 1, 4, 0), (0x61, 4, 1, 8, 0), (0xB7, 0, 0, 0, rng.choice(imms)), (0xB7, 5, 0, 0, rng.choice(imms))]
+        for i in range(n):
+            kind = rng.randint(0, 9)
+            dst, src = rng.choice([0, 2, 3, 4, 5]), rng.choice([0, 2, 3, 4, 5])
+            if kind <= 5:
+                cls, op, use_reg = rng.choice([0x04, 0x07]), rng.choice(alu), rng.random() < 0.5
+                imm = rng.choice(imms)
+                if op in (0x60, 0x70, 0xC0) and not use_reg:
+                    imm = rng.choice([0, 1, 7, 16, 31])                      # the verifier refuses shifts >= the width
+                prog.append((cls | op | (0x08 if use_reg else 0), dst, src if use_reg else 0, 0, 0 if use_reg else imm))
+            elif kind == 6:
+                prog.append((rng.choice([0x84, 0x87]), dst, 0, 0, 0))
+            elif kind == 7:
+                prog.append(rng.choice([(0x61, dst, 1, 0, 0), (0x61, dst, 1, 4, 0), (0x61, dst, 1, 8, 0), (0x69, dst, 1, 0, 0),
+                                        (0x69, dst, 1, 2, 0), (0x71, dst, 1, 1, 0)]))
+            else:
+                cls, op, use_reg = rng.choice([0x05, 0x06]), rng.choice(jmp), rng.random() < 0.5
+                prog.append((cls | op | (0x08 if use_reg else 0), dst, src if use_reg else 0, rng.randint(0, n - 1 - i),
+                             0 if use_reg else rng.choice(imms)))
+        prog += [(0x57, 0, 0, 0, 1), (0x95, 0, 0, 0, 0)]   # r0 &= 1: the verifier wants a return value it can prove is 0 or 1
+        return prog
+
+    requests = [(t, ma, mi) for t in (c.DEV_CHAR, c.DEV_BLOCK) for ma, mi in [(1, 3), (195, 0), (195, 255), (0, 1), (4095, 1048575), (7, 16)]]
+    # (not 0:0: a character device 0:0 is overlayfs's whiteout, which vfs_mknod lets through without asking the filter)
+    child = (
+        "import json, os, stat, sys\n"
+        "cg, base, reqs = sys.argv[1], sys.argv[2], json.loads(sys.argv[3])\n"
+        "open(cg + '/cgroup.procs', 'w').write(str(os.getpid()))\n"
+        "out = []\n"
+        "for k, (t, ma, mi) in enumerate(reqs):\n"
+        "    path = f'{base}/n{k}'\n"
+        "    try:\n"
+        "        os.mknod(path, (stat.S_IFCHR if t == 2 else stat.S_IFBLK) | 0o600, os.makedev(ma, mi)); os.unlink(path); out.append(0)\n"
+        "    except OSError as e:\n"
+        "        out.append(e.errno)\n"
+        "print(json.dumps(out))\n")
+    root = o.cgroup2_mount()
+    checked = skipped = 0
+    while checked < 120 and checked + skipped < 600:
+        prog = program()
+        try:
+            fd = o.kernel_load(prog)
+        except OSError:
+            skipped += 1
+            continue
+        cg = f"{root}/gmp-fuzz-{uuid.uuid4().hex[:8]}"
+        os.mkdir(cg)
+        try:
+            o.kernel_attach(cg, fd)
+            os.close(fd)
+            out = subprocess.run([sys.executable, "-c", child, cg, str(tmp_path), json.dumps(requests)], capture_output=True, text=True,
+                                 timeout=60)
+            assert out.returncode == 0, out.stderr
+            verdicts = json.loads(out.stdout)
+        finally:
+            os.rmdir(cg)
+        for (t, ma, mi), err in zip(requests, verdicts):
+            assert err in (0, errno.EPERM), err
+            kernel_allows = err == 0
+            assert c.evaluate(prog, t, c.ACC_MKNOD, ma, mi) == kernel_allows, (prog, t, ma, mi)
+            assert o.interpret(prog, t, c.ACC_MKNOD, ma, mi) == kernel_allows, (prog, t, ma, mi)
+        checked += 1
+    assert checked == 120, (checked, skipped)

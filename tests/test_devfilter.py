@@ -224,3 +224,47 @@ def test_random_grant_revoke_sequences_on_both_layouts(rules, default_allow, for
             touched = type_ == c.DEV_CHAR and major == 195 and minor2 in state and (access & ~GPU_RW) == 0
             if not touched and not (type_ == c.DEV_CHAR and major == 195 and minor2 in state):
                 assert c.evaluate(prog, type_, access, major, minor2) == base(type_, access, major, minor2)
+
+
+# ---- the two interpreters against each other on arbitrary (forward-jumping) programs ---------------------------------
+ALU_OPS = [0x00, 0x10, 0x20, 0x30, 0x40, 0x50, 0x60, 0x70, 0x90, 0xA0, 0xB0, 0xC0]      # add sub mul div or and lsh rsh mod xor mov arsh
+JMP_OPS = [0x10, 0x20, 0x30, 0x40, 0x50, 0x60, 0x70, 0xA0, 0xB0, 0xC0, 0xD0]            # jeq jgt jge jset jne jsgt jsge jlt jle jslt jsle
+imm_st = st.sampled_from([0, 1, 2, 7, 16, 31, 32, 63, 195, 0xFFFF, 0x7FFFFFFF, -1, -2, -0x80000000])
+
+
+@st.composite
+def random_program(draw):
+    n = draw(st.integers(1, 24))
+    prog = [(0x61, 2, 1, 0, 0), (0x61, 3, 1, 4, 0), (0x61, 4, 1, 8, 0), (0xB7, 0, 0, 0, draw(imm_st)), (0xB7, 5, 0, 0, draw(imm_st))]
+    for i in range(n):
+        kind = draw(st.integers(0, 9))
+        dst, src = draw(st.integers(0, 5)), draw(st.integers(0, 5))
+        if dst == 1 or src == 1:
+            dst, src = 2, 3                                   # keep the context pointer out of the arithmetic
+        if kind <= 5:
+            cls = draw(st.sampled_from([0x04, 0x07]))
+            op = draw(st.sampled_from(ALU_OPS))
+            use_reg = draw(st.booleans())
+            prog.append((cls | op | (0x08 if use_reg else 0), dst, src if use_reg else 0, 0, 0 if use_reg else draw(imm_st)))
+        elif kind == 6:
+            prog.append((draw(st.sampled_from([0x84, 0x87])), dst, 0, 0, 0))                      # neg
+        elif kind == 7:
+            size = draw(st.sampled_from([(0x61, 4), (0x69, 2), (0x71, 1)]))
+            prog.append((size[0], dst, 1, draw(st.integers(0, 12 - size[1])), 0))                 # narrow context loads
+        else:
+            cls = draw(st.sampled_from([0x05, 0x06]))
+            op = draw(st.sampled_from(JMP_OPS))
+            use_reg = draw(st.booleans())
+            off = draw(st.integers(0, n - 1 - i))                                                  # forward only: terminates
+            prog.append((cls | op | (0x08 if use_reg else 0), dst, src if use_reg else 0, off, 0 if use_reg else draw(imm_st)))
+    prog.append((0x95, 0, 0, 0, 0))
+    return prog
+
+
+@settings(max_examples=400, deadline=None)
+@given(random_program(), st.sampled_from([1, 2]), st.integers(1, 7), st.sampled_from([0, 1, 195, 0xFFFFFFFF]), st.sampled_from([0, 3, 255, 0x80000000]))
+def test_interpreters_agree_on_random_programs(prog, type_, access, major, minor):
+    """gmp_devfilter_eval decides whether a revoke needs a deny rule in front of a foreign program, so it has to compute
+    what the kernel would: checked here against the independent Python interpreter on random ALU/JMP/LDX programs."""
+    want = o.interpret(prog, type_, access, major, minor)
+    assert c.evaluate(prog, type_, access, major, minor) == want
