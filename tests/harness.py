@@ -41,7 +41,7 @@ def can_run_cgroup2() -> Optional[str]:
 
 class Target:
     def __init__(self, real_cgroup: bool = False, qos_dir: str = "besteffort", cgroup2: bool = False, runtime_rules=None,
-                 runtime_program=None):
+                 runtime_program=None, container_whitelist: bool = False):
         self.base = tempfile.mkdtemp(prefix="gmp_target_")
         self.devdir = os.path.join(self.base, "dev")
         os.mkdir(self.devdir)
@@ -52,6 +52,9 @@ class Target:
         self.cgroup2 = cgroup2
         self.runtime_rules = runtime_rules
         self.runtime_program = runtime_program  # explicit instructions instead of runc's layout of runtime_rules
+        # real cgroup-v1 only: start from what a container runtime gives a pod WITHOUT GPUs (default-deny, the standard
+        # character devices, mknod of anything, the NVIDIA control devices) instead of the parent's allow-everything
+        self.container_whitelist = container_whitelist
         if cgroup2:
             from oracle import gmo_devfilter
 
@@ -78,6 +81,8 @@ class Target:
                     os.close(fd)
             else:
                 gmo_devfilter.kernel_attach_rules(self.cgroup_dir, rules)
+        if self.container_whitelist and self.real_cgroup and not self.cgroup2:
+            self._write_v1_whitelist()
         script = f"mount -t tmpfs -o mode=755 tmpfs {self.devdir} && echo ready && exec sleep 600"
         self.proc = subprocess.Popen(["unshare", "-m", "--propagation", "private", "sh", "-c", script],
                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
@@ -88,6 +93,25 @@ class Target:
             raise RuntimeError(f"target did not come up: {err}")
         self.register(self.proc.pid)
         return self
+
+    def _write_v1_whitelist(self) -> None:
+        def put(name, line):
+            with open(os.path.join(self.cgroup_dir, name), "w") as f:
+                f.write(line)
+
+        put("devices.deny", "a")
+        lines = ["c *:* m", "b *:* m", "c 1:3 rwm", "c 1:5 rwm", "c 1:7 rwm", "c 1:8 rwm", "c 1:9 rwm", "c 5:0 rwm", "c 5:1 rwm",
+                 "c 5:2 rwm", "c 136:* rwm", "c 195:255 rw"]          # ... /dev/nvidiactl
+        try:
+            with open("/proc/devices") as f:                          # nvidia-uvm, nvidia-caps: dynamic majors
+                for row in f:
+                    parts = row.split()
+                    if len(parts) == 2 and parts[1].startswith("nvidia-") and parts[0].isdigit():
+                        lines.append(f"c {parts[0]}:* rw")
+        except OSError:
+            pass
+        for line in lines:
+            put("devices.allow", line)
 
     def register(self, pid: int) -> None:
         procs = os.path.join(self.cgroup_dir, "cgroup.procs")

@@ -274,3 +274,34 @@ def test_unmount_is_verified_from_inside_the_pod(fake_nvml):
         assert rc == 0 and rep == {"status": 0, "verdict": "ok", "detail": "", "checked": 2}
         # the host's view of that directory was empty all along: the check really ran inside the target
         assert t.host_sees() == []
+
+
+@pytest.mark.skipif(not (os.path.isdir(REAL) and os.access(REAL, os.W_OK)), reason="no writable cgroup-v1 devices hierarchy")
+def test_real_v1_cgroup_gates_open_until_the_gpu_is_mounted(fake_nvml):
+    """A real cgroup-v1 devices group set up like a container without GPUs (default-deny + the standard devices + the
+    NVIDIA control node): the kernel refuses open() of a GPU node until MountGPU has written devices.allow, lets it through
+    afterwards (ENXIO: no driver on this box), and refuses again after UnmountGPU."""
+    import errno
+
+    fake_nvml()
+    try:
+        t = harness.Target(real_cgroup=True, container_whitelist=True).start()
+    except OSError as e:
+        pytest.skip(f"cannot create a devices cgroup: {e}")
+    try:
+        assert "c 195:255 rw" in t.read("devices.list") and "a *:* rwm" not in t.read("devices.list")
+        gpu = device.New(3, FAKE_UUIDS[0])
+        os.mknod(t.node_path_in_target(3), 0o666 | 0o020000, os.makedev(195, 3))
+        assert t.try_open(3) == errno.EPERM
+        os.unlink(t.node_path_in_target(3))
+        util.MountGPU(product_pod(), gpu, env_of(t))
+        assert t.try_open(3) in (errno.ENXIO, errno.ENODEV)
+        assert "c 195:3 rw\n" in t.read("devices.list")
+        util.UnmountGPU(product_pod(), gpu, False, env_of(t))
+        os.mknod(t.node_path_in_target(3), 0o666 | 0o020000, os.makedev(195, 3))
+        assert t.try_open(3) == errno.EPERM
+        os.unlink(t.node_path_in_target(3))
+    finally:
+        with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+            f.write(f"{t.pid}\n")
+        t.stop()

@@ -172,14 +172,31 @@ def mknod_like(src, dst):
     os.chmod(dst, 0o666)
 
 
-def to_usable(iters, hbm_bytes, n_gpus):
+def new_target(real_cgroup):
+    """real_cgroup: a real cgroup-v1 devices group set up like a container without GPUs (tests/harness.py), so that the
+    kernel gates every open() of the in-pod probe - otherwise a scratch directory that only records what was written."""
+    if real_cgroup:
+        return harness.Target(real_cgroup=True, container_whitelist=True)
+    return harness.Target()
+
+
+def release_target(t):
+    if getattr(t, "container_whitelist", False):  # the main process must leave the group before it can be removed
+        try:
+            with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+                f.write(f"{t.pid}\n")
+        except OSError:
+            pass
+
+
+def to_usable(iters, hbm_bytes, n_gpus, real_cgroup=False):
     """Real GPUs only: native mount into the target, then the in-pod probe; t1 is reported by the probe."""
     nv = {d.uuid: d for d in probe.enumerate_nvml()}
     cu = probe.enumerate_cuda()[:n_gpus]
     gpus = [(d.uuid, nv[d.uuid].minor) for d in cu]
     lat, phases, last = [], [], None
     for _ in range(iters):
-        with harness.Target() as t:
+        with new_target(real_cgroup) as t:
             # what nvidia-container-runtime provides to a pod started with NVIDIA_VISIBLE_DEVICES=none
             # (ref: docs/guide/QuickStart.md:9,26-28): the control nodes, but no GPU node
             for name in ("nvidiactl", "nvidia-uvm"):
@@ -202,6 +219,7 @@ def to_usable(iters, hbm_bytes, n_gpus):
             last = rep
             usable = rep["mono_usable_ns"]
             lat.append((usable - t0) / 1e9)
+            release_target(t)
             phases.append({"mount_ms": (t_mounted - t0) / 1e6, "exec_to_probe_start_ms": (rep["mono_start_ns"] - t_mounted) / 1e6,
                            "probe_start_to_usable_ms": rep["ms_to_usable"], "cuda_init_ms": rep["ms_cuda_init"],
                            "nvml_ms_overlapped": rep["ms_nvml"], "context_ms": max(h["ms_context"] for h in rep["hbm"]),
@@ -328,6 +346,8 @@ def main():
     ap.add_argument("--usable-bytes", type=int, default=1 << 30)
     ap.add_argument("--resident-iters", type=int, default=0,
                     help="> 0 only on a box with real GPUs: two-stage hook, kernels run from this (resident) process")
+    ap.add_argument("--real-cgroup", action="store_true",
+                    help="mount-to-usable inside a real cgroup-v1 devices group that denies GPUs until they are mounted")
     ap.add_argument("--churn-real-rounds", type=int, default=0, help="> 0 only on a box with real GPUs")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
@@ -389,8 +409,9 @@ def main():
         out["churn_1_8_1"] = {"skipped": "churn uses made-up UUIDs, which a real NVML refuses; run on a driver-less box"}
     if args.usable_iters > 0 and have_gpu:
         n_vis = len(probe.enumerate_cuda())
-        out["mount_to_usable"] = {str(n): to_usable(args.usable_iters, args.usable_bytes, n)
+        out["mount_to_usable"] = {str(n): to_usable(args.usable_iters, args.usable_bytes, n, args.real_cgroup)
                                   for n in (1, 2, 4, 8) if n <= n_vis}
+        out["mount_to_usable_cgroup"] = "real cgroup-v1 devices group, container whitelist" if args.real_cgroup else "scratch directory"
     if args.resident_iters > 0 and have_gpu:
         n_vis = len(probe.enumerate_cuda())
         out["mount_to_usable_resident_worker"] = {
