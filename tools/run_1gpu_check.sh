@@ -25,3 +25,7 @@ print(d["churn_real"])
 PY
 gpumounter_b200/gpumounter-probe --bytes 1G --iters 1 | python -c "
 import json,sys; j=json.load(sys.stdin); print({k: j[k] for k in ('status','ms_nodes','ms_cuda_init','ms_nvml','ms_hbm','ms_p2p','ms_to_usable','ms_total')})"
+# the same mount-to-usable, but inside a REAL cgroup-v1 devices group that denies GPU nodes until they are mounted
+# (never run on a GPU box yet: if cuInit needs a device the whitelist lacks, the probe says which open() was refused)
+timeout 200 python tools/mount_latency.py --iters 3 --gpus 1 --churn-rounds 0 --usable-iters 5 --real-cgroup \
+    --out gpurun_out/mount_latency_real_cgroup.json > gpurun_out/ml_real_cgroup.log 2>&1; tail -c 600 gpurun_out/ml_real_cgroup.log
