@@ -156,7 +156,7 @@ extern "C" const char* gmp_strerror(int code) {
     }
 }
 
-extern "C" int gmp_enumerate_cuda(gmp_device* out, int cap, int* n) {
+extern "C" int gmp_enumerate_cuda(gmp_device* out, int cap, int* n) try {
     clear_error();
     if (out == nullptr || n == nullptr || cap < 0) {
         set_error("NULL argument");
@@ -181,9 +181,11 @@ extern "C" int gmp_enumerate_cuda(gmp_device* out, int cap, int* n) {
     }
     *n = count;
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_device_sets_equal(const gmp_device* a, int na, const gmp_device* b, int nb) {
+extern "C" int gmp_device_sets_equal(const gmp_device* a, int na, const gmp_device* b, int nb) try {
     clear_error();
     if ((na > 0 && a == nullptr) || (nb > 0 && b == nullptr) || na < 0 || nb < 0) {
         set_error("NULL argument");
@@ -213,6 +215,8 @@ extern "C" int gmp_device_sets_equal(const gmp_device* a, int na, const gmp_devi
         used[hit] = 1;
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
 // ---- one-shot HBM probe ---------------------------------------------------------------
@@ -493,7 +497,7 @@ int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeReso
 
 }  // namespace
 
-extern "C" int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out) {
+extern "C" int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out) try {
     clear_error();
     if (out == nullptr) {
         set_error("out is NULL");
@@ -554,4 +558,6 @@ extern "C" int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm
         rc = GMP_ERR_VERIFY;
     }
     return out->status = rc;
+} catch (...) {
+    return ::gmp::caught_exception();
 }

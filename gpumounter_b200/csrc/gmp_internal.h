@@ -15,6 +15,8 @@ namespace gmp {
 // ---- error plumbing ---------------------------------------------------------
 void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
 void clear_error();
+// For `extern "C" int f(...) try { ... } catch (...) { return ::gmp::caught_exception(); }` (gmp_nvml.cpp)
+int caught_exception() noexcept;
 // Maps a CUDA failure to a GMP code and records "what: cudaGetErrorString".
 int cuda_fail(cudaError_t e, const char* what);
 

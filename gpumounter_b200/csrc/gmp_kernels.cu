@@ -783,7 +783,7 @@ extern "C" int gmp_hbm_write_pattern(void* dptr, size_t bytes, int pattern, uint
 }
 
 extern "C" int gmp_hbm_read_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed, gmp_verify_result* out,
-                                   void* stream) {
+                                   void* stream) try {
     clear_error();
     if (out == nullptr) {
         set_error("out is NULL");
@@ -804,6 +804,8 @@ extern "C" int gmp_hbm_read_verify(const void* dptr, size_t bytes, int pattern, 
     if (ef != cudaSuccess) return cuda_fail(ef, "cudaFree(accumulator)");
     decode_acc(raw, out);
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
 extern "C" int gmp_hbm_copy(void* dst, const void* src, size_t bytes, void* stream) {
@@ -856,7 +858,7 @@ extern "C" int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, v
 
 extern "C" unsigned long long gmp_kernel_launches(void) { return g_kernel_launches.load(std::memory_order_relaxed); }
 
-extern "C" int gmp_tune(const char* knob, int value) {
+extern "C" int gmp_tune(const char* knob, int value) try {
     clear_error();
     if (knob == nullptr) return GMP_ERR_INVALID;
     Tunables& t = tunables();
@@ -881,6 +883,8 @@ extern "C" int gmp_tune(const char* knob, int value) {
         *slot = value;
     }
     return *slot;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
 // ---- read-verify without any allocation -----------------------------------------------------
@@ -1047,7 +1051,7 @@ static cudaError_t launch_segments(const uint4* src, uint64_t nlanes, uint32_t t
 }  // namespace gmp
 
 extern "C" int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int pattern, uint64_t seed,
-                                           gmp_verify_result* out, void* stream) {
+                                           gmp_verify_result* out, void* stream) try {
     clear_error();
     if (out == nullptr) {
         set_error("out is NULL");
@@ -1090,4 +1094,6 @@ extern "C" int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int p
     GMP_CUDA(cudaStreamSynchronize(s));
     decode_acc(raw, out);
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }

@@ -11,6 +11,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <exception>
 #include <map>
 #include <new>
 #include <mutex>
@@ -20,6 +21,23 @@
 namespace gmp {
 void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
 void clear_error();
+
+// What a function-try-block of an extern "C" entry point returns: the exception in flight is named and swallowed,
+// nothing crosses the C ABI.  Lives here because this translation unit is part of every build of the host code.
+int caught_exception() noexcept {
+    try {
+        throw;
+    } catch (const std::bad_alloc&) {
+        set_error("out of memory");
+        return GMP_ERR_NOMEM;
+    } catch (const std::exception& e) {
+        set_error("unexpected exception: %s", e.what());
+        return GMP_ERR_SYS;
+    } catch (...) {
+        set_error("unexpected exception");
+        return GMP_ERR_SYS;
+    }
+}
 
 namespace {
 
@@ -148,7 +166,7 @@ using namespace gmp;
         if (r__ != NVML_SUCCESS) return (sess).fail(r__, what); \
     } while (0)
 
-extern "C" int gmp_nvml_hold(int acquire) {
+extern "C" int gmp_nvml_hold(int acquire) try {
     clear_error();
     std::lock_guard<std::mutex> lock(g_holds_mu);
     if (acquire) {
@@ -172,9 +190,11 @@ extern "C" int gmp_nvml_hold(int acquire) {
     delete holds().back();
     holds().pop_back();
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_enumerate_nvml(gmp_device* out, int cap, int* n) {
+extern "C" int gmp_enumerate_nvml(gmp_device* out, int cap, int* n) try {
     clear_error();
     if (out == nullptr || n == nullptr || cap < 0) {
         set_error("NULL argument");
@@ -211,9 +231,11 @@ extern "C" int gmp_enumerate_nvml(gmp_device* out, int cap, int* n) {
     }
     *n = (int)count;
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_nvml_versions(char* driver, size_t driver_cap, char* nvml, size_t nvml_cap) {
+extern "C" int gmp_nvml_versions(char* driver, size_t driver_cap, char* nvml, size_t nvml_cap) try {
     clear_error();
     NvmlSession nv;
     int rc = nv.open();
@@ -229,9 +251,11 @@ extern "C" int gmp_nvml_versions(char* driver, size_t driver_cap, char* nvml, si
             GMP_NVML(nv, nv.SystemGetNVMLVersion(nvml, (unsigned)nvml_cap), "nvmlSystemGetNVMLVersion");
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_gpu_running_processes(const char* uuid, gmp_process_info* out, int cap, int* n) {
+extern "C" int gmp_gpu_running_processes(const char* uuid, gmp_process_info* out, int cap, int* n) try {
     clear_error();
     if (uuid == nullptr || n == nullptr || cap < 0 || (cap > 0 && out == nullptr)) {
         set_error("NULL argument");
@@ -270,9 +294,11 @@ extern "C" int gmp_gpu_running_processes(const char* uuid, gmp_process_info* out
         return GMP_ERR_BUFFER_TOO_SMALL;
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_index, int32_t* status) {
+extern "C" int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_index, int32_t* status) try {
     clear_error();
     if (uuids == nullptr || status == nullptr || n <= 0 || n > GMP_MAX_DEVICES) {
         set_error("bad argument (n=%d)", n);
@@ -304,9 +330,11 @@ extern "C" int gmp_nvml_p2p_status(const char* const* uuids, int n, int caps_ind
         }
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_nvml_health(const char* uuid, gmp_gpu_health* out) {
+extern "C" int gmp_nvml_health(const char* uuid, gmp_gpu_health* out) try {
     clear_error();
     if (uuid == nullptr || out == nullptr) {
         set_error("NULL argument");
@@ -334,9 +362,11 @@ extern "C" int gmp_nvml_health(const char* uuid, gmp_gpu_health* out) {
             out->ecc_corrected_volatile = w;
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* max_links) {
+extern "C" int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* max_links) try {
     clear_error();
     if (uuid == nullptr || active_links == nullptr) {
         set_error("NULL argument");
@@ -355,6 +385,8 @@ extern "C" int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* 
         if (nv.DeviceGetNvLinkState(dev, l, &st) == NVML_SUCCESS && st == NVML_FEATURE_ENABLED) ++*active_links;
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
 // All four capability matrices and the active-link counts in ONE NVML session (internal; the P2P probe

@@ -368,7 +368,7 @@ int run(const char* const* uuids, const gmp_p2p_opts& o, gmp_p2p_result* out, Se
 
 }  // namespace
 
-extern "C" int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts* opts, gmp_p2p_result* out) {
+extern "C" int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts* opts, gmp_p2p_result* out) try {
     clear_error();
     if (out == nullptr) {
         set_error("out is NULL");
@@ -432,9 +432,11 @@ extern "C" int gmp_probe_p2p(const char* const* uuids, int n, const gmp_p2p_opts
         return out->status = GMP_ERR_P2P_MATRIX;
     }
     return out->status = GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_peer_access(int device, int peer, int enable) {
+extern "C" int gmp_peer_access(int device, int peer, int enable) try {
     clear_error();
     int prev = -1;
     (void)cudaGetDevice(&prev);
@@ -447,4 +449,6 @@ extern "C" int gmp_peer_access(int device, int peer, int enable) {
     if (prev >= 0) (void)cudaSetDevice(prev);
     if (e != cudaSuccess) return cuda_fail(e, enable ? "cudaDeviceEnablePeerAccess" : "cudaDeviceDisablePeerAccess");
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }

@@ -12,6 +12,7 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <exception>
 #include <memory>
 #include <new>
 #include <string>
@@ -147,7 +148,26 @@ struct Json {
 
 }  // namespace
 
+namespace {
+int probe_all_impl(const gmp_device* expected, int n_expected, const gmp_probe_opts* opts, gmp_report* out);
+}
+
 extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const gmp_probe_opts* opts, gmp_report* out) {
+    try {  // std::thread / std::string / std::vector may throw; nothing crosses the C ABI
+        return probe_all_impl(expected, n_expected, opts, out);
+    } catch (const std::bad_alloc&) {
+        set_error("out of memory");
+        if (out) out->status = GMP_ERR_NOMEM;
+        return GMP_ERR_NOMEM;
+    } catch (const std::exception& e) {
+        set_error("gmp_probe_all: %s", e.what());
+        if (out) out->status = GMP_ERR_SYS;
+        return GMP_ERR_SYS;
+    }
+}
+
+namespace {
+int probe_all_impl(const gmp_device* expected, int n_expected, const gmp_probe_opts* opts, gmp_report* out) {
     clear_error();
     if (out == nullptr || n_expected < 0 || n_expected > GMP_MAX_DEVICES || (n_expected > 0 && expected == nullptr)) {
         set_error("bad argument");
@@ -336,8 +356,9 @@ extern "C" int gmp_probe_all(const gmp_device* expected, int n_expected, const g
     out->ns_total = now_ns() - t_begin;
     return out->status;
 }
+}  // namespace
 
-extern "C" int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_dir) {
+extern "C" int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_dir) try {
     clear_error();
     if (n < 0 || (n > 0 && gone == nullptr)) {
         set_error("bad argument");
@@ -362,9 +383,11 @@ extern "C" int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_di
         }
     }
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
 
-extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
+extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
     clear_error();
     if (r == nullptr || buf == nullptr) {
         set_error("NULL argument");
@@ -508,4 +531,6 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) {
     }
     memcpy(buf, j.s.c_str(), j.s.size() + 1);
     return GMP_OK;
+} catch (...) {
+    return ::gmp::caught_exception();
 }
