@@ -410,7 +410,7 @@ int write_permissions(const gmp_mount_env* env, const std::string& cgroup_path, 
 }
 
 // ---- namespace work in a forked child ---------------------------------------------------------------
-enum class NodeOp { kCreate, kRemove };
+enum class NodeOp { kCreate, kRemove, kOpen };
 
 struct NodeJob {
     NodeOp op;
@@ -460,16 +460,42 @@ struct NsHelperArgs {
     const NodeJob* jobs;
     size_t njobs;
     int report_fd;
+    const char* join_procs_file;  // when set: the helper first moves ITSELF into this cgroup (kOpen jobs need the pod's verdict)
 };
+
+// Writes "<pid>\n" of the calling process to an open cgroup.procs; system calls only (runs in the clone helper).
+bool write_own_pid(int fd) {
+    char me[24], rev[24];
+    int len = 0, n = 0;
+    long v = (long)getpid();
+    do {
+        rev[n++] = (char)('0' + v % 10);
+        v /= 10;
+    } while (v > 0);
+    while (n > 0) me[len++] = rev[--n];
+    me[len++] = '\n';
+    return write(fd, me, (size_t)len) == len;
+}
 
 int ns_helper_main(void* p) {
     // only raw system calls on memory the parent prepared; no allocation, no locks, no stdio
     const NsHelperArgs* a = static_cast<const NsHelperArgs*>(p);
     NsReport rep = {0, 0, 0};
     const int nsfd = open(a->ns_path, O_RDONLY | O_CLOEXEC);
+    int cgfd = -1;
+    if (nsfd >= 0 && a->join_procs_file != nullptr) {
+        cgfd = open(a->join_procs_file, O_WRONLY | O_APPEND | O_CLOEXEC);
+        if (cgfd < 0 || !write_own_pid(cgfd)) {
+            rep.err = errno;
+            rep.stage = 7;
+        }
+        if (cgfd >= 0) close(cgfd);
+    }
     if (nsfd < 0) {
         rep.err = errno;
         rep.stage = 1;
+    } else if (rep.stage != 0) {
+        // could not join the pod's cgroup: reported as is
     } else if (setns(nsfd, CLONE_NEWNS) != 0) {
         rep.err = errno;
         rep.stage = 2;
@@ -489,6 +515,14 @@ int ns_helper_main(void* p) {
                     rep.stage = 4;
                     break;
                 }
+            } else if (j.op == NodeOp::kOpen) {
+                const int fd = open(path, O_RDWR | O_CLOEXEC);
+                if (fd < 0) {
+                    rep.err = errno;
+                    rep.stage = 6;
+                    break;
+                }
+                close(fd);
             } else if (unlink(path) != 0) {
                 rep.err = errno;
                 rep.stage = 5;
@@ -505,7 +539,8 @@ int ns_helper_main(void* p) {
 
 // Runs `jobs` inside the mount namespace named by ns_path.  Returns GMP_OK or GMP_ERR_SYS and, through
 // *done, how many jobs completed.  The helper reports (jobs done, errno, failing syscall) over a pipe.
-int run_in_mount_ns(const std::string& ns_path, const std::vector<NodeJob>& jobs, int* done) {
+int run_in_mount_ns(const std::string& ns_path, const std::vector<NodeJob>& jobs, int* done, const char* join_procs_file = nullptr,
+                    int* failed_errno = nullptr, int* failed_stage = nullptr) {
     using Report = NsReport;
     if (done) *done = 0;
     int pfd[2];
@@ -514,7 +549,7 @@ int run_in_mount_ns(const std::string& ns_path, const std::vector<NodeJob>& jobs
         return GMP_ERR_SYS;
     }
     HelperStack stack;
-    NsHelperArgs args = {ns_path.c_str(), jobs.data(), jobs.size(), pfd[1]};
+    NsHelperArgs args = {ns_path.c_str(), jobs.data(), jobs.size(), pfd[1], join_procs_file};
     const pid_t child = spawn_helper(ns_helper_main, &args, stack);
     if (child < 0) {
         set_error("clone: %s", strerror(errno));
@@ -537,10 +572,13 @@ int run_in_mount_ns(const std::string& ns_path, const std::vector<NodeJob>& jobs
         return GMP_ERR_SYS;
     }
     if (done) *done = rep.done;
+    if (failed_errno) *failed_errno = rep.err;
+    if (failed_stage) *failed_stage = rep.stage;
     if (rep.stage == 0) return GMP_OK;
-    static const char* const what[] = {"", "open", "setns", "mknod", "chmod", "unlink"};
+    static const char* const what[] = {"", "open", "setns", "mknod", "chmod", "unlink", "open", "join"};
     const char* target = rep.stage <= 2 ? ns_path.c_str()
-                                        : (rep.done < (int)jobs.size() ? jobs[(size_t)rep.done].path.c_str() : "?");
+                         : rep.stage == 7 ? (join_procs_file ? join_procs_file : "?")
+                                          : (rep.done < (int)jobs.size() ? jobs[(size_t)rep.done].path.c_str() : "?");
     set_error("%s %s: %s", what[rep.stage], target, strerror(rep.err));
     return GMP_ERR_SYS;
 }
@@ -1264,20 +1302,7 @@ int probe_helper_main(void* p) {
     if (ns_fd < 0) _exit(121);
     const int cg_fd = open(a->procs_file, O_WRONLY | O_APPEND | O_CLOEXEC);
     if (cg_fd < 0) _exit(122);
-    char me[24];
-    int len = 0;
-    {
-        char rev[24];
-        int n = 0;
-        long v = (long)getpid();
-        do {
-            rev[n++] = (char)('0' + v % 10);
-            v /= 10;
-        } while (v > 0);
-        while (n > 0) me[len++] = rev[--n];
-        me[len++] = '\n';
-    }
-    if (write(cg_fd, me, (size_t)len) != len) _exit(123);
+    if (!write_own_pid(cg_fd)) _exit(123);
     close(cg_fd);
     if (setns(ns_fd, CLONE_NEWNS) != 0) _exit(124);
     dup2(a->stdout_fd, 1);
@@ -1288,6 +1313,43 @@ int probe_helper_main(void* p) {
     _exit(125);
 }
 }  // namespace
+
+// ---- the pod's view of the device nodes, without executing anything in the pod ------------------------------
+// Stage 1 of the two-stage hook (gmp_probe_all(GMP_PROBE_F_NODES_ONLY) is the same check done by the probe binary): a
+// clone helper joins the pod's device cgroup, enters its mount namespace and open(2)s /dev/nvidiactl, /dev/nvidia-uvm
+// and every mounted GPU's node.  Nothing of the pod's image is run, so it also works for musl, distroless and scratch
+// images, where the probe binary cannot start.
+extern "C" int gmp_check_nodes_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int* failed_index) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && n >= 0 && (n == 0 || gpus != nullptr));
+        if (failed_index) *failed_index = -1;
+        std::string cgroup_path;
+        int rc = pod_cgroup_path(env, pod, &cgroup_path);
+        if (rc != GMP_OK) return rc;
+        std::vector<std::string> pids;
+        rc = read_cgroup_pids(env, cgroup_path, &pids);
+        if (rc != GMP_OK) return rc;
+        int target = 0;
+        rc = first_pid(pids, &target);
+        if (rc != GMP_OK) return rc;
+        const std::string ns_path = proc_root(env) + "/" + std::to_string(target) + "/ns/mnt";
+        const std::string procs_file = devices_root(env) + cgroup_path + "/cgroup.procs";
+        // with a custom prefix ("/x/dev/nvidia") the control nodes sit next to the GPU nodes, as in the harness
+        const std::string prefix = dev_prefix(env);
+        std::vector<NodeJob> jobs = {{NodeOp::kOpen, prefix + "ctl", -1}, {NodeOp::kOpen, prefix + "-uvm", -1}};
+        for (int i = 0; i < n; ++i) jobs.push_back({NodeOp::kOpen, device_node_path(env, &gpus[i]), gpus[i].minor_number});
+        int done = 0, err = 0, stage = 0;
+        rc = run_in_mount_ns(ns_path, jobs, &done, procs_file.c_str(), &err, &stage);
+        if (rc == GMP_OK) return GMP_OK;
+        if (stage != 6) return rc;  // set-up failure (namespace, cgroup): GMP_ERR_SYS with the step named
+        const std::string detail = gmp_last_error();
+        set_error("%s", detail.c_str());
+        if (done == 0) return GMP_ERR_NODE_CTL;
+        if (done == 1) return GMP_ERR_NODE_UVM;
+        if (failed_index) *failed_index = done - 2;
+        return (err == EPERM || err == EACCES) ? GMP_ERR_NODE_DENIED : GMP_ERR_NODE_GPU;
+    });
+}
 
 // ---- in-pod execution of the probe -------------------------------------------------------------------
 // A probe run from the worker's own context proves nothing: the worker is privileged and sees every GPU

@@ -74,6 +74,18 @@ class NvmlAttached:
         return False
 
 
+def CheckNodesInPod(pod: Pod, gpus: Sequence[NvidiaGPU], env: Optional[MountEnv] = None, raise_on_error: bool = True):
+    """Do /dev/nvidiactl, /dev/nvidia-uvm and the GPUs' nodes open from inside the pod (its device cgroup, its mount
+    namespace)?  Nothing of the pod's image is executed.  Returns (status, index of the failing GPU or -1).
+    No reference counterpart; see gmp_check_nodes_in_pod."""
+    failed = ctypes.c_int(-1)
+    c = pod.to_c()
+    rc = lib().gmp_check_nodes_in_pod(env_ptr(env), ctypes.byref(c), as_c_array(gpus), len(gpus), ctypes.byref(failed))
+    if raise_on_error:
+        check(rc, "CheckNodesInPod")
+    return rc, failed.value
+
+
 def ProbeInPod(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = (), env: Optional[MountEnv] = None,
                probe_exe: Optional[str] = None, raise_on_error: bool = True):
     """Run gpumounter-probe inside the pod (device cgroup + mount namespace) and return (status, report dict).

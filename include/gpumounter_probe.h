@@ -646,6 +646,17 @@ GMP_API int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const
                              const char* probe_exe, const char* const* extra_args, int n_extra,
                              char* json, size_t cap, int* exit_status);
 
+/*
+ * The pod's view of its device nodes without running anything of the pod's image: a helper process joins the pod's
+ * device cgroup and mount namespace and open(2)s /dev/nvidiactl, /dev/nvidia-uvm and the node of every GPU in `gpus`.
+ * GMP_OK, or GMP_ERR_NODE_CTL / GMP_ERR_NODE_UVM / GMP_ERR_NODE_GPU (absent, or no device behind it) /
+ * GMP_ERR_NODE_DENIED (the device cgroup refuses: EPERM) with *failed_index = the position in `gpus`, or GMP_ERR_SYS
+ * when the namespace or cgroup could not be entered.  No reference counterpart; stage 1 of the resident hook
+ *  for images in which gpumounter-probe cannot start (musl, distroless, scratch).
+ */
+GMP_API int gmp_check_nodes_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
+                                   int* failed_index);
+
 /* kubelet PodResources listing, ref: collector.go:114-122 (v1alpha1 messages). */
 typedef struct gmp_container_devices { const char* resource_name; int32_t n_ids; const char* const* device_ids; } gmp_container_devices;
 typedef struct gmp_container_entry   { const char* name; int32_t n_devices; const gmp_container_devices* devices; } gmp_container_entry;

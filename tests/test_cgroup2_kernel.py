@@ -383,3 +383,20 @@ def test_interpreters_compute_what_the_kernel_computes(tmp_path):
             assert o.interpret(prog, t, c.ACC_MKNOD, ma, mi) == kernel_allows, (prog, t, ma, mi)
         checked += 1
     assert checked == 120, (checked, skipped)
+
+
+def test_check_nodes_in_pod_on_the_unified_hierarchy(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        env, pod = env_of(t), product_pod()
+        u, m, _ = gpus_cfg[0]
+        gpu = device.New(m, u)
+        for name in ("nvidiactl", "nvidia-uvm"):
+            open(f"/proc/{t.pid}/root{t.devdir}/{name}", "w").close()
+        os.mknod(t.node_path_in_target(m), 0o666 | 0o020000, os.makedev(195, m))
+        assert util.CheckNodesInPod(pod, [gpu], env, raise_on_error=False) == (_lib.GMP_ERR_NODE_DENIED, 0)   # the v2 program says no
+        os.unlink(t.node_path_in_target(m))
+        util.MountGPU(pod, gpu, env)
+        rc, idx = util.CheckNodesInPod(pod, [gpu], env, raise_on_error=False)
+        assert rc in (0, _lib.GMP_ERR_NODE_GPU)          # past the filter (ENXIO here: no driver), never "denied"
+        util.UnmountGPU(pod, gpu, False, env)

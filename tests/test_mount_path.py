@@ -6,7 +6,7 @@ import os
 
 import pytest
 
-from gpumounter_b200 import ProbeError, _lib, cgroup, device, namespace, util
+from gpumounter_b200 import ProbeError, _lib, cgroup, device, lib, namespace, util
 from gpumounter_b200._model import MountEnv, Pod
 from oracle import gmo_ref_ctypes as ref
 from tests import harness
@@ -301,6 +301,55 @@ def test_real_v1_cgroup_gates_open_until_the_gpu_is_mounted(fake_nvml):
         os.mknod(t.node_path_in_target(3), 0o666 | 0o020000, os.makedev(195, 3))
         assert t.try_open(3) == errno.EPERM
         os.unlink(t.node_path_in_target(3))
+    finally:
+        with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+            f.write(f"{t.pid}\n")
+        t.stop()
+
+
+def test_check_nodes_in_pod_without_executing_anything(fake_nvml):
+    """Stage 1 of the resident hook for images where the probe binary cannot start: the helper itself opens the nodes
+    from inside the pod's cgroup and mount namespace."""
+    gpus_cfg = fake_nvml()
+    with harness.Target() as t:
+        env, pod = env_of(t), product_pod()
+        gpus = [device.New(m, u) for u, m, _ in gpus_cfg[:2]]
+        rc, idx = util.CheckNodesInPod(pod, gpus, env, raise_on_error=False)
+        assert rc == _lib.GMP_ERR_NODE_CTL and "nvidiactl" in lib().gmp_last_error().decode()
+        open(f"/proc/{t.pid}/root{t.devdir}/nvidiactl", "w").close()
+        assert util.CheckNodesInPod(pod, gpus, env, raise_on_error=False)[0] == _lib.GMP_ERR_NODE_UVM
+        open(f"/proc/{t.pid}/root{t.devdir}/nvidia-uvm", "w").close()
+        assert util.CheckNodesInPod(pod, gpus, env, raise_on_error=False) == (_lib.GMP_ERR_NODE_GPU, 0)     # not mounted yet
+        util.MountGPU(pod, gpus[0], env)
+        rc, idx = util.CheckNodesInPod(pod, gpus, env, raise_on_error=False)
+        # gpus[0] now has a node; with no driver on this box open() says ENXIO, which is still "GPU node unusable" for
+        # index 0 - on a GPU box it opens and the verdict moves on to the unmounted gpus[1]
+        assert rc == _lib.GMP_ERR_NODE_GPU and idx in (0, 1)
+        assert util.CheckNodesInPod(pod, [], env) == (0, -1)                                                # control nodes only
+        # every check joined the pod's cgroup first (the scratch cgroup.procs is a plain file: each join is a line)
+        assert len(t.read("cgroup.procs").split()) == 1 + 5
+    with pytest.raises(ProbeError) as e:
+        util.CheckNodesInPod(product_pod(), [], MountEnv(devices_root="/nonexistent", cgroup_driver="cgroupfs"))
+    assert e.value.code == _lib.GMP_ERR_SYS
+
+
+@pytest.mark.skipif(not (os.path.isdir(REAL) and os.access(REAL, os.W_OK)), reason="no writable cgroup-v1 devices hierarchy")
+def test_check_nodes_in_pod_sees_the_kernels_verdict(fake_nvml):
+    fake_nvml()
+    try:
+        t = harness.Target(real_cgroup=True, container_whitelist=True).start()
+    except OSError as e:
+        pytest.skip(f"cannot create a devices cgroup: {e}")
+    try:
+        env, pod, gpu = env_of(t), product_pod(), device.New(3, FAKE_UUIDS[0])
+        for name in ("nvidiactl", "nvidia-uvm"):
+            open(f"/proc/{t.pid}/root{t.devdir}/{name}", "w").close()
+        os.mknod(t.node_path_in_target(3), 0o666 | 0o020000, os.makedev(195, 3))      # a node, but no permission
+        assert util.CheckNodesInPod(pod, [gpu], env, raise_on_error=False) == (_lib.GMP_ERR_NODE_DENIED, 0)
+        os.unlink(t.node_path_in_target(3))
+        util.MountGPU(pod, gpu, env)
+        rc, idx = util.CheckNodesInPod(pod, [gpu], env, raise_on_error=False)
+        assert rc in (0, _lib.GMP_ERR_NODE_GPU) and "Operation not permitted" not in lib().gmp_last_error().decode()
     finally:
         with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
             f.write(f"{t.pid}\n")

@@ -250,8 +250,8 @@ def to_usable(iters, hbm_bytes, n_gpus, real_cgroup=False):
 
 def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts):
     """Two-stage hook with a resident worker (this process stands in for it: on the host, sees every GPU, cuInit paid once at
-    start-up): native mount -> `gpumounter-probe --nodes-only` fexecve'd in the pod (device cgroup + mount namespace: the nodes
-    open there; no CUDA) -> gmp_probe_all(HOST_VIEW) in-process on the mounted GPUs.  keep_contexts: the worker retains the
+    start-up): native mount -> gmp_check_nodes_in_pod (a helper joins the pod's device cgroup + mount namespace and opens the
+    nodes there; nothing executed, no CUDA) -> gmp_probe_all(HOST_VIEW) in-process on the mounted GPUs.  keep_contexts: the worker retains the
     primary contexts between calls (KEEP_DEVICE) or releases them (cudaDeviceReset) after each probe.
     What this does NOT time is the tenant's own CUDA start-up in the pod - that is to_usable()."""
     nv = {d.uuid: d for d in probe.enumerate_nvml()}
@@ -269,9 +269,9 @@ def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts):
             t0 = time.monotonic_ns()
             util.MountGPUs(pod, recs, env)
             t_mounted = time.monotonic_ns()
-            rc, nodes = util.ProbeInPod(pod, recs, ["--dev-dir", t.devdir, "--nodes-only"], env, raise_on_error=False)
+            rc, failed = util.CheckNodesInPod(pod, recs, env, raise_on_error=False)   # helper in the pod's cgroup + mount ns, no exec
             t_nodes = time.monotonic_ns()
-            assert rc == 0 and nodes.get("status") == 0 and nodes.get("nodes_status") == 0, nodes
+            assert rc == 0, (rc, failed, probe.lib().gmp_last_error())
             r = probe.probe_all(expected, hbm_bytes=hbm_bytes, hbm_iters=1, dma_bytes=16 << 20, p2p_bytes=256 << 20, p2p_iters=1,
                                 flags=flags, raise_on_error=False)
             t_done = time.monotonic_ns()
