@@ -410,7 +410,7 @@ int write_permissions(const gmp_mount_env* env, const std::string& cgroup_path, 
 }
 
 // ---- namespace work in a forked child ---------------------------------------------------------------
-enum class NodeOp { kCreate, kRemove, kOpen };
+enum class NodeOp { kCreate, kRemove, kOpen, kAbsent };
 
 struct NodeJob {
     NodeOp op;
@@ -523,6 +523,14 @@ int ns_helper_main(void* p) {
                     break;
                 }
                 close(fd);
+            } else if (j.op == NodeOp::kAbsent) {
+                struct stat st;
+                const int r = lstat(path, &st);
+                if (r == 0 || errno != ENOENT) {  // still there (or not even answerable): not "gone"
+                    rep.err = r == 0 ? EEXIST : errno;
+                    rep.stage = 8;
+                    break;
+                }
             } else if (unlink(path) != 0) {
                 rep.err = errno;
                 rep.stage = 5;
@@ -575,7 +583,7 @@ int run_in_mount_ns(const std::string& ns_path, const std::vector<NodeJob>& jobs
     if (failed_errno) *failed_errno = rep.err;
     if (failed_stage) *failed_stage = rep.stage;
     if (rep.stage == 0) return GMP_OK;
-    static const char* const what[] = {"", "open", "setns", "mknod", "chmod", "unlink", "open", "join"};
+    static const char* const what[] = {"", "open", "setns", "mknod", "chmod", "unlink", "open", "join", "still present:"};
     const char* target = rep.stage <= 2 ? ns_path.c_str()
                          : rep.stage == 7 ? (join_procs_file ? join_procs_file : "?")
                                           : (rep.done < (int)jobs.size() ? jobs[(size_t)rep.done].path.c_str() : "?");
@@ -1348,6 +1356,34 @@ extern "C" int gmp_check_nodes_in_pod(const gmp_mount_env* env, const gmp_pod* p
         if (done == 1) return GMP_ERR_NODE_UVM;
         if (failed_index) *failed_index = done - 2;
         return (err == EPERM || err == EACCES) ? GMP_ERR_NODE_DENIED : GMP_ERR_NODE_GPU;
+    });
+}
+
+// After an unmount: none of the GPUs' nodes may exist in the pod any more (what `gpumounter-probe --gone` checks from an
+// exec'ed binary, here from the helper: nothing of the pod's image runs).
+extern "C" int gmp_verify_gone_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n, int* failed_index) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && n >= 0 && (n == 0 || gpus != nullptr));
+        if (failed_index) *failed_index = -1;
+        std::string cgroup_path;
+        int rc = pod_cgroup_path(env, pod, &cgroup_path);
+        if (rc != GMP_OK) return rc;
+        std::vector<std::string> pids;
+        rc = read_cgroup_pids(env, cgroup_path, &pids);
+        if (rc != GMP_OK) return rc;
+        int target = 0;
+        rc = first_pid(pids, &target);
+        if (rc != GMP_OK) return rc;
+        const std::string ns_path = proc_root(env) + "/" + std::to_string(target) + "/ns/mnt";
+        std::vector<NodeJob> jobs;
+        for (int i = 0; i < n; ++i) jobs.push_back({NodeOp::kAbsent, device_node_path(env, &gpus[i]), gpus[i].minor_number});
+        int done = 0, err = 0, stage = 0;
+        rc = run_in_mount_ns(ns_path, jobs, &done, nullptr, &err, &stage);
+        if (rc == GMP_OK || stage != 8) return rc;
+        if (failed_index) *failed_index = done;
+        const std::string detail = gmp_last_error();
+        set_error("%s", detail.c_str());
+        return GMP_ERR_STILL_MOUNTED;
     });
 }
 

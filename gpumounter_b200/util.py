@@ -86,6 +86,17 @@ def CheckNodesInPod(pod: Pod, gpus: Sequence[NvidiaGPU], env: Optional[MountEnv]
     return rc, failed.value
 
 
+def VerifyGoneInPod(pod: Pod, gpus: Sequence[NvidiaGPU], env: Optional[MountEnv] = None, raise_on_error: bool = True):
+    """After UnmountGPU(s): none of the GPUs' nodes may exist in the pod any more; checked by a helper in the pod's mount
+    namespace, nothing executed there.  Returns (status, index of the first GPU still present or -1)."""
+    failed = ctypes.c_int(-1)
+    c = pod.to_c()
+    rc = lib().gmp_verify_gone_in_pod(env_ptr(env), ctypes.byref(c), as_c_array(gpus), len(gpus), ctypes.byref(failed))
+    if raise_on_error:
+        check(rc, "VerifyGoneInPod")
+    return rc, failed.value
+
+
 def ProbeInPod(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = (), env: Optional[MountEnv] = None,
                probe_exe: Optional[str] = None, raise_on_error: bool = True):
     """Run gpumounter-probe inside the pod (device cgroup + mount namespace) and return (status, report dict).

@@ -657,6 +657,12 @@ GMP_API int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const
 GMP_API int gmp_check_nodes_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
                                    int* failed_index);
 
+/* The RemoveGPU-side counterpart: GMP_OK when none of the GPUs' nodes exists in the pod's mount namespace any more,
+ * GMP_ERR_STILL_MOUNTED with *failed_index otherwise (the reference returns Success once `rm` exited 0, util.go:131-134).
+ * Same helper, nothing executed in the pod; gmp_verify_gone is the check run from inside by gpumounter-probe --gone. */
+GMP_API int gmp_verify_gone_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
+                                   int* failed_index);
+
 /* kubelet PodResources listing, ref: collector.go:114-122 (v1alpha1 messages). */
 typedef struct gmp_container_devices { const char* resource_name; int32_t n_ids; const char* const* device_ids; } gmp_container_devices;
 typedef struct gmp_container_entry   { const char* name; int32_t n_devices; const gmp_container_devices* devices; } gmp_container_entry;

@@ -354,3 +354,21 @@ def test_check_nodes_in_pod_sees_the_kernels_verdict(fake_nvml):
         with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
             f.write(f"{t.pid}\n")
         t.stop()
+
+
+def test_verify_gone_in_pod_without_executing_anything(fake_nvml):
+    gpus_cfg = fake_nvml()
+    with harness.Target() as t:
+        env, pod = env_of(t), product_pod()
+        gpus = [device.New(m, u) for u, m, _ in gpus_cfg[:3]]
+        util.MountGPUs(pod, gpus, env)
+        assert util.VerifyGoneInPod(pod, gpus, env, raise_on_error=False) == (_lib.GMP_ERR_STILL_MOUNTED, 0)
+        util.UnmountGPUs(pod, gpus[:2], False, env)
+        rc, idx = util.VerifyGoneInPod(pod, gpus, env, raise_on_error=False)
+        assert (rc, idx) == (_lib.GMP_ERR_STILL_MOUNTED, 2) and f"nvidia{gpus[2].MinorNumber}" in lib().gmp_last_error().decode()
+        assert util.VerifyGoneInPod(pod, gpus[:2], env) == (0, -1)
+        util.UnmountGPUs(pod, gpus[2:], False, env)
+        assert util.VerifyGoneInPod(pod, gpus, env) == (0, -1)
+        # the same verdict as the probe binary's --gone mode, run inside
+        rc, rep = util.VerifyUnmountedInPod(pod, gpus, env, dev_dir=t.devdir, raise_on_error=False)
+        assert rc == 0 and rep["status"] == 0
