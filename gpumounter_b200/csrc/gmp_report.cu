@@ -12,6 +12,7 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <exception>
 #include <memory>
 #include <new>
@@ -506,6 +507,39 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
         }
         j.raw("]");
         j.knum("alltoall_gbs", p.alltoall_gbs);
+        // NVSwitch gives every pair the same bandwidth: a pair well below the others is the finding an operator wants
+        // named (a degraded link, a GPU routed over PCIe).  Per kind, pairs under 80 % of that kind's median.
+        j.key("slow_pairs");
+        j.raw("[");
+        {
+            const struct {
+                const char* kind;
+                const double* m;
+            } kinds[] = {{"store", p.write_gbs}, {"load", p.read_gbs}, {"memcpy_peer", p.memcpy_gbs}};
+            for (const auto& k : kinds) {
+                std::vector<double> measured;
+                for (int a = 0; a < p.n; ++a)
+                    for (int b = 0; b < p.n; ++b)
+                        if (a != b && k.m[a * p.n + b] > 0.0) measured.push_back(k.m[a * p.n + b]);
+                if (measured.size() < 2) continue;
+                std::sort(measured.begin(), measured.end());
+                const double median = measured[measured.size() / 2];
+                for (int a = 0; a < p.n; ++a)
+                    for (int b = 0; b < p.n; ++b) {
+                        const double v = k.m[a * p.n + b];
+                        if (a == b || !(v > 0.0) || v >= 0.8 * median) continue;
+                        j.sep();
+                        j.raw("{");
+                        j.ki("src", a);
+                        j.ki("dst", b);
+                        j.kstr("kind", k.kind);
+                        j.knum("gbs", v);
+                        j.knum("median_gbs", median);
+                        j.raw("}");
+                    }
+            }
+        }
+        j.raw("]");
         j.kms("ms_setup", p.ns_setup);
         j.kms("ms_pairs", p.ns_pairs);
         j.kms("ms_bidir", p.ns_bidir);

@@ -120,3 +120,26 @@ def test_report_json_is_always_valid_json():
     assert j["detail"].startswith('quote " backslash \\ newline \n tab \t bell \x07 <script>')
     assert j["detail"].endswith("é€😀\ufffd\ufffd\ufffd")      # well-formed UTF-8 kept, stray bytes replaced
     assert j["devices"][0]["uuid"] == 'GPU-"x"\\'
+
+
+def test_slow_p2p_pairs_are_named_in_the_report():
+    """NVSwitch: every pair should measure the same.  The JSON names the pairs under 80 % of their kind's median."""
+    r = probe.gmp_report()
+    r.n, r.p2p.n = 4, 4
+    for i in range(4):
+        for k in range(4):
+            if i != k:
+                r.p2p.write_gbs[i * 4 + k] = 713.0
+                r.p2p.read_gbs[i * 4 + k] = 778.0
+                r.p2p.memcpy_gbs[i * 4 + k] = 777.0
+    r.p2p.write_gbs[2 * 4 + 1] = 52.0      # GPU 2 -> GPU 1 fell back to PCIe
+    r.p2p.read_gbs[3 * 4 + 0] = 600.0      # 77 % of the median: a degraded link
+    r.p2p.read_gbs[0 * 4 + 3] = 640.0      # 82 %: within tolerance
+    j = json.loads(probe.report_json(r))
+    assert j["p2p"]["slow_pairs"] == [
+        {"src": 2, "dst": 1, "kind": "store", "gbs": 52.0, "median_gbs": 713.0},
+        {"src": 3, "dst": 0, "kind": "load", "gbs": 600.0, "median_gbs": 778.0},
+    ]
+    r.p2p.write_gbs[2 * 4 + 1] = 713.0
+    r.p2p.read_gbs[3 * 4 + 0] = 778.0
+    assert json.loads(probe.report_json(r))["p2p"]["slow_pairs"] == []
