@@ -35,6 +35,7 @@ GMP_ERR_NODE_DENIED = -21
 GMP_ERR_DRIVER_LIB = -22
 GMP_ERR_STILL_MOUNTED = -23
 GMP_ERR_UNSUPPORTED = -24
+GMP_ERR_SLOW = -25
 
 
 class ProbeError(RuntimeError):

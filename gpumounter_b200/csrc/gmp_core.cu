@@ -151,7 +151,8 @@ extern "C" const char* gmp_strerror(int code) {
         case GMP_ERR_NODE_DENIED: return "GPU device node not openable (device cgroup)";
         case GMP_ERR_DRIVER_LIB: return "libcuda.so.1 not found";
         case GMP_ERR_STILL_MOUNTED: return "device node still present after unmount";
-        case GMP_ERR_UNSUPPORTED: return "cgroup device program is not in the canonical block form";
+        case GMP_ERR_UNSUPPORTED: return "cgroup device program can be neither decoded nor re-loaded";
+        case GMP_ERR_SLOW: return "a measured rate is under the threshold";
         default: return "unknown error";
     }
 }

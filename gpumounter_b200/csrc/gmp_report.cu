@@ -388,6 +388,40 @@ extern "C" int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_di
     return ::gmp::caught_exception();
 }
 
+extern "C" int gmp_report_apply_thresholds(gmp_report* r, double min_hbm_gbs, double min_p2p_gbs) {
+    clear_error();
+    if (r == nullptr) {
+        set_error("report is NULL");
+        return GMP_ERR_INVALID;
+    }
+    if (r->status != GMP_OK) return r->status;
+    auto fail = [r](const char* what, const char* uuid, int src, int dst, double got, double want) {
+        if (uuid) snprintf(r->detail, sizeof(r->detail), "%s: %s %.1f GB/s is under the threshold of %.1f", uuid, what, got, want);
+        else snprintf(r->detail, sizeof(r->detail), "GPU %d -> GPU %d: peer %s %.1f GB/s is under the threshold of %.1f", src, dst, what, got, want);
+        set_error("%s", r->detail);
+        return r->status = GMP_ERR_SLOW;
+    };
+    if (min_hbm_gbs > 0.0) {
+        for (int i = 0; i < r->n && i < GMP_MAX_DEVICES; ++i) {
+            const gmp_hbm_result& h = r->hbm[i];
+            if (h.write_gbs_best > 0.0 && h.write_gbs_best < min_hbm_gbs) return fail("write", h.uuid, 0, 0, h.write_gbs_best, min_hbm_gbs);
+            if (h.read_gbs_best > 0.0 && h.read_gbs_best < min_hbm_gbs) return fail("read-verify", h.uuid, 0, 0, h.read_gbs_best, min_hbm_gbs);
+            if (h.copy_gbs_best > 0.0 && h.copy_gbs_best < min_hbm_gbs) return fail("copy", h.uuid, 0, 0, h.copy_gbs_best, min_hbm_gbs);
+        }
+    }
+    if (min_p2p_gbs > 0.0 && r->p2p.n >= 2 && r->p2p.n <= GMP_MAX_DEVICES) {
+        const int n = r->p2p.n;
+        for (int a = 0; a < n; ++a)
+            for (int b = 0; b < n; ++b) {
+                if (a == b) continue;
+                const double w = r->p2p.write_gbs[a * n + b], l = r->p2p.read_gbs[a * n + b];
+                if (w > 0.0 && w < min_p2p_gbs) return fail("store", nullptr, a, b, w, min_p2p_gbs);
+                if (l > 0.0 && l < min_p2p_gbs) return fail("load", nullptr, a, b, l, min_p2p_gbs);
+            }
+    }
+    return r->status;
+}
+
 extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
     clear_error();
     if (r == nullptr || buf == nullptr) {

@@ -74,7 +74,8 @@ enum {
     GMP_ERR_NODE_DENIED      = -21, /* /dev/nvidiaN exists but open() is refused (device cgroup) */
     GMP_ERR_DRIVER_LIB       = -22, /* libcuda.so.1 not resolvable from the probing context */
     GMP_ERR_STILL_MOUNTED    = -23, /* after an unmount: the device node is still there (or still opens) in the pod */
-    GMP_ERR_UNSUPPORTED      = -24  /* section 7: a cgroup-v2 device program that can be neither decoded nor re-loaded */
+    GMP_ERR_UNSUPPORTED      = -24, /* section 7: a cgroup-v2 device program that can be neither decoded nor re-loaded */
+    GMP_ERR_SLOW             = -25  /* everything verified, but a measured rate is under the caller's threshold */
 };
 
 GMP_API int         gmp_abi_version(void);
@@ -483,6 +484,15 @@ GMP_API int gmp_probe_all(const gmp_device* expected, int n_expected, const gmp_
  * open (the detail string says which).  dev_dir NULL = "/dev".
  */
 GMP_API int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_dir);
+/*
+ * Acceptance thresholds on a finished report (the operator's policy, e.g. "85 % of this node's usual HBM rate"): when the
+ * report is otherwise GMP_OK and any GPU's best write, read-verify or copy rate is under min_hbm_gbs, or any measured
+ * peer store / load rate is under min_p2p_gbs, status becomes GMP_ERR_SLOW and detail names the first offender.  A
+ * threshold of 0 is not applied; rates that were not measured (0) are not judged.  Returns the report's status.
+ * gpumounter-probe: --min-hbm-gbs N, --min-p2p-gbs N.  No reference counterpart.
+ */
+GMP_API int gmp_report_apply_thresholds(gmp_report* report, double min_hbm_gbs, double min_p2p_gbs);
+
 /* One JSON object (single line, no trailing newline) describing the report.  GMP_ERR_BUFFER_TOO_SMALL
  * when cap is not enough (32 KiB always is). */
 GMP_API int gmp_report_json(const gmp_report* report, char* buf, size_t cap);

@@ -108,7 +108,7 @@ def test_report_json_is_always_valid_json():
         r.devices[i].uuid = b'GPU-"x"\\'
         r.devices[i].pci_bus_id = b"0000:1B:00.0"
         r.hbm[i].uuid = b"GPU-y"
-        r.hbm[i].write_gbs, r.hbm[i].read_gbs, r.hbm[i].copy_gbs = math.inf, -math.inf, math.nan
+        r.hbm[i].write_gbs_best, r.hbm[i].read_gbs_best, r.hbm[i].copy_gbs_best = math.inf, -math.inf, math.nan
         r.hbm[i].h2d_gbs = 1e308
     r.p2p.n = 2
     for k in range(4):
@@ -143,3 +143,29 @@ def test_slow_p2p_pairs_are_named_in_the_report():
     r.p2p.write_gbs[2 * 4 + 1] = 713.0
     r.p2p.read_gbs[3 * 4 + 0] = 778.0
     assert json.loads(probe.report_json(r))["p2p"]["slow_pairs"] == []
+
+
+def test_thresholds_turn_a_clean_report_into_slow():
+    """The operator's acceptance policy, applied to a finished report: rates under the threshold are GMP_ERR_SLOW with the
+    offender named; unmeasured rates (0) and an already failed report are left alone."""
+    import ctypes
+
+    f = _lib.lib().gmp_report_apply_thresholds
+    f.argtypes = [ctypes.POINTER(probe.gmp_report), ctypes.c_double, ctypes.c_double]
+    r = probe.gmp_report()
+    r.n, r.p2p.n = 2, 2
+    for i, (w, rd, c) in enumerate([(7100.0, 6840.0, 6930.0), (7090.0, 5100.0, 0.0)]):   # GPU 1 reads slowly, copy not run
+        r.hbm[i].uuid = f"GPU-{i}".encode()
+        r.hbm[i].write_gbs_best, r.hbm[i].read_gbs_best, r.hbm[i].copy_gbs_best = w, rd, c
+    r.p2p.write_gbs[1], r.p2p.write_gbs[2], r.p2p.read_gbs[1], r.p2p.read_gbs[2] = 713.0, 712.0, 778.0, 300.0
+    assert f(ctypes.byref(r), 0.0, 0.0) == 0 and f(ctypes.byref(r), 5000.0, 250.0) == 0
+    assert f(ctypes.byref(r), 5500.0, 0.0) == _lib.GMP_ERR_SLOW
+    assert r.status == _lib.GMP_ERR_SLOW and r.detail == b"GPU-1: read-verify 5100.0 GB/s is under the threshold of 5500.0"
+    j = json.loads(probe.report_json(r))
+    assert j["status"] == _lib.GMP_ERR_SLOW and j["verdict"] == "a measured rate is under the threshold"
+    assert f(ctypes.byref(r), 1.0, 1.0) == _lib.GMP_ERR_SLOW           # a failed report stays failed
+    r.status = 0
+    assert f(ctypes.byref(r), 0.0, 700.0) == _lib.GMP_ERR_SLOW
+    assert r.detail == b"GPU 1 -> GPU 0: peer load 300.0 GB/s is under the threshold of 700.0"
+    p = subprocess.run([EXE, "--min-hbm-gbs"], capture_output=True, text=True)
+    assert p.returncode == 64 and "needs a value" in p.stderr
