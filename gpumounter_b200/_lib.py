@@ -36,6 +36,7 @@ GMP_ERR_DRIVER_LIB = -22
 GMP_ERR_STILL_MOUNTED = -23
 GMP_ERR_UNSUPPORTED = -24
 GMP_ERR_SLOW = -25
+GMP_ERR_UNHEALTHY = -26
 
 
 class ProbeError(RuntimeError):

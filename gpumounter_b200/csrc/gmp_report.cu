@@ -422,6 +422,36 @@ extern "C" int gmp_report_apply_thresholds(gmp_report* r, double min_hbm_gbs, do
     return r->status;
 }
 
+extern "C" int gmp_report_check_health(gmp_report* r) {
+    clear_error();
+    if (r == nullptr) {
+        set_error("report is NULL");
+        return GMP_ERR_INVALID;
+    }
+    if (r->status != GMP_OK) return r->status;
+    for (int i = 0; i < r->n && i < GMP_MAX_DEVICES; ++i) {
+        const gmp_gpu_health& h = r->health[i];
+        const char* why = nullptr;
+        char buf[96];
+        if (h.ecc_uncorrected_volatile != UINT64_MAX && h.ecc_uncorrected_volatile > 0) {
+            snprintf(buf, sizeof(buf), "%llu uncorrected ECC errors since the last driver load", (unsigned long long)h.ecc_uncorrected_volatile);
+            why = buf;
+        } else if (h.throttle_reasons != UINT64_MAX && (h.throttle_reasons & 0x8ull)) {
+            why = "hardware slowdown is active";
+        } else if (h.throttle_reasons != UINT64_MAX && (h.throttle_reasons & 0x40ull)) {
+            why = "hardware thermal slowdown is active";
+        } else if (h.throttle_reasons != UINT64_MAX && (h.throttle_reasons & 0x80ull)) {
+            why = "hardware power brake is active";
+        }
+        if (why != nullptr) {
+            snprintf(r->detail, sizeof(r->detail), "%s: %s", r->devices[i].uuid, why);
+            set_error("%s", r->detail);
+            return r->status = GMP_ERR_UNHEALTHY;
+        }
+    }
+    return r->status;
+}
+
 extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
     clear_error();
     if (r == nullptr || buf == nullptr) {

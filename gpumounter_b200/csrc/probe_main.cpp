@@ -139,6 +139,7 @@ void usage() {
             "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
             "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only] [--lib-baselines]\n"
             "         [--min-hbm-gbs N] [--min-p2p-gbs N]  (fail with -25 when a measured rate is lower)\n"
+            "         [--strict-health]  (fail with -26 on uncorrected ECC errors or a hardware slowdown)\n"
             "         [--nodes-only]  (device nodes + driver library only: no CUDA, a few ms)\n"
             "         [--host-view]   (run from the host: CUDA may see more GPUs than the listed ones)\n"
             "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n"
@@ -160,6 +161,8 @@ int main(int argc, char** argv) {
     o.hbm.dma_bytes = UINT64_MAX;  // library default
     o.flags |= GMP_PROBE_F_KEEP_DEVICE;  // a process of its own: exit releases everything, no explicit reset needed
     double min_hbm_gbs = 0.0, min_p2p_gbs = 0.0;  // acceptance thresholds; 0 = report only
+    bool strict_health = false;
+    if (const char* v = getenv("GPUMOUNTER_PROBE_STRICT_HEALTH")) strict_health = parse_u32(v) != 0;
     if (const char* v = getenv("GPUMOUNTER_PROBE_MIN_HBM_GBS")) min_hbm_gbs = (double)parse_u32(v);
     if (const char* v = getenv("GPUMOUNTER_PROBE_MIN_P2P_GBS")) min_p2p_gbs = (double)parse_u32(v);
     std::vector<gmp_device> expected, gone;
@@ -212,6 +215,7 @@ int main(int argc, char** argv) {
         else if (a == "--skip-nvml") o.flags |= GMP_PROBE_F_SKIP_NVML;
         else if (a == "--min-hbm-gbs") min_hbm_gbs = (double)parse_u32(need("--min-hbm-gbs"));
         else if (a == "--min-p2p-gbs") min_p2p_gbs = (double)parse_u32(need("--min-p2p-gbs"));
+        else if (a == "--strict-health") strict_health = true;
         else if (a == "--nodes-only") o.flags |= GMP_PROBE_F_NODES_ONLY;
         else if (a == "--host-view") o.flags |= GMP_PROBE_F_HOST_VIEW;
         else if (a == "--skip-copy") o.hbm.flags |= GMP_HBM_F_SKIP_COPY;
@@ -245,6 +249,7 @@ int main(int argc, char** argv) {
     static gmp_report report;  // ~100 KB: keep it off the stack
     int rc = gmp_probe_all(expected.empty() ? nullptr : expected.data(), (int)expected.size(), &o, &report);
     if (rc == GMP_OK) rc = gmp_report_apply_thresholds(&report, min_hbm_gbs, min_p2p_gbs);
+    if (rc == GMP_OK && strict_health) rc = gmp_report_check_health(&report);
     static char json[1 << 16];
     if (gmp_report_json(&report, json, sizeof(json)) == GMP_OK) puts(json);
     else printf("{\"status\":%d,\"detail\":\"report too large\"}\n", rc);

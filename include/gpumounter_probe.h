@@ -75,7 +75,8 @@ enum {
     GMP_ERR_DRIVER_LIB       = -22, /* libcuda.so.1 not resolvable from the probing context */
     GMP_ERR_STILL_MOUNTED    = -23, /* after an unmount: the device node is still there (or still opens) in the pod */
     GMP_ERR_UNSUPPORTED      = -24, /* section 7: a cgroup-v2 device program that can be neither decoded nor re-loaded */
-    GMP_ERR_SLOW             = -25  /* everything verified, but a measured rate is under the caller's threshold */
+    GMP_ERR_SLOW             = -25, /* everything verified, but a measured rate is under the caller's threshold */
+    GMP_ERR_UNHEALTHY        = -26  /* everything verified, but NVML reports uncorrected ECC errors or a hardware slowdown */
 };
 
 GMP_API int         gmp_abi_version(void);
@@ -492,6 +493,15 @@ GMP_API int gmp_verify_gone(const gmp_device* gone, int n, const char* dev_dir);
  * gpumounter-probe: --min-hbm-gbs N, --min-p2p-gbs N.  No reference counterpart.
  */
 GMP_API int gmp_report_apply_thresholds(gmp_report* report, double min_hbm_gbs, double min_p2p_gbs);
+
+/*
+ * Health policy on a finished report: when the report is otherwise GMP_OK and a GPU's NVML sample (health[], taken
+ * right after the passes) shows volatile UNCORRECTED ECC errors, or a throttle reason that means the hardware is
+ * protecting itself - HW slowdown (0x8), HW thermal slowdown (0x40), HW power brake (0x80) - status becomes
+ * GMP_ERR_UNHEALTHY and detail names the GPU and the reason.  Values NVML could not supply (all ones) are not judged.
+ * gpumounter-probe: --strict-health.  No reference counterpart.
+ */
+GMP_API int gmp_report_check_health(gmp_report* report);
 
 /* One JSON object (single line, no trailing newline) describing the report.  GMP_ERR_BUFFER_TOO_SMALL
  * when cap is not enough (32 KiB always is). */

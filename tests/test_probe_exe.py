@@ -169,3 +169,26 @@ def test_thresholds_turn_a_clean_report_into_slow():
     assert r.detail == b"GPU 1 -> GPU 0: peer load 300.0 GB/s is under the threshold of 700.0"
     p = subprocess.run([EXE, "--min-hbm-gbs"], capture_output=True, text=True)
     assert p.returncode == 64 and "needs a value" in p.stderr
+
+
+def test_health_policy_on_a_finished_report():
+    import ctypes
+
+    f = _lib.lib().gmp_report_check_health
+    f.argtypes = [ctypes.POINTER(probe.gmp_report)]
+    r = probe.gmp_report()
+    r.n = 3
+    for i in range(3):
+        r.devices[i].uuid = f"GPU-{i}".encode()
+        ctypes.memset(ctypes.byref(r.health[i]), 0xFF, ctypes.sizeof(r.health[i]))      # NVML could not say: not judged
+    assert f(ctypes.byref(r)) == 0
+    r.health[0].throttle_reasons, r.health[0].ecc_uncorrected_volatile = 0x4 | 0x1, 0    # SW power cap + idle: fine
+    r.health[1].throttle_reasons, r.health[1].ecc_uncorrected_volatile = 0, 0
+    assert f(ctypes.byref(r)) == 0
+    r.health[2].throttle_reasons, r.health[2].ecc_uncorrected_volatile = 0x40, 0
+    assert f(ctypes.byref(r)) == _lib.GMP_ERR_UNHEALTHY and r.detail == b"GPU-2: hardware thermal slowdown is active"
+    r.status = 0
+    r.health[1].ecc_uncorrected_volatile = 3
+    assert f(ctypes.byref(r)) == _lib.GMP_ERR_UNHEALTHY
+    assert r.detail == b"GPU-1: 3 uncorrected ECC errors since the last driver load"
+    assert json.loads(probe.report_json(r))["verdict"] == "NVML reports uncorrected ECC errors or a hardware slowdown"
