@@ -100,6 +100,7 @@ int NvmlSession::open() {
         {(void**)&DeviceGetPowerUsage, "nvmlDeviceGetPowerUsage", false},
         {(void**)&DeviceGetClocksReasons, "nvmlDeviceGetCurrentClocksThrottleReasons", false},
         {(void**)&DeviceGetTotalEccErrors, "nvmlDeviceGetTotalEccErrors", false},
+        {(void**)&DeviceGetRemappedRows, "nvmlDeviceGetRemappedRows", false},
     };
     for (const Sym& s : syms) {
         *s.slot = dlsym(h, s.name);
@@ -360,6 +361,13 @@ extern "C" int gmp_nvml_health(const char* uuid, gmp_gpu_health* out) try {
             out->ecc_uncorrected_volatile = w;
         if (nv.DeviceGetTotalEccErrors(dev, NVML_MEMORY_ERROR_TYPE_CORRECTED, NVML_VOLATILE_ECC, &w) == NVML_SUCCESS)
             out->ecc_corrected_volatile = w;
+    }
+    unsigned int corr = 0, unc = 0, pending = 0, failure = 0;
+    if (nv.DeviceGetRemappedRows && nv.DeviceGetRemappedRows(dev, &corr, &unc, &pending, &failure) == NVML_SUCCESS) {
+        out->remapped_rows_correctable = corr;
+        out->remapped_rows_uncorrectable = unc;
+        out->remap_pending = pending;
+        out->remap_failure = failure;
     }
     return GMP_OK;
 } catch (...) {

@@ -49,6 +49,7 @@ class NvmlSession {
     nvmlReturn_t (*DeviceGetPowerUsage)(nvmlDevice_t, unsigned int*) = nullptr;
     nvmlReturn_t (*DeviceGetClocksReasons)(nvmlDevice_t, unsigned long long*) = nullptr;
     nvmlReturn_t (*DeviceGetTotalEccErrors)(nvmlDevice_t, nvmlMemoryErrorType_t, nvmlEccCounterType_t, unsigned long long*) = nullptr;
+    nvmlReturn_t (*DeviceGetRemappedRows)(nvmlDevice_t, unsigned int*, unsigned int*, unsigned int*, unsigned int*) = nullptr;
 
   private:
     void* handle_ = nullptr;

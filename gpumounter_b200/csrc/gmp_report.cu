@@ -436,6 +436,10 @@ extern "C" int gmp_report_check_health(gmp_report* r) {
         if (h.ecc_uncorrected_volatile != UINT64_MAX && h.ecc_uncorrected_volatile > 0) {
             snprintf(buf, sizeof(buf), "%llu uncorrected ECC errors since the last driver load", (unsigned long long)h.ecc_uncorrected_volatile);
             why = buf;
+        } else if (h.remap_failure != UINT32_MAX && h.remap_failure != 0) {
+            why = "HBM row remapping has failed (no spare rows left)";
+        } else if (h.remap_pending != UINT32_MAX && h.remap_pending != 0) {
+            why = "an HBM row remap is pending: the GPU needs a reset";
         } else if (h.throttle_reasons != UINT64_MAX && (h.throttle_reasons & 0x8ull)) {
             why = "hardware slowdown is active";
         } else if (h.throttle_reasons != UINT64_MAX && (h.throttle_reasons & 0x40ull)) {
@@ -535,6 +539,10 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
         j.ki("throttle_reasons", opt64(h.throttle_reasons));
         j.ki("ecc_uncorrected_volatile", opt64(h.ecc_uncorrected_volatile));
         j.ki("ecc_corrected_volatile", opt64(h.ecc_corrected_volatile));
+        j.ki("remapped_rows_correctable", opt32(h.remapped_rows_correctable));
+        j.ki("remapped_rows_uncorrectable", opt32(h.remapped_rows_uncorrectable));
+        j.ki("remap_pending", opt32(h.remap_pending));
+        j.ki("remap_failure", opt32(h.remap_failure));
         j.raw("}");
     }
     j.raw("]");

@@ -304,7 +304,9 @@ class gmp_gpu_health(ctypes.Structure):
     _fields_ = [("sm_mhz", ctypes.c_uint32), ("mem_mhz", ctypes.c_uint32), ("sm_max_mhz", ctypes.c_uint32),
                 ("mem_max_mhz", ctypes.c_uint32), ("temperature_c", ctypes.c_uint32), ("power_mw", ctypes.c_uint32),
                 ("throttle_reasons", ctypes.c_uint64), ("ecc_uncorrected_volatile", ctypes.c_uint64),
-                ("ecc_corrected_volatile", ctypes.c_uint64)]
+                ("ecc_corrected_volatile", ctypes.c_uint64), ("remapped_rows_correctable", ctypes.c_uint32),
+                ("remapped_rows_uncorrectable", ctypes.c_uint32), ("remap_pending", ctypes.c_uint32),
+                ("remap_failure", ctypes.c_uint32)]
 
 
 def nvml_health(uuid: str) -> gmp_gpu_health:

@@ -171,6 +171,10 @@ typedef struct gmp_gpu_health {
     uint64_t throttle_reasons;
     uint64_t ecc_uncorrected_volatile;
     uint64_t ecc_corrected_volatile;
+    /* HBM row remapping (nvmlDeviceGetRemappedRows): rows replaced after correctable / uncorrectable errors, whether a
+     * remap is still waiting for the next GPU reset, and whether remapping has FAILED (no spare rows left in a bank) */
+    uint32_t remapped_rows_correctable, remapped_rows_uncorrectable;
+    uint32_t remap_pending, remap_failure;
 } gmp_gpu_health;
 
 GMP_API int gmp_nvml_health(const char* uuid, gmp_gpu_health* out);
@@ -497,7 +501,8 @@ GMP_API int gmp_report_apply_thresholds(gmp_report* report, double min_hbm_gbs, 
 /*
  * Health policy on a finished report: when the report is otherwise GMP_OK and a GPU's NVML sample (health[], taken
  * right after the passes) shows volatile UNCORRECTED ECC errors, or a throttle reason that means the hardware is
- * protecting itself - HW slowdown (0x8), HW thermal slowdown (0x40), HW power brake (0x80) - status becomes
+ * protecting itself - HW slowdown (0x8), HW thermal slowdown (0x40), HW power brake (0x80) - or an HBM row remap that
+ * failed or is still pending (the GPU needs a reset before it is handed to a tenant), status becomes
  * GMP_ERR_UNHEALTHY and detail names the GPU and the reason.  Values NVML could not supply (all ones) are not judged.
  * gpumounter-probe: --strict-health.  No reference counterpart.
  */

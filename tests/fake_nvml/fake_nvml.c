@@ -271,6 +271,30 @@ static const struct fake_health* health_of(int i) {
     return &dflt;
 }
 
+/* "remap <uuid> <correctable rows> <uncorrectable rows> <pending 0|1> <failure 0|1>"; default: nothing remapped */
+nvmlReturn_t nvmlDeviceGetRemappedRows(nvmlDevice_t d, unsigned int* corr, unsigned int* unc, unsigned int* pending,
+                                       unsigned int* failure) {
+    MAYBE_FAIL("nvmlDeviceGetRemappedRows");
+    int i = index_of(d);
+    if (i < 0) return NVML_ERROR_INVALID_ARGUMENT;
+    *corr = *unc = *pending = *failure = 0;
+    const char* path = getenv("GMP_FAKE_NVML_CONFIG");
+    FILE* f = path ? fopen(path, "r") : NULL;
+    char line[512];
+    while (f && fgets(line, sizeof(line), f)) {
+        char uuid[96];
+        unsigned a, b, c, e;
+        if (strncmp(line, "remap ", 6) == 0 && sscanf(line, "%*s %95s %u %u %u %u", uuid, &a, &b, &c, &e) == 5 && gpu_index(uuid) == i) {
+            *corr = a;
+            *unc = b;
+            *pending = c;
+            *failure = e;
+        }
+    }
+    if (f) fclose(f);
+    return NVML_SUCCESS;
+}
+
 nvmlReturn_t nvmlDeviceGetClockInfo(nvmlDevice_t d, nvmlClockType_t t, unsigned int* c) {
     MAYBE_FAIL("nvmlDeviceGetClockInfo");
     int i = index_of(d);

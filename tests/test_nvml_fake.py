@@ -179,3 +179,33 @@ def test_hold_without_nvml_is_an_error_and_changes_nothing(monkeypatch):
     from gpumounter_b200 import util
     with util.NvmlAttached() as h:
         assert h.held is False
+
+
+def test_health_reports_hbm_row_remapping(fake_nvml):
+    """nvmlDeviceGetRemappedRows: what the HBM has already repaired, and whether a repair is pending or has failed."""
+    fake_nvml(extra=[f"remap {FAKE_UUIDS[2]} 3 1 1 0", f"remap {FAKE_UUIDS[3]} 0 8 0 1"])
+    h = probe.nvml_health(FAKE_UUIDS[0])
+    assert (h.remapped_rows_correctable, h.remapped_rows_uncorrectable, h.remap_pending, h.remap_failure) == (0, 0, 0, 0)
+    h = probe.nvml_health(FAKE_UUIDS[2])
+    assert (h.remapped_rows_correctable, h.remapped_rows_uncorrectable, h.remap_pending, h.remap_failure) == (3, 1, 1, 0)
+    # the health policy on a report carrying these samples
+    check = lib().gmp_report_check_health
+    check.argtypes = [ctypes.POINTER(probe.gmp_report)]
+    r = probe.gmp_report()
+    r.n = 2
+    for i, u in enumerate((FAKE_UUIDS[0], FAKE_UUIDS[2])):
+        r.devices[i].uuid = u.encode()
+        r.health[i] = probe.nvml_health(u)
+    assert check(ctypes.byref(r)) == _lib.GMP_ERR_UNHEALTHY
+    assert r.detail.decode() == f"{FAKE_UUIDS[2]}: an HBM row remap is pending: the GPU needs a reset"
+    r.status = 0
+    r.health[1] = probe.nvml_health(FAKE_UUIDS[3])
+    r.devices[1].uuid = FAKE_UUIDS[3].encode()
+    assert check(ctypes.byref(r)) == _lib.GMP_ERR_UNHEALTHY and b"row remapping has failed" in r.detail
+    # an older driver without the entry point (or a refusal): unknown, and not judged
+    fake_nvml(fail=[("nvmlDeviceGetRemappedRows", 3)])
+    h = probe.nvml_health(FAKE_UUIDS[0])
+    assert h.remap_pending == 0xFFFFFFFF and h.remap_failure == 0xFFFFFFFF
+    r.status, r.n = 0, 1
+    r.health[0] = h
+    assert check(ctypes.byref(r)) == 0
