@@ -101,6 +101,7 @@ int NvmlSession::open() {
         {(void**)&DeviceGetClocksReasons, "nvmlDeviceGetCurrentClocksThrottleReasons", false},
         {(void**)&DeviceGetTotalEccErrors, "nvmlDeviceGetTotalEccErrors", false},
         {(void**)&DeviceGetRemappedRows, "nvmlDeviceGetRemappedRows", false},
+        {(void**)&DeviceGetFieldValues, "nvmlDeviceGetFieldValues", false},
     };
     for (const Sym& s : syms) {
         *s.slot = dlsym(h, s.name);
@@ -368,6 +369,27 @@ extern "C" int gmp_nvml_health(const char* uuid, gmp_gpu_health* out) try {
         out->remapped_rows_uncorrectable = unc;
         out->remap_pending = pending;
         out->remap_failure = failure;
+    }
+    if (nv.DeviceGetFieldValues) {
+        nvmlFieldValue_t fv[4];
+        memset(fv, 0, sizeof(fv));
+        fv[0].fieldId = NVML_FI_DEV_NVLINK_CRC_FLIT_ERROR_COUNT_TOTAL;
+        fv[1].fieldId = NVML_FI_DEV_NVLINK_CRC_DATA_ERROR_COUNT_TOTAL;
+        fv[2].fieldId = NVML_FI_DEV_NVLINK_REPLAY_ERROR_COUNT_TOTAL;
+        fv[3].fieldId = NVML_FI_DEV_NVLINK_RECOVERY_ERROR_COUNT_TOTAL;
+        if (nv.DeviceGetFieldValues(dev, 4, fv) == NVML_SUCCESS) {
+            uint64_t* slots[4] = {&out->nvlink_crc_flit_errors, &out->nvlink_crc_data_errors, &out->nvlink_replay_errors,
+                                  &out->nvlink_recovery_errors};
+            for (int k = 0; k < 4; ++k) {
+                if (fv[k].nvmlReturn != NVML_SUCCESS) continue;
+                switch (fv[k].valueType) {
+                    case NVML_VALUE_TYPE_UNSIGNED_INT: *slots[k] = fv[k].value.uiVal; break;
+                    case NVML_VALUE_TYPE_UNSIGNED_LONG: *slots[k] = fv[k].value.ulVal; break;
+                    case NVML_VALUE_TYPE_UNSIGNED_LONG_LONG: *slots[k] = fv[k].value.ullVal; break;
+                    default: break;  // a type these counters are not documented to have: left unknown
+                }
+            }
+        }
     }
     return GMP_OK;
 } catch (...) {

@@ -50,6 +50,7 @@ class NvmlSession {
     nvmlReturn_t (*DeviceGetClocksReasons)(nvmlDevice_t, unsigned long long*) = nullptr;
     nvmlReturn_t (*DeviceGetTotalEccErrors)(nvmlDevice_t, nvmlMemoryErrorType_t, nvmlEccCounterType_t, unsigned long long*) = nullptr;
     nvmlReturn_t (*DeviceGetRemappedRows)(nvmlDevice_t, unsigned int*, unsigned int*, unsigned int*, unsigned int*) = nullptr;
+    nvmlReturn_t (*DeviceGetFieldValues)(nvmlDevice_t, int, nvmlFieldValue_t*) = nullptr;
 
   private:
     void* handle_ = nullptr;

@@ -543,6 +543,10 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
         j.ki("remapped_rows_uncorrectable", opt32(h.remapped_rows_uncorrectable));
         j.ki("remap_pending", opt32(h.remap_pending));
         j.ki("remap_failure", opt32(h.remap_failure));
+        j.ki("nvlink_crc_flit_errors", opt64(h.nvlink_crc_flit_errors));
+        j.ki("nvlink_crc_data_errors", opt64(h.nvlink_crc_data_errors));
+        j.ki("nvlink_replay_errors", opt64(h.nvlink_replay_errors));
+        j.ki("nvlink_recovery_errors", opt64(h.nvlink_recovery_errors));
         j.raw("}");
     }
     j.raw("]");

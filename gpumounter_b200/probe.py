@@ -306,7 +306,9 @@ class gmp_gpu_health(ctypes.Structure):
                 ("throttle_reasons", ctypes.c_uint64), ("ecc_uncorrected_volatile", ctypes.c_uint64),
                 ("ecc_corrected_volatile", ctypes.c_uint64), ("remapped_rows_correctable", ctypes.c_uint32),
                 ("remapped_rows_uncorrectable", ctypes.c_uint32), ("remap_pending", ctypes.c_uint32),
-                ("remap_failure", ctypes.c_uint32)]
+                ("remap_failure", ctypes.c_uint32), ("nvlink_crc_flit_errors", ctypes.c_uint64),
+                ("nvlink_crc_data_errors", ctypes.c_uint64), ("nvlink_replay_errors", ctypes.c_uint64),
+                ("nvlink_recovery_errors", ctypes.c_uint64)]
 
 
 def nvml_health(uuid: str) -> gmp_gpu_health:

@@ -175,6 +175,10 @@ typedef struct gmp_gpu_health {
      * remap is still waiting for the next GPU reset, and whether remapping has FAILED (no spare rows left in a bank) */
     uint32_t remapped_rows_correctable, remapped_rows_uncorrectable;
     uint32_t remap_pending, remap_failure;
+    /* NVLink error counters, totals over all links since the driver was loaded (nvmlDeviceGetFieldValues,
+     * NVML_FI_DEV_NVLINK_*_ERROR_COUNT_TOTAL): flow-control CRC, data CRC, replays, recoveries.  Reported, not judged:
+     * what matters is whether they MOVE while the P2P probe runs, which two consecutive reports show. */
+    uint64_t nvlink_crc_flit_errors, nvlink_crc_data_errors, nvlink_replay_errors, nvlink_recovery_errors;
 } gmp_gpu_health;
 
 GMP_API int gmp_nvml_health(const char* uuid, gmp_gpu_health* out);

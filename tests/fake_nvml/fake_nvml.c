@@ -295,6 +295,41 @@ nvmlReturn_t nvmlDeviceGetRemappedRows(nvmlDevice_t d, unsigned int* corr, unsig
     return NVML_SUCCESS;
 }
 
+/* "nvlinkerr <uuid> <crc flit> <crc data> <replay> <recovery>": totals, answered as unsigned long long; any other
+ * field id is NOT_SUPPORTED in its own nvmlReturn, as the real call does per field */
+nvmlReturn_t nvmlDeviceGetFieldValues(nvmlDevice_t d, int count, nvmlFieldValue_t* values) {
+    MAYBE_FAIL("nvmlDeviceGetFieldValues");
+    int i = index_of(d);
+    if (i < 0 || count < 0 || values == NULL) return NVML_ERROR_INVALID_ARGUMENT;
+    unsigned long long v[4] = {0, 0, 0, 0};
+    const char* path = getenv("GMP_FAKE_NVML_CONFIG");
+    FILE* f = path ? fopen(path, "r") : NULL;
+    char line[512];
+    while (f && fgets(line, sizeof(line), f)) {
+        char uuid[96];
+        unsigned long long a, b, c, e;
+        if (strncmp(line, "nvlinkerr ", 10) == 0 && sscanf(line, "%*s %95s %llu %llu %llu %llu", uuid, &a, &b, &c, &e) == 5 &&
+            gpu_index(uuid) == i) {
+            v[0] = a; v[1] = b; v[2] = c; v[3] = e;
+        }
+    }
+    if (f) fclose(f);
+    for (int k = 0; k < count; ++k) {
+        int slot = values[k].fieldId == NVML_FI_DEV_NVLINK_CRC_FLIT_ERROR_COUNT_TOTAL ? 0
+                 : values[k].fieldId == NVML_FI_DEV_NVLINK_CRC_DATA_ERROR_COUNT_TOTAL ? 1
+                 : values[k].fieldId == NVML_FI_DEV_NVLINK_REPLAY_ERROR_COUNT_TOTAL ? 2
+                 : values[k].fieldId == NVML_FI_DEV_NVLINK_RECOVERY_ERROR_COUNT_TOTAL ? 3 : -1;
+        if (slot < 0) {
+            values[k].nvmlReturn = NVML_ERROR_NOT_SUPPORTED;
+            continue;
+        }
+        values[k].nvmlReturn = NVML_SUCCESS;
+        values[k].valueType = NVML_VALUE_TYPE_UNSIGNED_LONG_LONG;
+        values[k].value.ullVal = v[slot];
+    }
+    return NVML_SUCCESS;
+}
+
 nvmlReturn_t nvmlDeviceGetClockInfo(nvmlDevice_t d, nvmlClockType_t t, unsigned int* c) {
     MAYBE_FAIL("nvmlDeviceGetClockInfo");
     int i = index_of(d);

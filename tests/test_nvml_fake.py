@@ -209,3 +209,13 @@ def test_health_reports_hbm_row_remapping(fake_nvml):
     r.status, r.n = 0, 1
     r.health[0] = h
     assert check(ctypes.byref(r)) == 0
+
+
+def test_health_reports_nvlink_error_totals(fake_nvml):
+    fake_nvml(extra=[f"nvlinkerr {FAKE_UUIDS[4]} 7 0 12 1"])
+    h = probe.nvml_health(FAKE_UUIDS[4])
+    assert (h.nvlink_crc_flit_errors, h.nvlink_crc_data_errors, h.nvlink_replay_errors, h.nvlink_recovery_errors) == (7, 0, 12, 1)
+    h = probe.nvml_health(FAKE_UUIDS[0])
+    assert (h.nvlink_crc_flit_errors, h.nvlink_replay_errors) == (0, 0)
+    fake_nvml(fail=[("nvmlDeviceGetFieldValues", 3)])
+    assert probe.nvml_health(FAKE_UUIDS[0]).nvlink_replay_errors == (1 << 64) - 1     # unknown, not zero
