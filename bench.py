@@ -170,6 +170,13 @@ def mount_section(n_gpus: int, iters: int):
                "native_mount_ms": {"p50": nat_m["p50_ms"], "p99": nat_m["p99_ms"]},
                "note": "slave-pod scheduling (ref: allocator.go:40-99) needs a cluster and is not included"}
         out["mount_to_usable"] = ml.to_usable(iters, 1 << 30, n_gpus)
+        try:
+            # the two-stage hook of a resident worker (this process: cuInit and contexts already paid).  Contexts are kept
+            # and peer access is left alone: the process still belongs to torch.
+            out["mount_to_usable_resident_worker"] = ml.to_usable_resident(iters, 1 << 30, n_gpus, keep_contexts=True,
+                                                                          skip_p2p=True, release_at_end=False)
+        except Exception as e:
+            out["mount_to_usable_resident_worker"] = {"unavailable": f"{type(e).__name__}: {e}"}
         return out
     except Exception as e:  # the bench line must still be printed
         return {"unavailable": f"{type(e).__name__}: {e}"}

@@ -248,7 +248,7 @@ def to_usable(iters, hbm_bytes, n_gpus, real_cgroup=False):
     return out
 
 
-def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts):
+def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts, skip_p2p=False, release_at_end=True):
     """Two-stage hook with a resident worker (this process stands in for it: on the host, sees every GPU, cuInit paid once at
     start-up): native mount -> gmp_check_nodes_in_pod (a helper joins the pod's device cgroup + mount namespace and opens the
     nodes there; nothing executed, no CUDA) -> gmp_probe_all(HOST_VIEW) in-process on the mounted GPUs.  keep_contexts: the worker retains the
@@ -259,6 +259,8 @@ def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts):
     gpus = [(d.uuid, nv[d.uuid].minor) for d in cu]
     expected = [probe.Device(u, m, "", -1, -1) for u, m in gpus]
     flags = probe.PROBE_F_HOST_VIEW | probe.PROBE_F_SKIP_NODES | (probe.PROBE_F_KEEP_DEVICE if keep_contexts else 0)
+    if skip_p2p:  # a caller that shares the process with other CUDA users (bench.py) must not toggle peer access
+        flags |= probe.PROBE_F_SKIP_P2P
     lat, phases = [], []
     for it in range(iters + 1):  # iteration 0 warms the worker (first contexts, module load); not counted
         with harness.Target() as t:
@@ -286,7 +288,7 @@ def to_usable_resident(iters, hbm_bytes, n_gpus, keep_contexts):
                            "alloc_ms": max(h["ms_alloc"] for h in rep["hbm"]),
                            "first_kernel_ms": max(h["ms_first_kernel"] for h in rep["hbm"]),
                            "full_probe_ms": (t_done - t_nodes) / 1e6})
-    if keep_contexts:
+    if keep_contexts and release_at_end:
         # hand the contexts back: one last probe without KEEP_DEVICE resets every device it touched
         probe.probe_all(expected, hbm_bytes=1 << 20, hbm_iters=1, dma_bytes=0,
                         flags=probe.PROBE_F_HOST_VIEW | probe.PROBE_F_SKIP_NODES | probe.PROBE_F_SKIP_P2P, raise_on_error=False)
