@@ -29,3 +29,4 @@ import json,sys; j=json.load(sys.stdin); print({k: j[k] for k in ('status','ms_n
 # (never run on a GPU box yet: if cuInit needs a device the whitelist lacks, the probe says which open() was refused)
 timeout 200 python tools/mount_latency.py --iters 3 --gpus 1 --churn-rounds 0 --usable-iters 5 --real-cgroup \
     --out gpurun_out/mount_latency_real_cgroup.json > gpurun_out/ml_real_cgroup.log 2>&1; tail -c 600 gpurun_out/ml_real_cgroup.log
+timeout 120 python tools/alloc_costs.py 2>/dev/null > gpurun_out/alloc_costs.json; tail -c 1200 gpurun_out/alloc_costs.json
