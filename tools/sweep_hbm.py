@@ -19,6 +19,9 @@ VARIANTS = {0: "256x4x16B default", 1: "256x4x16B .cs", 2: "256x8x16B .cs", 3: "
             4: "256x4x16B no_alloc", 5: "512x2x16B .cs", 6: "128x8x16B .cs", 7: "256x2x32B .cs", 8: "256x4x32B .cs",
             9: "512x2x32B .cs", 10: "256x2x32B default", 11: "1024x1x32B .cs", 12: "1024x2x16B .cs",
             13: "256x1x32B .cs", 14: "512x1x32B .cs", 15: "256x4x32B L2::evict_first"}
+# copy only: the TMA engine (cp.async.bulk through shared memory), stages x chunk
+BULK_VARIANTS = {16: "TMA bulk 6x16K", 17: "TMA bulk 3x32K", 18: "TMA bulk 12x8K", 19: "TMA bulk 3x64K", 20: "TMA bulk 2x96K",
+                 21: "TMA bulk 2x112K", 22: "TMA bulk 4x48K", 23: "TMA bulk 7x32K"}
 
 
 def timeit(fn, iters, warm=2):
@@ -61,8 +64,7 @@ def main():
     }
     probe.hbm_write_pattern(a.data_ptr(), n, 0, 1, s)
     kinds = {k: v for k, v in kinds.items() if k in args.kernels.split(",")}
-    bulk = {16: "TMA bulk 6x16K", 17: "TMA bulk 3x32K", 18: "TMA bulk 12x8K", 19: "TMA bulk 3x64K", 20: "TMA bulk 2x96K",
-            21: "TMA bulk 2x112K", 22: "TMA bulk 4x48K", 23: "TMA bulk 7x32K"}
+    bulk = BULK_VARIANTS
     for kind, (fn, nbytes) in kinds.items():
         variants = {**VARIANTS, **bulk} if kind == "copy" else VARIANTS
         if args.variants:

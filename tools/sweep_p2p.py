@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
 from gpumounter_b200 import probe
-from tools.sweep_hbm import VARIANTS, timeit
+from tools.sweep_hbm import BULK_VARIANTS, VARIANTS, timeit
 
 assert torch.cuda.device_count() >= 2
 n = 1 << 30
@@ -28,12 +28,15 @@ kinds = {"write": lambda: probe.hbm_write_pattern(remote.data_ptr(), n, 0, 1, s)
          "copy_push": lambda: probe.hbm_copy(remote.data_ptr(), local.data_ptr(), n, s)}
 for kind, fn in kinds.items():
     knob = "copy" if kind.startswith("copy") else kind
-    for v in VARIANTS:
+    # copies also through the TMA engine: peer stores from vector instructions plateau at 713 GB/s for every geometry
+    # (profiles/r01_sweep_p2p.json) while the copy engines reach 777 - bulk stores to the peer have not been tried yet
+    variants = {**VARIANTS, **BULK_VARIANTS} if knob == "copy" else VARIANTS
+    for v in variants:
         for c in (0, 1, 2, 4, 8, 16, 32):
             probe.tune(f"{knob}_variant", v)
             probe.tune(f"{knob}_ctas_per_sm", c)
             best, avg = timeit(fn, 5)
-            rows.append({"kernel": kind, "variant": v, "desc": VARIANTS[v], "ctas_per_sm": c, "best_gbs": n / best / 1e6, "avg_gbs": n / avg / 1e6})
+            rows.append({"kernel": kind, "variant": v, "desc": variants[v], "ctas_per_sm": c, "best_gbs": n / best / 1e6, "avg_gbs": n / avg / 1e6})
     top = sorted([r for r in rows if r["kernel"] == kind], key=lambda r: -r["avg_gbs"])[:6]
     print(kind, "top:", [(r["desc"], r["ctas_per_sm"], round(r["avg_gbs"])) for r in top], flush=True)
     worst = sorted([r for r in rows if r["kernel"] == kind], key=lambda r: r["avg_gbs"])[:2]
