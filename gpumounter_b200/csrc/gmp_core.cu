@@ -335,8 +335,9 @@ int run_probe(int ordinal, const gmp_hbm_opts& o, gmp_hbm_result* out, ProbeReso
     // Untimed first touch, in a small allocation of its own and BEFORE the large buffers exist: it loads the three
     // kernels (lazy module loading makes the first launch of each cost milliseconds) and yields the earliest possible
     // "a kernel ran on this GPU and its result verified" milestone, which is what mount-to-usable latency waits for.
-    // cudaMalloc of the large buffers costs ~30 ms per GiB and serialises across the GPUs of one process (8 x 2 GiB:
-    // 0.47 s, profiles/r01_8gpu/mount_latency_resident_8gpu.json), so it must not sit in front of that milestone.
+    // cudaMalloc of the large buffers can be slow - in a process that holds peer mappings every allocation is mapped
+    // into all peers (8 x 2 GiB: 0.47 s, profiles/r01_8gpu/mount_latency_resident_8gpu.json) - so it must not sit in
+    // front of that milestone.
     {
         const uint64_t tf = now_ns();
         const size_t wb = (size_t)std::min<uint64_t>(o.bytes, 4ull << 20);
