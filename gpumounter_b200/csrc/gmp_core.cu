@@ -248,6 +248,10 @@ struct ProbeResources {
     unsigned long long* acc = nullptr;
     void* pinned = nullptr;
     void* touch = nullptr;  // first-touch scratch, normally freed before the large buffers are allocated
+    ProbeResources() = default;
+    ProbeResources(const ProbeResources&) = delete;
+    ProbeResources& operator=(const ProbeResources&) = delete;
+    ~ProbeResources() { release(); }  // idempotent: a normal return has released (and nulled) everything already
     void release() {
         if (pinned) cudaFreeHost(pinned);
         if (touch) cudaFree(touch);
