@@ -37,6 +37,7 @@ GMP_ERR_STILL_MOUNTED = -23
 GMP_ERR_UNSUPPORTED = -24
 GMP_ERR_SLOW = -25
 GMP_ERR_UNHEALTHY = -26
+GMP_ERR_TIMEOUT = -27
 
 
 class ProbeError(RuntimeError):

@@ -29,7 +29,7 @@ class gmp_pod(ctypes.Structure):
 class gmp_mount_env(ctypes.Structure):
     _fields_ = [("devices_root", ctypes.c_char_p), ("dev_prefix", ctypes.c_char_p),
                 ("cgroup_driver", ctypes.c_char_p), ("proc_root", ctypes.c_char_p),
-                ("cgroup2_root", ctypes.c_char_p), ("extensions", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
+                ("cgroup2_root", ctypes.c_char_p), ("extensions", ctypes.c_uint32), ("probe_timeout_ms", ctypes.c_uint32)]
 
 
 EXT_CRI_RUNTIMES, EXT_CGROUP_V2 = 1, 2  # GMP_EXT_*: off by default (section 7 of the header)
@@ -114,10 +114,11 @@ class MountEnv:
     proc_root: Optional[str] = None
     cgroup2_root: Optional[str] = None
     extensions: int = 0
+    probe_timeout_ms: int = 0  # ProbeInPod: kill the probe after this long (0 = no limit)
 
     def to_c(self):
         return gmp_mount_env(enc(self.devices_root), enc(self.dev_prefix), enc(self.cgroup_driver), enc(self.proc_root),
-                             enc(self.cgroup2_root), self.extensions, 0)
+                             enc(self.cgroup2_root), self.extensions, self.probe_timeout_ms)
 
 
 def env_ptr(env: Optional[MountEnv]):

@@ -154,6 +154,7 @@ extern "C" const char* gmp_strerror(int code) {
         case GMP_ERR_UNSUPPORTED: return "cgroup device program can be neither decoded nor re-loaded";
         case GMP_ERR_SLOW: return "a measured rate is under the threshold";
         case GMP_ERR_UNHEALTHY: return "NVML reports uncorrected ECC errors or a hardware slowdown";
+        case GMP_ERR_TIMEOUT: return "the in-pod probe did not finish in time and was killed";
         default: return "unknown error";
     }
 }

@@ -11,6 +11,7 @@
 
 #include <errno.h>
 #include <fcntl.h>
+#include <poll.h>
 #include <pthread.h>
 #include <sched.h>
 #include <signal.h>
@@ -1443,11 +1444,41 @@ extern "C" int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, co
         std::string output;
         char tmp[4096];
         ssize_t r;
-        while ((r = read(out_pipe[0], tmp, sizeof(tmp))) > 0 || (r < 0 && errno == EINTR))
-            if (r > 0) output.append(tmp, (size_t)r);
+        const uint32_t timeout_ms = env ? env->probe_timeout_ms : 0;
+        bool timed_out = false;
+        if (timeout_ms == 0) {
+            while ((r = read(out_pipe[0], tmp, sizeof(tmp))) > 0 || (r < 0 && errno == EINTR))
+                if (r > 0) output.append(tmp, (size_t)r);
+        } else {
+            // bounded wait: the pipe's write end closes when the probe exits, so EOF is "finished"
+            struct timespec t0;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
+            for (;;) {
+                struct timespec now;
+                clock_gettime(CLOCK_MONOTONIC, &now);
+                const long long elapsed = (now.tv_sec - t0.tv_sec) * 1000ll + (now.tv_nsec - t0.tv_nsec) / 1000000ll;
+                if (elapsed >= (long long)timeout_ms) {
+                    timed_out = true;
+                    break;
+                }
+                struct pollfd pf = {out_pipe[0], POLLIN, 0};
+                const int pr = poll(&pf, 1, (int)((long long)timeout_ms - elapsed));
+                if (pr < 0 && errno == EINTR) continue;
+                if (pr <= 0) continue;  // 0: the loop head notices the deadline
+                r = read(out_pipe[0], tmp, sizeof(tmp));
+                if (r > 0) output.append(tmp, (size_t)r);
+                else if (r == 0 || errno != EINTR) break;
+            }
+            if (timed_out) (void)kill(child, SIGKILL);  // host pid: only the mount namespace and the cgroup were entered
+        }
         close(out_pipe[0]);
         int status = 0;
         while (waitpid(child, &status, 0) < 0 && errno == EINTR) {
+        }
+        if (timed_out) {
+            if (exit_status) *exit_status = -1;
+            set_error("in-pod probe did not finish within %u ms and was killed", timeout_ms);
+            return GMP_ERR_TIMEOUT;
         }
         const int code = WIFEXITED(status) ? WEXITSTATUS(status) : -1;
         if (exit_status) *exit_status = code;

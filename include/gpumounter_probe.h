@@ -76,7 +76,8 @@ enum {
     GMP_ERR_STILL_MOUNTED    = -23, /* after an unmount: the device node is still there (or still opens) in the pod */
     GMP_ERR_UNSUPPORTED      = -24, /* section 7: a cgroup-v2 device program that can be neither decoded nor re-loaded */
     GMP_ERR_SLOW             = -25, /* everything verified, but a measured rate is under the caller's threshold */
-    GMP_ERR_UNHEALTHY        = -26  /* everything verified, but NVML reports uncorrected ECC errors or a hardware slowdown */
+    GMP_ERR_UNHEALTHY        = -26, /* everything verified, but NVML reports uncorrected ECC errors or a hardware slowdown */
+    GMP_ERR_TIMEOUT          = -27  /* the in-pod probe did not finish within gmp_mount_env.probe_timeout_ms and was killed */
 };
 
 GMP_API int         gmp_abi_version(void);
@@ -594,7 +595,8 @@ typedef struct gmp_mount_env {
     const char* proc_root;      /* "/proc": where <pid>/ns/mnt is looked up */
     const char* cgroup2_root;   /* "/sys/fs/cgroup": the unified hierarchy, used with GMP_EXT_CGROUP_V2 (section 7) */
     uint32_t    extensions;     /* GMP_EXT_* bits (section 7); 0 = exactly the reference's behaviour */
-    uint32_t    reserved;
+    uint32_t    probe_timeout_ms; /* gmp_probe_in_pod: kill the probe and return GMP_ERR_TIMEOUT after this long; 0 = wait
+                                     for ever (a GPU that hangs must not hang the worker's AddGPU with it) */
 } gmp_mount_env;
 
 /* ref: util.go:21-34 (the first steps of MountGPU / UnmountGPU): container id of ContainerStatuses[0] with

@@ -372,3 +372,30 @@ def test_verify_gone_in_pod_without_executing_anything(fake_nvml):
         # the same verdict as the probe binary's --gone mode, run inside
         rc, rep = util.VerifyUnmountedInPod(pod, gpus, env, dev_dir=t.devdir, raise_on_error=False)
         assert rc == 0 and rep["status"] == 0
+
+
+def test_in_pod_probe_is_killed_when_it_overruns_its_deadline(fake_nvml, tmp_path):
+    """A GPU that hangs must not hang the worker with it: gmp_mount_env.probe_timeout_ms bounds the in-pod probe."""
+    import time
+
+    fake_nvml()
+    slow = tmp_path / "slow-probe"
+    slow.write_text("#!/bin/sh\necho $$ > %s\nexec sleep 30\n" % (tmp_path / "pid"))
+    slow.chmod(0o755)
+    quick = tmp_path / "quick-probe"
+    quick.write_text("#!/bin/sh\nsleep 0.2\necho '{\"status\":0}'\n")
+    quick.chmod(0o755)
+    with harness.Target() as t:
+        env = env_of(t)
+        env.probe_timeout_ms = 400
+        gpu = device.New(3, FAKE_UUIDS[0])
+        t0 = time.monotonic()
+        with pytest.raises(ProbeError) as e:
+            util.ProbeInPod(product_pod(), [gpu], [], env, probe_exe=str(slow))
+        took = time.monotonic() - t0
+        assert e.value.code == _lib.GMP_ERR_TIMEOUT and "400 ms" in e.value.detail and 0.35 < took < 5
+        pid = int((tmp_path / "pid").read_text())
+        time.sleep(0.05)
+        assert not os.path.exists(f"/proc/{pid}") or open(f"/proc/{pid}/stat").read().split()[2] == "Z"   # killed, not left running
+        rc, rep = util.ProbeInPod(product_pod(), [gpu], [], env, probe_exe=str(quick))     # a probe within the deadline is untouched
+        assert rc == 0 and rep == {"status": 0}
