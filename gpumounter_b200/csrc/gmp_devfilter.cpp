@@ -430,12 +430,15 @@ int open_cgroup(const char* dir, Fd* out) {
     return GMP_OK;
 }
 
-int query_programs(int cgroup_fd, std::vector<uint32_t>* ids, uint32_t* attach_flags) {
+// effective = false: the programs attached to this very cgroup.  true: everything the kernel will run for a task in it,
+// i.e. including what ancestors attached (every one of them has to say yes).
+int query_programs(int cgroup_fd, std::vector<uint32_t>* ids, uint32_t* attach_flags, bool effective = false) {
     uint32_t buf[64];
     union bpf_attr a;
     memset(&a, 0, sizeof(a));
     a.query.target_fd = (uint32_t)cgroup_fd;
     a.query.attach_type = BPF_CGROUP_DEVICE;
+    a.query.query_flags = effective ? BPF_F_QUERY_EFFECTIVE : 0;
     a.query.prog_ids = (uint64_t)(uintptr_t)buf;
     a.query.prog_cnt = 64;
     if (sys_bpf(BPF_PROG_QUERY, &a) != 0) {
@@ -617,6 +620,42 @@ void edit_rules(std::vector<gmp_dev_rule>* list, bool default_allow, const gmp_d
 
 // ---- C ABI ------------------------------------------------------------------------------------------
 namespace {
+
+// A grant at the container's level cannot take effect if a program attached further up refuses the device: the kernel
+// runs every effective program and all must agree.  The v1 controller says so itself (writing devices.allow of a child
+// fails with EPERM when the parent lacks the permission); here the ancestors' programs are run on the request.  Programs
+// the interpreter cannot run are not judged.
+int ancestors_allow(int cgroup_fd, const std::vector<uint32_t>& own, const gmp_dev_rule* rules, int n) {
+    std::vector<uint32_t> effective;
+    if (query_programs(cgroup_fd, &effective, nullptr, true) != GMP_OK) {
+        clear_error();  // older kernels: no effective query for this attach type; nothing to judge
+        return GMP_OK;
+    }
+    for (uint32_t id : effective) {
+        if (std::find(own.begin(), own.end(), id) != own.end()) continue;
+        Fd fd;
+        std::vector<gmp_bpf_insn> insns;
+        if (program_fd_by_id(id, &fd) != GMP_OK || read_program(fd.fd, &insns) != GMP_OK) {
+            clear_error();
+            continue;
+        }
+        for (int i = 0; i < n; ++i) {
+            if (rules[i].major < 0 || rules[i].minor < 0) continue;
+            int allowed = 1;
+            if (eval(insns.data(), (int)insns.size(), rules[i].type, rules[i].access, (uint32_t)rules[i].major,
+                     (uint32_t)rules[i].minor, &allowed) != GMP_OK) {
+                clear_error();
+                continue;
+            }
+            if (!allowed) {
+                set_error("device program %u of an ancestor cgroup refuses %c %d:%d: a grant at this level cannot take effect", id,
+                          rules[i].type == GMP_DEV_CHAR ? 'c' : 'b', rules[i].major, rules[i].minor);
+                return GMP_ERR_NODE_DENIED;
+            }
+        }
+    }
+    return GMP_OK;
+}
 
 template <typename F>
 int guarded(F&& body) {  // no C++ exception crosses the C ABI
@@ -876,6 +915,10 @@ extern "C" int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_
             bool lost_race = false;
             rc = query_programs(cg.fd, &ids, &flags);
             if (rc != GMP_OK) return rc;
+            if (grant != 0 && attempt == 0) {
+                rc = ancestors_allow(cg.fd, ids, rules, n_rules);
+                if (rc != GMP_OK) return rc;
+            }
             // 1. plan and 2. load every replacement before 3. attaching any: a program that cannot be edited, or a
             //    replacement the verifier refuses, leaves the cgroup untouched
             struct Step {

@@ -801,7 +801,10 @@ GMP_API int gmp_cgroup2_attach_rules(const char* cgroup_dir, const gmp_dev_rule*
  * shadow are dropped).  grant == 0: remove exactly the allow rules a previous grant appended; where there is none
  * (the runtime itself had granted the device) append a deny rule instead.  A cgroup with no device program is
  * unrestricted at that level: nothing to do, *programs = 0.  Programs in other layouts are handled as gmp_devfilter_plan
- * describes.  Any error leaves every program of the cgroup untouched.
+ * describes.  Before a grant the programs ANCESTOR cgroups attached are run on the request: if one of them refuses the
+ * device, no grant at this level can take effect and the call returns GMP_ERR_NODE_DENIED (what the v1 controller does
+ * itself: writing a child's devices.allow fails with EPERM when the parent lacks the permission).  Any error leaves
+ * every program of the cgroup untouched.
  */
 GMP_API int gmp_cgroup2_update_devices(const char* cgroup_dir, const gmp_dev_rule* rules, int n_rules, int grant,
                                        int* programs);

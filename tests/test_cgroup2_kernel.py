@@ -400,3 +400,26 @@ def test_check_nodes_in_pod_on_the_unified_hierarchy(fake_nvml):
         rc, idx = util.CheckNodesInPod(pod, [gpu], env, raise_on_error=False)
         assert rc in (0, _lib.GMP_ERR_NODE_GPU)          # past the filter (ENXIO here: no driver), never "denied"
         util.UnmountGPU(pod, gpu, False, env)
+
+
+def test_an_ancestor_that_refuses_the_gpu_is_reported_before_anything_changes(fake_nvml):
+    """The kernel runs the device programs of every level and all must agree.  v1 refuses the write to a child's
+    devices.allow when the parent lacks the permission; on v2 the ancestors' programs are run on the request first."""
+    gpus_cfg = fake_nvml()
+    with harness.Target(cgroup2=True) as t:
+        env, pod = env_of(t), product_pod()
+        u, m, _ = gpus_cfg[0]
+        gpu = device.New(m, u)
+        pod_level = os.path.dirname(t.cgroup_dir)                       # .../pod<uid>: an ancestor of the container
+        o.kernel_attach_rules(pod_level, o.RUNC_DEFAULT_RULES)          # knows nothing of 195:*
+        before = attached(t)
+        with pytest.raises(ProbeError) as e:
+            util.MountGPU(pod, gpu, env)
+        assert e.value.code == _lib.GMP_ERR_NODE_DENIED and "ancestor cgroup refuses" in e.value.detail
+        assert attached(t) == before and t.nodes() == []
+        # the ancestor learns about the GPUs (its own program is edited the same way): now the container-level grant works
+        assert c.update_devices(pod_level, [c.Rule(c.DEV_CHAR, 195, -1, c.ACC_ALL)], True) == 1
+        util.MountGPU(pod, gpu, env)
+        assert t.try_open(m) in NO_DRIVER
+        util.UnmountGPU(pod, gpu, False, env)
+        assert attached(t) == before
