@@ -87,8 +87,9 @@ cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, c
 cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed,
                           unsigned long long* d_acc, cudaStream_t s, const LaunchCfg* cfg = nullptr);
 cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s, const LaunchCfg* cfg = nullptr);
-// Geometry for kernels whose pointer is PEER memory (NVLink): picked by tools/sweep_p2p.py.
-extern const LaunchCfg kPeerStoreCfg, kPeerLoadCfg;
+// Geometry for kernels whose pointer is PEER memory (NVLink): picked by tools/sweep_p2p.py, held in tunables().
+LaunchCfg peer_store_cfg();
+LaunchCfg peer_load_cfg();
 void decode_acc(const unsigned long long raw[4], gmp_verify_result* out);
 
 // Launch geometry knobs (benchmarking only; see gmp_tune()).
@@ -99,6 +100,10 @@ struct Tunables {
     int write_variant;
     int read_variant;
     int copy_variant;
+    int peer_store_variant;
+    int peer_store_ctas_per_sm;
+    int peer_load_variant;
+    int peer_load_ctas_per_sm;
 };
 Tunables& tunables();
 
@@ -106,7 +111,11 @@ Tunables& tunables();
 // READ/WRITE/NVLINK/ATOMICS status matrices (n x n each) and active NVLink counts in one NVML session.
 int nvml_p2p_everything(const char* const* uuids, int n, int32_t* caps_out[4], int32_t* nvlink_active);
 
-// Drops per-device state cached across calls (looked-up symbol addresses); call after cudaDeviceReset().
+// NVML's (minor, index, bus id) of the devices named by devs[i].uuid, looked up one by one; entries NVML cannot
+// answer for get minor = UINT32_MAX.  GMP_OK when all n were found.
+int nvml_lookup_by_uuid(gmp_device* devs, int n, int* n_found);
+
+// Drops per-device state cached across calls (what GMP_HBM_F_RETAIN calls left behind); call after cudaDeviceReset().
 void forget_device_state(int ordinal);
 
 // ---- misc --------------------------------------------------------------------

@@ -444,6 +444,44 @@ __global__ void __launch_bounds__(32) k_hbm_copy_bulk(unsigned char* __restrict_
     bulk::wait_all();  // writes complete before the CTA (and its shared memory) goes away
 }
 
+// ---- pattern write through the TMA engine (peer stores) -------------------------------------------
+// Vector stores into PEER memory plateau at ~713 GB/s per direction whatever the geometry (profiles/r01_sweep_p2p.json)
+// while the copy engines move 777 GB/s over the same NVLink pair.  Here the CTA's threads only generate the pattern -
+// into shared memory - and ONE thread hands each finished CHUNK to the bulk-copy engine (cp.async.bulk shared -> global),
+// which issues the largest write requests the fabric takes; STAGES chunks are in flight per CTA.  The last chunk may be
+// short (any multiple of 16 bytes).  SASS: STS.128, UBLKCP.G.S, no STG at all.
+template <int PAT, int THREADS, int STAGES, int CHUNK>
+__global__ void __launch_bounds__(THREADS) k_hbm_write_pattern_bulk(unsigned char* __restrict__ dst, uint64_t nlanes, uint64_t seed) {
+    extern __shared__ __align__(128) unsigned char stage_mem[];
+    constexpr uint64_t kChunkLanes = CHUNK / 16;
+    const uint64_t nchunks = (nlanes + kChunkLanes - 1) / kChunkLanes;
+    uint64_t k = 0;
+    for (uint64_t c = blockIdx.x; c < nchunks; c += gridDim.x, ++k) {
+        const int st = (int)(k % STAGES);
+        if (k >= (uint64_t)STAGES) {
+            // the bulk store that last used this stage must have finished READING it
+            if (threadIdx.x == 0) bulk::wait_read<STAGES - 1>();
+            __syncthreads();
+        }
+        uint4* stage = reinterpret_cast<uint4*>(stage_mem + (size_t)st * CHUNK);
+        const uint64_t L0 = c * kChunkLanes;
+        const uint32_t lanes = (uint32_t)(nlanes - L0 < kChunkLanes ? nlanes - L0 : kChunkLanes);
+#pragma unroll 4
+        for (uint32_t l = threadIdx.x; l < lanes; l += THREADS) {
+            uint64_t w0, w1;
+            lane_words<PAT>(seed, L0 + l, w0, w1);
+            stage[l] = pack(w0, w1);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the bulk engine
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            bulk::store(dst + L0 * 16, stage, lanes * 16u);
+            bulk::commit();
+        }
+    }
+    if (threadIdx.x == 0) bulk::wait_all();  // writes complete before the CTA (and its shared memory) goes away
+}
+
 __global__ void k_hbm_corrupt(unsigned char* p, size_t off, unsigned char mask) { p[off] ^= mask; }
 
 // ---- launch geometry --------------------------------------------------------------
@@ -455,7 +493,10 @@ Tunables& tunables() {
     // hardware balances the ~10% speed spread between SMs) for the store-heavy kernels, exactly one resident
     // wave for the register-accumulating verify kernel.
     static Tunables t = {/*write_ctas_per_sm*/ 24, /*read*/ 4, /*copy*/ 128,
-                         /*write_variant*/ 12, /*read_variant*/ 10, /*copy_variant*/ 21};
+                         /*write_variant*/ 12, /*read_variant*/ 10, /*copy_variant*/ 21,
+                         // pointers into PEER memory (NVLink), picked by tools/sweep_p2p.py:
+                         /*peer_store_variant*/ 11, /*peer_store_ctas_per_sm*/ 8,  // 1024x1x32B .cs: ~713 GB/s whatever the geometry
+                         /*peer_load_variant*/ 1, /*peer_load_ctas_per_sm*/ 32};   // 256x4x16B .cs x 32 CTAs/SM: 781 GB/s (cudaMemcpyPeer: 770)
     return t;
 }
 
@@ -618,8 +659,56 @@ static cudaError_t launch_verify_pat(const uint4* src, uint64_t nlanes, uint32_t
             return cudaErrorInvalidValue;        \
     }
 
-const LaunchCfg kPeerStoreCfg = {11, 8};  // 1024x1x32B .cs: peer stores plateau at ~713 GB/s whatever the geometry
-const LaunchCfg kPeerLoadCfg = {1, 32};   // 256x4x16B .cs x 32 CTAs/SM: 781 GB/s (cudaMemcpyPeer: 770)
+LaunchCfg peer_store_cfg() { return {tunables().peer_store_variant, tunables().peer_store_ctas_per_sm}; }
+LaunchCfg peer_load_cfg() { return {tunables().peer_load_variant, tunables().peer_load_ctas_per_sm}; }
+
+// Write variants kBulkWriteFirst.. : pattern -> shared memory -> bulk store (k_hbm_write_pattern_bulk).
+constexpr int kBulkWriteFirst = 32;
+#ifdef GMP_LEAN
+#define GMP_BULK_WRITE_VARIANTS(X) X(1, 256, 4, 32768)
+#else
+#define GMP_BULK_WRITE_VARIANTS(X) \
+    X(0, 256, 4, 16384)           \
+    X(1, 256, 4, 32768)           \
+    X(2, 512, 4, 32768)           \
+    X(3, 256, 2, 65536)           \
+    X(4, 512, 3, 65536)           \
+    X(5, 128, 8, 8192)            \
+    X(6, 1024, 2, 98304)          \
+    X(7, 256, 6, 32768)
+#endif
+constexpr int kBulkWriteCount = 8;
+
+template <int PAT, int THREADS, int STAGES, int CHUNK>
+static cudaError_t launch_write_bulk_cfg(unsigned char* dst, uint64_t nlanes, uint64_t seed, int sm_count, int ctas_per_sm,
+                                         cudaStream_t s) {
+    constexpr int kSmem = STAGES * CHUNK;
+    // set on every launch: the attribute lives in the context, which callers may have reset since the last call
+    cudaError_t e = cudaFuncSetAttribute(k_hbm_write_pattern_bulk<PAT, THREADS, STAGES, CHUNK>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+    if (e != cudaSuccess) return e;
+    const uint64_t nchunks = (nlanes * 16 + CHUNK - 1) / CHUNK;
+    const int fit = (227 * 1024) / (kSmem + 1024);
+    const int per_sm = ctas_per_sm > 0 ? ctas_per_sm : (fit > 0 ? fit : 1);
+    uint64_t grid = (uint64_t)sm_count * (uint64_t)per_sm;
+    if (grid > nchunks) grid = nchunks;
+    k_hbm_write_pattern_bulk<PAT, THREADS, STAGES, CHUNK><<<(unsigned)grid, THREADS, kSmem, s>>>(dst, nlanes, seed);
+    return cudaGetLastError();
+}
+
+template <int PAT>
+static cudaError_t launch_write_bulk_pat(int variant, unsigned char* dst, uint64_t nlanes, uint64_t seed, int sm_count,
+                                         int ctas_per_sm, cudaStream_t s) {
+    switch (variant - kBulkWriteFirst) {
+#define X(ID, T, ST, CH) \
+    case ID:             \
+        return launch_write_bulk_cfg<PAT, T, ST, CH>(dst, nlanes, seed, sm_count, ctas_per_sm, s);
+        GMP_BULK_WRITE_VARIANTS(X)
+#undef X
+        default:
+            return cudaErrorNotSupported;
+    }
+}
 
 cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, cudaStream_t s, const LaunchCfg* cfg) {
     if (bytes == 0) return cudaSuccess;
@@ -629,6 +718,39 @@ cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, c
     const uint64_t nlanes = bytes / 16;
     const uint32_t tail = (uint32_t)(bytes % 16);
     count_launch();
+    const int variant = cfg ? cfg->variant : tunables().write_variant;
+    LaunchCfg fallback = {kFallbackVariant, cfg ? cfg->ctas_per_sm : tunables().write_ctas_per_sm};
+    if (variant >= kBulkWriteFirst) {
+        // whole 16-byte lanes through the bulk engine; a ragged buffer (never the case for the P2P probe) or a pattern
+        // / geometry this build does not carry goes through the vector kernel
+        if (tail == 0 && nlanes != 0 && (reinterpret_cast<uintptr_t>(dptr) & 15u) == 0) {
+            const int ctas = cfg ? cfg->ctas_per_sm : tunables().write_ctas_per_sm;
+            cudaError_t be = cudaErrorNotSupported;
+            switch (pattern) {
+                case GMP_PAT_SPLITMIX:
+                    be = launch_write_bulk_pat<GMP_PAT_SPLITMIX>(variant, static_cast<unsigned char*>(dptr), nlanes, seed, di.sm_count, ctas, s);
+                    break;
+#ifndef GMP_LEAN
+                case GMP_PAT_ZERO:
+                    be = launch_write_bulk_pat<GMP_PAT_ZERO>(variant, static_cast<unsigned char*>(dptr), nlanes, seed, di.sm_count, ctas, s);
+                    break;
+                case GMP_PAT_ONES:
+                    be = launch_write_bulk_pat<GMP_PAT_ONES>(variant, static_cast<unsigned char*>(dptr), nlanes, seed, di.sm_count, ctas, s);
+                    break;
+                case GMP_PAT_CHECKER:
+                    be = launch_write_bulk_pat<GMP_PAT_CHECKER>(variant, static_cast<unsigned char*>(dptr), nlanes, seed, di.sm_count, ctas, s);
+                    break;
+                case GMP_PAT_ADDRESS:
+                    be = launch_write_bulk_pat<GMP_PAT_ADDRESS>(variant, static_cast<unsigned char*>(dptr), nlanes, seed, di.sm_count, ctas, s);
+                    break;
+#endif
+                default:
+                    break;
+            }
+            if (be != cudaErrorNotSupported) return be;
+        }
+        cfg = &fallback;
+    }
 #define CALL(P) launch_write_pat<P>(static_cast<uint4*>(dptr), nlanes, tail, seed, di.sm_count, s, cfg)
     GMP_PATTERN_SWITCH(pattern, CALL)
 #undef CALL
@@ -868,9 +990,13 @@ extern "C" int gmp_tune(const char* knob, int value) try {
     if (k == "write_ctas_per_sm") slot = &t.write_ctas_per_sm;
     else if (k == "read_ctas_per_sm") slot = &t.read_ctas_per_sm;
     else if (k == "copy_ctas_per_sm") slot = &t.copy_ctas_per_sm;
-    else if (k == "write_variant") { slot = &t.write_variant; limit = kVariantCount - 1; }
+    else if (k == "write_variant") { slot = &t.write_variant; limit = kBulkWriteFirst + kBulkWriteCount - 1; }
     else if (k == "read_variant") { slot = &t.read_variant; limit = kVariantCount - 1; }
     else if (k == "copy_variant") { slot = &t.copy_variant; limit = kVariantCount + 8 - 1; }
+    else if (k == "peer_store_variant") { slot = &t.peer_store_variant; limit = kBulkWriteFirst + kBulkWriteCount - 1; }
+    else if (k == "peer_store_ctas_per_sm") slot = &t.peer_store_ctas_per_sm;
+    else if (k == "peer_load_variant") { slot = &t.peer_load_variant; limit = kVariantCount - 1; }
+    else if (k == "peer_load_ctas_per_sm") slot = &t.peer_load_ctas_per_sm;
     if (slot == nullptr) {
         set_error("unknown knob '%s'", knob);
         return GMP_ERR_INVALID;
@@ -894,8 +1020,8 @@ extern "C" int gmp_tune(const char* knob, int value) try {
 //     allocator may simply answer out-of-memory, and a probe must not compete with the workload for it;
 //   * a monitor that must not disturb the tenant: cudaFree synchronises the WHOLE device, so a periodic
 //     check through the allocating entry point stalls every stream of the workload once per call;
-//   * code that runs while the allocator is off limits, e.g. while some other thread of the process is
-//     capturing a stream in global capture mode, where cudaMalloc is a forbidden call.
+//   * a caller whose own rules forbid allocator calls at that point (a latency-critical section of the worker, a
+//     process whose device memory is budgeted up front).
 // For them the scratch lives in device memory that exists from the moment the library is loaded: a
 // file-scope array that every GPU using the library holds until the process exits (65 568 bytes).  The
 // buffer is cut into 4 MiB segments, one CTA per segment writes that segment's partial verdict into its
@@ -1015,29 +1141,27 @@ __global__ void __launch_bounds__(256) k_noalloc_fold(unsigned long long* __rest
     block_fold_and_publish<256>(bad, inv_first, x, s, slots + (size_t)kNoAllocResultSlot * 4);
 }
 
-// Device address of g_noalloc_scratch on the CURRENT device, looked up once per device.
-static std::atomic<unsigned long long*> g_noalloc_scratch_addr[64];
-
-// A cudaDeviceReset() destroys the context the address was looked up in; the library's own resets call this.
-void forget_device_state(int ordinal) {
-    if (ordinal >= 0 && ordinal < 64) g_noalloc_scratch_addr[ordinal].store(nullptr, std::memory_order_release);
-}
-
-static cudaError_t noalloc_scratch_on_current_device(unsigned long long** out) {
-    std::atomic<unsigned long long*>* cache = g_noalloc_scratch_addr;
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
+// Set-up for the CURRENT device, done by every call (a few microseconds once the module is resident):
+//  * the array's device address.  Looked up each time instead of cached per device: the address belongs to the device's
+//    current primary context, and a cudaDeviceReset() made by the caller - which this library cannot see - would turn a
+//    cached pointer into a dangling one for the rest of the process;
+//  * all six kernels of this entry point are made resident (cudaFuncGetAttributes loads a kernel's module without
+//    launching it).  CUDA loads a kernel lazily at its first launch, and that load allocates device memory for the
+//    code: without this step a first call with pattern A would leave the kernels of patterns B..E to be loaded - and
+//    allocated - by some later call, on a GPU that may be full by then.  After ONE call on a device, whatever its
+//    pattern or size, no later call on that device allocates anything.
+static cudaError_t noalloc_setup_on_current_device(unsigned long long** out) {
+    void* addr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);  // the current device's copy of the array
     if (e != cudaSuccess) return e;
-    const bool cacheable = dev >= 0 && dev < 64;
-    unsigned long long* p = cacheable ? cache[dev].load(std::memory_order_acquire) : nullptr;
-    if (p == nullptr) {
-        void* addr = nullptr;
-        e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);  // `dev` is current: this is ITS copy of the array
-        if (e != cudaSuccess) return e;
-        p = static_cast<unsigned long long*>(addr);
-        if (cacheable) cache[dev].store(p, std::memory_order_release);
-    }
-    *out = p;
+    cudaFuncAttributes fa;
+    if ((e = cudaFuncGetAttributes(&fa, k_hbm_read_verify_segments<GMP_PAT_SPLITMIX>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, k_hbm_read_verify_segments<GMP_PAT_ZERO>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, k_hbm_read_verify_segments<GMP_PAT_ONES>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, k_hbm_read_verify_segments<GMP_PAT_CHECKER>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, k_hbm_read_verify_segments<GMP_PAT_ADDRESS>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, k_noalloc_fold)) != cudaSuccess) return e;
+    *out = static_cast<unsigned long long*>(addr);
     return cudaSuccess;
 }
 
@@ -1067,7 +1191,7 @@ extern "C" int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int p
     }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     unsigned long long* scratch = nullptr;
-    GMP_CUDA(noalloc_scratch_on_current_device(&scratch));
+    GMP_CUDA(noalloc_setup_on_current_device(&scratch));
     unsigned long long* result = scratch + (size_t)kNoAllocResultSlot * 4;
     // The array still holds the previous call's slots and result.  Slots are fully rewritten by the CTAs that
     // own them and only the first nsegs are read back; the result slot is accumulated into, so it must be zero.

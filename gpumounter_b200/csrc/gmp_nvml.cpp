@@ -88,6 +88,7 @@ int NvmlSession::open() {
         {(void**)&DeviceGetMinorNumber, "nvmlDeviceGetMinorNumber", true},
         {(void**)&DeviceGetUUID, "nvmlDeviceGetUUID", true},
         {(void**)&DeviceGetPciInfo, "nvmlDeviceGetPciInfo_v3", false},
+        {(void**)&DeviceGetIndex, "nvmlDeviceGetIndex", false},
         {(void**)&DeviceGetP2PStatus, "nvmlDeviceGetP2PStatus", false},
         {(void**)&DeviceGetNvLinkState, "nvmlDeviceGetNvLinkState", false},
         {(void**)&DeviceGetComputeRunningProcesses, "nvmlDeviceGetComputeRunningProcesses_v3", false},
@@ -418,6 +419,43 @@ extern "C" int gmp_nvml_nvlink_active(const char* uuid, int* active_links, int* 
 } catch (...) {
     return ::gmp::caught_exception();
 }
+
+// NVML's record of the devices named by UUID, one by one (minor, index, bus id filled in; `found[i]` says which).
+// For a caller INSIDE a pod that holds only some of the node's GPUs: there the index walk of gmp_enumerate_nvml, which
+// follows the reference to the letter (ref: collector.go:56-77 returns at the first failing handle), stops at the first
+// GPU whose node the pod's device cgroup does not let NVML open, while a by-UUID lookup of a mounted GPU still works.
+namespace gmp {
+int nvml_lookup_by_uuid(gmp_device* devs, int n, int* n_found) {
+    *n_found = 0;
+    NvmlSession nv;
+    int rc = nv.open();
+    if (rc != GMP_OK) return rc;
+    int first_error = GMP_OK;
+    for (int i = 0; i < n; ++i) {
+        nvmlDevice_t dev;
+        unsigned int minor = 0;
+        nvmlReturn_t r = nv.DeviceGetHandleByUUID(devs[i].uuid, &dev);
+        if (r == NVML_SUCCESS) r = nv.DeviceGetMinorNumber(dev, &minor);
+        if (r != NVML_SUCCESS) {
+            if (first_error == GMP_OK) first_error = nv.fail(r, "nvmlDeviceGetHandleByUUID");
+            devs[i].nvml_index = -1;
+            devs[i].minor = UINT32_MAX;
+            continue;
+        }
+        devs[i].minor = minor;
+        devs[i].nvml_index = -1;
+        unsigned int index = 0;
+        if (nv.DeviceGetIndex && nv.DeviceGetIndex(dev, &index) == NVML_SUCCESS) devs[i].nvml_index = (int32_t)index;
+        if (nv.DeviceGetPciInfo) {
+            nvmlPciInfo_t pci;
+            memset(&pci, 0, sizeof(pci));
+            if (nv.DeviceGetPciInfo(dev, &pci) == NVML_SUCCESS) snprintf(devs[i].pci_bus_id, GMP_PCI_LEN, "%s", pci.busId);
+        }
+        ++*n_found;
+    }
+    return *n_found == n ? GMP_OK : first_error;
+}
+}  // namespace gmp
 
 // All four capability matrices and the active-link counts in ONE NVML session (internal; the P2P probe
 // would otherwise pay NVML's ~100 ms load+init five times over).

@@ -37,6 +37,7 @@ class NvmlSession {
     nvmlReturn_t (*DeviceGetMinorNumber)(nvmlDevice_t, unsigned int*) = nullptr;
     nvmlReturn_t (*DeviceGetUUID)(nvmlDevice_t, char*, unsigned int) = nullptr;
     nvmlReturn_t (*DeviceGetPciInfo)(nvmlDevice_t, nvmlPciInfo_t*) = nullptr;
+    nvmlReturn_t (*DeviceGetIndex)(nvmlDevice_t, unsigned int*) = nullptr;
     nvmlReturn_t (*DeviceGetP2PStatus)(nvmlDevice_t, nvmlDevice_t, nvmlGpuP2PCapsIndex_t, nvmlGpuP2PStatus_t*) = nullptr;
     nvmlReturn_t (*DeviceGetNvLinkState)(nvmlDevice_t, unsigned int, nvmlEnableState_t*) = nullptr;
     nvmlReturn_t (*DeviceGetComputeRunningProcesses)(nvmlDevice_t, unsigned int*, nvmlProcessInfo_t*) = nullptr;

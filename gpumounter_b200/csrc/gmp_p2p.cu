@@ -103,6 +103,7 @@ int verify_local(Session& s, gmp_p2p_result* out, int i, int j, size_t off, size
 
 int run_pairs(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
     const int n = out->n;
+    const LaunchCfg kPeerStoreCfg = peer_store_cfg(), kPeerLoadCfg = peer_load_cfg();
     for (int i = 0; i < n; ++i) {
         for (int j = 0; j < n; ++j) {
             if (i == j || !out->can_access[cell(n, i, j)]) continue;
@@ -186,6 +187,7 @@ int partner_in_round(int m, int r, int x) {
 
 int run_bidir(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
     const int n = out->n;
+    const LaunchCfg kPeerStoreCfg = peer_store_cfg();
     const int m = (n % 2 == 0) ? n : n + 1;  // odd n: one GPU sits out each round
     std::vector<double> worst((size_t)n, 0.0);
     std::vector<bool> seen((size_t)n, false);
@@ -234,6 +236,7 @@ int run_bidir(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
 
 int run_alltoall(Session& s, const gmp_p2p_opts& o, gmp_p2p_result* out) {
     const int n = out->n;
+    const LaunchCfg kPeerStoreCfg = peer_store_cfg();
     for (int i = 0; i < n; ++i)
         for (int j = 0; j < n; ++j)
             if (i != j && !out->can_access[cell(n, i, j)]) return GMP_OK;  // not a full mesh: skip

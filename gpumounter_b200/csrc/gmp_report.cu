@@ -217,6 +217,19 @@ int probe_all_impl(const gmp_device* expected, int n_expected, const gmp_probe_o
             const uint64_t tn = now_ns();
             nvml_hold.reset(new (std::nothrow) NvmlHold());
             out->nvml_status = gmp_enumerate_nvml(nvml, GMP_MAX_DEVICES, &n_nvml);
+            if (out->nvml_status == GMP_ERR_NVML && n_expected > 0) {
+                // Inside a pod that holds only some of the node's GPUs NVML's index walk stops at the first GPU the
+                // pod's device cgroup hides; the mounted ones still answer by UUID, which is all the cross-check needs.
+                for (int i = 0; i < n_expected; ++i) {
+                    nvml[i] = expected[i];
+                    nvml[i].cuda_ordinal = -1;
+                }
+                int found = 0;
+                if (nvml_lookup_by_uuid(nvml, n_expected, &found) == GMP_OK) {
+                    n_nvml = n_expected;
+                    out->nvml_status = GMP_OK;
+                }
+            }
             if (out->nvml_status != GMP_OK) {
                 n_nvml = 0;  // reported, not fatal: a pod need not ship libnvidia-ml
                 nvml_error = gmp_last_error();
@@ -517,6 +530,8 @@ extern "C" int gmp_report_json(const gmp_report* r, char* buf, size_t cap) try {
         j.kms("ms_teardown", h.ns_teardown);
         j.kms("ms_total", h.ns_total);
         j.ku("mono_first_verified_ns", h.mono_first_verified_ns);
+        j.ku("mono_context_begin_ns", h.mono_context_begin_ns);
+        j.ku("mono_context_end_ns", h.mono_context_end_ns);
         j.raw("}");
     }
     j.raw("]");

@@ -142,6 +142,7 @@ void usage() {
             "         [--strict-health]  (fail with -26 on uncorrected ECC errors or a hardware slowdown)\n"
             "         [--nodes-only]  (device nodes + driver library only: no CUDA, a few ms)\n"
             "         [--host-view]   (run from the host: CUDA may see more GPUs than the listed ones)\n"
+            "         [--tune knob=value]...  (launch geometry, see gmp_tune)\n"
             "Probes the GPUs visible to this process (or exactly the listed ones) and prints one JSON line.\n"
             "Defaults may come from GPUMOUNTER_PROBE_BYTES / _ITERS / _PATTERNS / _SEED / _DMA_BYTES / _P2P_BYTES / _SKIP_P2P /\n"
             "_MIN_HBM_GBS / _MIN_P2P_GBS.\n");
@@ -221,6 +222,14 @@ int main(int argc, char** argv) {
         else if (a == "--skip-copy") o.hbm.flags |= GMP_HBM_F_SKIP_COPY;
         else if (a == "--lib-baselines") o.hbm.flags |= GMP_HBM_F_LIB_BASELINES;
         else if (a == "--matrix-only") o.p2p.flags |= GMP_P2P_F_MATRIX_ONLY;
+        else if (a == "--tune") {  // benchmarking: --tune knob=value (gmp_tune)
+            const std::string kv = need("--tune");
+            const size_t eq = kv.find('=');
+            if (eq == std::string::npos || gmp_tune(kv.substr(0, eq).c_str(), (int)parse_u32(kv.c_str() + eq + 1)) < 0) {
+                fprintf(stderr, "bad --tune '%s': %s\n", kv.c_str(), gmp_last_error());
+                return 64;
+            }
+        }
         else if (a == "-h" || a == "--help") {
             usage();
             return 0;

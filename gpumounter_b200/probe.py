@@ -24,6 +24,7 @@ PATTERN_NAMES = ("splitmix", "zero", "ones", "checker", "address")
 HBM_F_SKIP_COPY = 1 << 0
 HBM_F_KEEP_DEVICE = 1 << 1
 HBM_F_LIB_BASELINES = 1 << 2
+HBM_F_RETAIN = 1 << 3  # keep buffers, streams and the pinned staging block for the next call on the device (implies KEEP_DEVICE)
 UINT64_MAX = (1 << 64) - 1
 
 
@@ -93,6 +94,8 @@ class gmp_hbm_result(ctypes.Structure):
         ("mono_first_verified_ns", ctypes.c_uint64),
         ("lib_memset_gbs", ctypes.c_double),
         ("lib_memcpy_gbs", ctypes.c_double),
+        ("mono_context_begin_ns", ctypes.c_uint64),
+        ("mono_context_end_ns", ctypes.c_uint64),
     ]
 
     def as_dict(self) -> dict:
@@ -202,9 +205,10 @@ NOALLOC_MAX_BYTES = 8 << 30
 
 def hbm_read_verify_noalloc(dptr: int, nbytes: int, pattern: int = PAT_SPLITMIX, seed: int = 0, stream: int = 0) -> VerifyResult:
     """hbm_read_verify() for callers that must not allocate device memory (a sidecar on a GPU the tenant has
-    filled, a monitor that must not trigger cudaFree's device-wide synchronisation, code running while another
-    thread captures a stream).  Scratch is a fixed array inside the library: at most NOALLOC_MAX_BYTES per call,
-    one call at a time per device, first call per device before any stream capture."""
+    filled, a monitor that must not trigger cudaFree's device-wide synchronisation, a caller whose own rules forbid
+    allocator calls at that point).  Scratch is a fixed array inside the library: at most NOALLOC_MAX_BYTES per call,
+    one call at a time per device; make the first call on a device early (it loads the kernels) and before any
+    stream capture."""
     f = lib().gmp_hbm_read_verify_noalloc
     f.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_uint64,
                   ctypes.POINTER(gmp_verify_result), ctypes.c_void_p]
@@ -262,6 +266,13 @@ def probe_hbm(uuid: Optional[str] = None, *, nbytes: int = 0, iters: int = 0, pa
     if raise_on_error:
         check(rc, "gmp_probe_hbm")
     return r
+
+
+def probe_hbm_release(uuid: Optional[str] = None) -> None:
+    """Free what HBM_F_RETAIN calls left on one device (or on every device)."""
+    f = lib().gmp_probe_hbm_release
+    f.argtypes = [ctypes.c_char_p]
+    check(f(uuid.encode() if uuid else None), "gmp_probe_hbm_release")
 
 
 GMP_P2P_CELLS = GMP_MAX_DEVICES * GMP_MAX_DEVICES

@@ -249,10 +249,9 @@ GMP_API int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, void
  * Who needs it: a health-check sidecar on a GPU whose memory the tenant has already filled (cudaMalloc
  * can fail there, and a probe should not compete with the workload for memory); a monitor that must
  * not stall the tenant (the allocating entry point ends in cudaFree, which synchronises the whole
- * device); and code that runs while the CUDA allocator is off limits, for instance while another
- * thread of the process is capturing a stream.  This call makes no cudaMalloc / cudaFree / other
- * allocating call: its scratch is a 65 568-byte array that is part of the library image and sits in
- * the memory of every GPU that uses the library, until the process exits.
+ * device); and a caller whose own rules forbid allocator calls at that point.  This call makes no
+ * cudaMalloc / cudaFree / other allocating call: its scratch is a 65 568-byte array that is part of the
+ * library image and sits in the memory of every GPU that uses the library, until the process exits.
  *
  * Same arguments, same result and the same bit-exact checksums as gmp_hbm_read_verify().  Limits and
  * rules that come with the fixed scratch:
@@ -261,11 +260,12 @@ GMP_API int gmp_hbm_verify_fetch(const void* d_acc, gmp_verify_result* out, void
  *   - every call on a device uses the same array, which still holds the previous call's data (the
  *     call clears the part that has to start at zero).  Two calls whose GPU work overlaps — different
  *     streams, different threads — race on it and return garbage: serialise them per device;
- *   - the first call on each device looks up the array's device address; make that first call before
- *     starting any stream capture.  The address belongs to the device's current context: the
- *     library forgets it when one of its own calls resets the device (gmp_probe_hbm without
- *     GMP_HBM_F_KEEP_DEVICE, gmp_probe_p2p, gmp_probe_all), but it cannot see a cudaDeviceReset()
- *     made by the caller — after one of those, do not call this entry point again in the process.
+ *   - the FIRST call on a device is the one that costs something: it loads the library's device code
+ *     there (the array comes with it) and makes all of this entry point's kernels resident, whatever
+ *     pattern that first call uses.  Make it early — while the GPU still has room, and before starting
+ *     any stream capture; whether later calls may run beside a capture is the caller's to establish.
+ *     Every call looks the array's address up again (microseconds), so a cudaDeviceReset() made by the
+ *     caller between two calls is harmless: the next call simply is a "first call" again.
  */
 #define GMP_NOALLOC_MAX_BYTES (8ull << 30)
 GMP_API int gmp_hbm_read_verify_noalloc(const void* dptr, size_t bytes, int pattern, uint64_t seed,
@@ -276,7 +276,8 @@ GMP_API int gmp_hbm_corrupt(void* dptr, size_t bytes, size_t byte_offset, uint8_
  * Benchmarking knob, process-wide, not for production callers: selects the
  * launch geometry of the three kernels.  Knobs: "write_ctas_per_sm",
  * "read_ctas_per_sm", "copy_ctas_per_sm", "write_variant", "read_variant",
- * "copy_variant".  A *_ctas_per_sm of 0 means one resident wave (persistent
+ * "copy_variant", and for pointers into peer memory "peer_store_variant",
+ * "peer_store_ctas_per_sm", "peer_load_variant", "peer_load_ctas_per_sm".  A *_ctas_per_sm of 0 means one resident wave (persistent
  * grid sized by the occupancy API); N > 0 launches N x (SM count) CTAs.
  * value < 0 only queries.  Returns the value in force (>= 0) or
  * GMP_ERR_INVALID.
@@ -316,7 +317,15 @@ typedef struct gmp_hbm_opts {
 enum {
     GMP_HBM_F_SKIP_COPY   = 1u << 0,
     GMP_HBM_F_KEEP_DEVICE = 1u << 1,  /* do not cudaDeviceReset() at the end (in-process callers that share the context) */
-    GMP_HBM_F_LIB_BASELINES = 1u << 2 /* also time cudaMemsetAsync and cudaMemcpyAsync D2D on the same buffers */
+    GMP_HBM_F_LIB_BASELINES = 1u << 2, /* also time cudaMemsetAsync and cudaMemcpyAsync D2D on the same buffers */
+    /* Implies KEEP_DEVICE.  For a resident worker that probes the same GPU again and again (the churn of BASELINE
+     * configs[4]): the call leaves its stream, events, accumulators, the registered host staging buffer AND the two
+     * device buffers in place for the next call on that device, so that a call is the passes and one synchronisation
+     * (cudaMalloc/cudaFree of 2 x 8 GiB and the pinning of the staging buffer are 30 of the 36 ms of a cold call, and
+     * they serialise inside the driver when several GPUs are probed at once).  The memory stays allocated until
+     * gmp_probe_hbm_release() or a call on that device without this flag: a worker must release before it hands the GPU
+     * to the tenant. */
+    GMP_HBM_F_RETAIN      = 1u << 3
 };
 
 typedef struct gmp_hbm_result {
@@ -341,8 +350,9 @@ typedef struct gmp_hbm_result {
     uint64_t ns_context;         /* primary-context creation (cudaFree(0)) */
     uint64_t ns_alloc;
     uint64_t ns_first_kernel;    /* untimed first touch: write+verify of a 4 MiB prefix, launch to verified result */
-    uint64_t ns_kernels;         /* all timed passes */
-    uint64_t ns_dma;
+    uint64_t ns_kernels;         /* all timed passes: first launch to the passes' stream drained (ONE synchronisation) */
+    uint64_t ns_dma;             /* what the DMA round trip added after that; its set-up and transfers run on a second
+                                    stream beside the passes, so this is only the part they did not hide */
     uint64_t ns_teardown;
     uint64_t ns_total;
     uint64_t mono_first_verified_ns; /* absolute CLOCK_MONOTONIC time at which the first kernel result verified
@@ -350,10 +360,15 @@ typedef struct gmp_hbm_result {
     double   lib_memset_gbs;         /* same buffer through cudaMemsetAsync (bytes written / time), best of iters */
     double   lib_memcpy_gbs;         /* A -> B through cudaMemcpyAsync device-to-device (2N bytes / time), best of iters;
                                         both 0 unless GMP_HBM_F_LIB_BASELINES is set */
+    uint64_t mono_context_begin_ns;  /* absolute CLOCK_MONOTONIC around primary-context creation on this GPU: with one */
+    uint64_t mono_context_end_ns;    /* host thread per GPU (gmp_probe_all) the intervals show whether the driver overlaps them */
 } gmp_hbm_result;
 
 /* uuid == NULL or "" probes CUDA ordinal 0. */
 GMP_API int gmp_probe_hbm(const char* uuid, const gmp_hbm_opts* opts, gmp_hbm_result* out);
+/* Frees what GMP_HBM_F_RETAIN calls left on the device named by uuid (NULL or "": on every device).  GMP_OK also when
+ * nothing was retained.  No reference counterpart. */
+GMP_API int gmp_probe_hbm_release(const char* uuid);
 
 /* ------------------------------------------------------------------------- */
 /* 5. Peer-to-peer probe across the GPUs mounted into one pod                 */

@@ -1,8 +1,8 @@
 """The allocation-free verify entry point against the allocating one, through the C ABI (GPU box only).
 
 gmp_hbm_read_verify_noalloc exists for callers that cannot allocate device memory: a health-check sidecar on a GPU
-whose memory the tenant has filled, a monitor that must not cause cudaFree's device-wide synchronisation, code that
-runs while another thread is capturing a stream.  Its scratch is one fixed array inside the library that every call
+whose memory the tenant has filled, a monitor that must not cause cudaFree's device-wide synchronisation, a caller
+whose own rules forbid allocator calls at that point.  Its scratch is one fixed array inside the library that every call
 on a device shares, so this file checks the thing that sharing could break: two calls in a row, on different data,
 each have to agree bit for bit with gmp_hbm_read_verify on the same buffer.
 
@@ -13,6 +13,7 @@ assumption about what ran before it and passes alone in a fresh process as well.
 import pytest
 
 from gpumounter_b200 import ProbeError, _lib, probe
+from oracle import gmo_ctypes as gmo  # the checker
 
 pytestmark = pytest.mark.gpu
 
@@ -108,6 +109,73 @@ def test_survives_a_device_reset_done_by_the_library():
         "r = probe.probe_hbm(nbytes=64 << 20, iters=1, dma_bytes=0)   # resets the device at the end\n"
         "assert r.status == 0\n"
         "check((9 << 20) + 5, 2)\n"
+        "print('ok')\n" % root
+    )
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stdout[-1000:] + out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("pattern", range(probe.PAT_COUNT))
+def test_agrees_with_the_cpu_oracle(cuda, pattern):
+    """Pinned to oracle/gmo_pattern.c, not only to the sibling CUDA entry point: closed-form checksum of a clean buffer,
+    and the oracle's own verify pass over the bytes of a buffer with faults in three segments and in the ragged tail."""
+    torch = cuda
+    s = torch.cuda.current_stream().cuda_stream
+    n = (9 << 20) + 11
+    t = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    seed = t.data_ptr() if pattern == probe.PAT_ADDRESS else SEED + 3 * pattern
+    probe.hbm_write_pattern(t.data_ptr(), n, pattern, seed, s)
+    clean = probe.hbm_read_verify_noalloc(t.data_ptr(), n, pattern, seed, s)
+    assert clean.ok and (clean.xor64, clean.sum64) == gmo.pattern_checksum(n, pattern, seed)
+    for off in (17, (4 << 20) + 4321, (8 << 20) + 16, n - 2):
+        probe.hbm_corrupt(t.data_ptr(), n, off, 0x21, s)
+    got = probe.hbm_read_verify_noalloc(t.data_ptr(), n, pattern, seed, s)
+    want = gmo.pattern_verify(bytes(t[:n].cpu().numpy().tobytes()), pattern, seed)
+    assert as_tuple(got) == tuple(want)
+    assert got.mismatch_lanes == 4 and got.first_bad_lane == 1
+
+
+def test_after_one_call_no_pattern_allocates(cuda):
+    """The point of the entry point: after ONE call on the device (whatever its pattern) further calls - every pattern,
+    several sizes - leave the device's free memory exactly where it was: no lazily loaded kernel, no hidden scratch."""
+    torch = cuda
+    s = torch.cuda.current_stream().cuda_stream
+    n = (12 << 20) + 5
+    t = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    probe.hbm_write_pattern(t.data_ptr(), n, probe.PAT_ZERO, 0, s)
+    assert probe.hbm_read_verify_noalloc(t.data_ptr(), 0, probe.PAT_ZERO, 0, s).ok  # the first call; it launches nothing
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for pattern in range(probe.PAT_COUNT):
+        for size in (n, 1 << 20, 16):
+            probe.hbm_read_verify_noalloc(t.data_ptr(), size, pattern, SEED, s)
+            free, _ = torch.cuda.mem_get_info()
+            assert free == free0, (pattern, size, free0 - free)
+
+
+def test_survives_a_device_reset_done_by_the_caller():
+    """A cudaDeviceReset() of the CALLER's, which the library cannot see: the next call sets itself up again (the array's
+    address is looked up per call, nothing stale is kept).  In a child: the reset would orphan this process's torch pool."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from gpumounter_b200 import probe\n"
+        "from cuda.bindings import runtime as rt\n"
+        "def check(nbytes, seed):\n"
+        "    err, p = rt.cudaMalloc(nbytes); assert int(err) == 0, err\n"
+        "    p = int(p)\n"
+        "    probe.hbm_write_pattern(p, nbytes, 0, seed)\n"
+        "    a = probe.hbm_read_verify(p, nbytes, 0, seed); b = probe.hbm_read_verify_noalloc(p, nbytes, 0, seed)\n"
+        "    assert (a.mismatch_lanes, a.xor64, a.sum64) == (b.mismatch_lanes, b.xor64, b.sum64) == (0, a.xor64, a.sum64)\n"
+        "    assert int(rt.cudaFree(p)[0]) == 0\n"
+        "check((9 << 20) + 5, 1)\n"
+        "assert int(rt.cudaDeviceReset()[0]) == 0          # the caller's own reset\n"
+        "check((9 << 20) + 5, 2)\n"
+        "check((5 << 20) + 9, 3)\n"
         "print('ok')\n" % root
     )
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
