@@ -3,6 +3,7 @@ the reference, on a cluster-less target (own mount namespace + private /dev tmpf
 CPU only; needs root, unshare and nsenter (skipped otherwise)."""
 
 import os
+import subprocess
 
 import pytest
 
@@ -399,3 +400,45 @@ def test_in_pod_probe_is_killed_when_it_overruns_its_deadline(fake_nvml, tmp_pat
         assert not os.path.exists(f"/proc/{pid}") or open(f"/proc/{pid}/stat").read().split()[2] == "Z"   # killed, not left running
         rc, rep = util.ProbeInPod(product_pod(), [gpu], [], env, probe_exe=str(quick))     # a probe within the deadline is untouched
         assert rc == 0 and rep == {"status": 0}
+
+
+def test_pod_like_target_has_its_own_dev_and_only_mounted_gpus_open(fake_nvml):
+    """The stand-in the GPU runs use (tools/standin_pod.py, pod_like): tmpfs ON /dev of the target's mount namespace,
+    populated like a container started with NVIDIA_VISIBLE_DEVICES=none, in a real devices cgroup with a container's
+    whitelist.  With the reference's own names (dev_prefix unset: /dev/nvidia<N>) the mount lands in THAT /dev and
+    nowhere else, and the kernel lets exactly the mounted minors through."""
+    import errno
+
+    why = harness.can_run_pod_like()
+    if why:
+        pytest.skip(why)
+    gpus_cfg = fake_nvml()
+    t = harness.Target(pod_like=True).start()
+    try:
+        env = MountEnv(devices_root=t.devices_root, cgroup_driver="cgroupfs")
+        assert {"null", "zero", "urandom", "tty", "nvidiactl"} <= set(t.nodes()) and t.gpu_nodes() == []
+        recs = [device.New(m, u) for u, m, _ in gpus_cfg[:3]]
+        minors = [m for _, m, _ in gpus_cfg[:3]]
+        other = next(m for m in range(8) if m not in minors)
+        before_host = sorted(x for x in os.listdir("/dev") if x.startswith("nvidia"))
+        assert util.MountGPUs(product_pod(), recs, env) == 3
+        assert t.gpu_nodes() == sorted(f"nvidia{m}" for m in minors)
+        assert sorted(x for x in os.listdir("/dev") if x.startswith("nvidia")) == before_host  # the host's /dev is untouched
+        for m in minors:
+            assert t.node(m) == (195, m, 0o666)
+            assert t.try_open(m) in (errno.ENXIO, errno.ENODEV)  # through the filter; no driver behind it on this box
+        os.mknod(t.node_path_in_target(other), 0o666 | 0o020000, os.makedev(195, other))
+        assert t.try_open(other) == errno.EPERM                   # a node alone opens nothing
+        os.unlink(t.node_path_in_target(other))
+        # a process started the way the pod's own processes are sees the pod's /dev and sits in the pod's cgroup
+        p = t.spawn_in_pod(["sh", "-c", "ls /dev; grep devices /proc/self/cgroup"], stdout=subprocess.PIPE, text=True)
+        out = p.communicate(timeout=30)[0]
+        assert all(f"nvidia{m}" in out.split() for m in minors) and t.cgroup_path in out
+        assert util.UnmountGPUs(product_pod(), recs, False, env) == 3
+        assert t.gpu_nodes() == [] and "195:%d" % minors[0] not in t.read("devices.list")
+        rc, _ = util.VerifyGoneInPod(product_pod(), recs, env, raise_on_error=False)
+        assert rc == 0
+    finally:
+        with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+            f.write(f"{t.pid}\n")
+        t.stop()
