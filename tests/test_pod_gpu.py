@@ -25,11 +25,14 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture
-def pod_target():
+def pod_target(monkeypatch):
     why = harness.can_run_pod_like()
     if why:
         pytest.skip(why)
-    assert "CUDA_VISIBLE_DEVICES" not in os.environ, "these tests prove the device cgroup gates CUDA, not the environment"
+    # these tests prove that the device cgroup and the pod's /dev gate CUDA, not the environment: whatever the box's
+    # launcher exported must not reach the processes started in the pod (they inherit this process's environment)
+    monkeypatch.delenv("CUDA_VISIBLE_DEVICES", raising=False)
+    monkeypatch.delenv("NVIDIA_VISIBLE_DEVICES", raising=False)
     t = harness.Target(pod_like=True).start()
     try:
         yield t

@@ -130,7 +130,7 @@ def test_agrees_with_the_cpu_oracle(cuda, pattern):
     for off in (17, (4 << 20) + 4321, (8 << 20) + 16, n - 2):
         probe.hbm_corrupt(t.data_ptr(), n, off, 0x21, s)
     got = probe.hbm_read_verify_noalloc(t.data_ptr(), n, pattern, seed, s)
-    want = gmo.pattern_verify(bytes(t[:n].cpu().numpy().tobytes()), pattern, seed)
+    want = gmo.pattern_verify(bytearray(t[:n].cpu().numpy().tobytes()), pattern, seed)
     assert as_tuple(got) == tuple(want)
     assert got.mismatch_lanes == 4 and got.first_bad_lane == 1
 

@@ -221,12 +221,16 @@ class GpuTarget:
         return [] if self.pod_like else ["--dev-dir", self.t.devdir]
 
     def restrict_cuda(self, gpus):
+        """pod-like: NOTHING may restrict CUDA through the environment the in-pod probe inherits (a box's launcher often
+        exports CUDA_VISIBLE_DEVICES); scratch: the environment is the only restriction there is."""
+        self.saved_env = os.environ.pop("CUDA_VISIBLE_DEVICES", None)
         if not self.pod_like:
             os.environ["CUDA_VISIBLE_DEVICES"] = ",".join(u for u, _ in gpus)
 
     def unrestrict_cuda(self):
-        if not self.pod_like:
-            os.environ.pop("CUDA_VISIBLE_DEVICES", None)
+        os.environ.pop("CUDA_VISIBLE_DEVICES", None)
+        if getattr(self, "saved_env", None) is not None:
+            os.environ["CUDA_VISIBLE_DEVICES"] = self.saved_env
 
 
 def mounted_set(n_gpus):

@@ -9,3 +9,4 @@ echo "== self cgroup (devices)"; grep devices /proc/self/cgroup; cat /sys/fs/cgr
 echo "== pid namespace"; readlink /proc/self/ns/pid /proc/1/ns/pid; echo "pid of this shell: $$"
 echo "== nvidia-smi"; nvidia-smi -L; nvidia-smi --query-gpu=index,uuid,pci.bus_id,persistence_mode --format=csv,noheader
 echo "== which"; for t in nvidia-smi nvidia-modprobe strace go; do printf "%s: " $t; command -v $t || echo absent; done
+echo "== env"; env | grep -E "CUDA|NVIDIA_VIS"
