@@ -451,7 +451,7 @@ def main():
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
             line["roofline"]["traffic"] = json.load(f).get("k_hbm_copy_dram_bytes_per_launch")
         line["roofline"]["traffic_source"] = ("profiles/ncu_traffic.json (one `ncu --set full` capture of this kernel, "
-                                              "profiles/r01_ncu_summary.md) - a citation, not measured in this run")
+                                              "profiles/r02_ncu_summary.md) - a citation, not measured in this run")
     except Exception:
         pass
     if noalloc_ms:

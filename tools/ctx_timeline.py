@@ -26,14 +26,15 @@ from tools import mount_latency as ml  # noqa: E402
 PROBE_ARGS = ["--bytes", "256M", "--iters", "1", "--dma-bytes", "1M", "--skip-p2p"]
 
 
-def child_cgroup(t, idx, minor):
+def child_cgroup(t, idx, minor, all_minors):
+    """Created AFTER the mount: a v1 devices child starts with its parent's list (the mounted GPUs included) and may
+    only be narrowed - here down to one GPU."""
     d = os.path.join(t.cgroup_dir, f"gmp-fan-{idx}")
     os.mkdir(d)
-    with open(os.path.join(d, "devices.deny"), "w") as f:
-        f.write("c 195:* rw")
-    for line in (f"c 195:{minor} rw", "c 195:255 rw"):
-        with open(os.path.join(d, "devices.allow"), "w") as f:
-            f.write(line)
+    for other in all_minors:
+        if other != minor:
+            with open(os.path.join(d, "devices.deny"), "w") as f:
+                f.write(f"c 195:{other} rw")
     return d
 
 
@@ -50,10 +51,11 @@ def fanout_once(g, gpus):
     recs = [device.New(m, u) for u, m in gpus]
     pod, env = ml.product_pod(), g.env()
     exe = probe.probe_executable()
-    dirs = [child_cgroup(t, i, m) for i, (_, m) in enumerate(gpus)]
+    dirs = []
     try:
         t0 = time.monotonic_ns()
         util.MountGPUs(pod, recs, env)
+        dirs = [child_cgroup(t, i, m, [mm for _, mm in gpus]) for i, (_, m) in enumerate(gpus)]
         procs = []
         for d, (u, m) in zip(dirs, gpus):
             argv = [sys.executable, "-c", BOOT, os.path.join(d, "cgroup.procs"), f"/proc/{t.pid}/ns/mnt", exe,
