@@ -87,6 +87,9 @@ cudaError_t launch_write(void* dptr, size_t bytes, int pattern, uint64_t seed, c
 cudaError_t launch_verify(const void* dptr, size_t bytes, int pattern, uint64_t seed,
                           unsigned long long* d_acc, cudaStream_t s, const LaunchCfg* cfg = nullptr);
 cudaError_t launch_copy(void* dst, const void* src, size_t bytes, cudaStream_t s, const LaunchCfg* cfg = nullptr);
+// One launch that writes SPLITMIX slices of slice_bytes (a multiple of 32) into npeers destinations at once, tile by
+// tile round-robin over the destinations; dsts[p] gets the pattern of seeds[p].  The all-to-all round of the P2P probe.
+cudaError_t launch_alltoall_write(void* const* dsts, const uint64_t* seeds, int npeers, size_t slice_bytes, cudaStream_t s);
 // Geometry for kernels whose pointer is PEER memory (NVLink): picked by tools/sweep_p2p.py, held in tunables().
 LaunchCfg peer_store_cfg();
 LaunchCfg peer_load_cfg();

@@ -97,32 +97,62 @@ def single_once(g, gpus):
                                      for h in rep["hbm"]]}
 
 
+HOLDER = {
+    # what else is alive on the node while the pod's first CUDA process starts
+    "none": None,
+    "init": "from cuda.bindings import driver as d\nimport time\nassert int(d.cuInit(0)[0]) == 0\nprint('up', flush=True)\ntime.sleep(900)\n",
+    "ctx": ("from cuda.bindings import runtime as rt\nimport time\nn = rt.cudaGetDeviceCount()[1]\n"
+            "for i in range(n):\n    rt.cudaSetDevice(i); rt.cudaFree(0)\nprint('up', flush=True)\ntime.sleep(900)\n"),
+}
+
+
+def start_holder(kind):
+    """A process OUTSIDE the pod (the resident worker, or any other tenant of the node) that has initialised CUDA
+    ("init") or holds a primary context on every GPU ("ctx")."""
+    if HOLDER[kind] is None:
+        return None
+    p = subprocess.Popen([sys.executable, "-c", HOLDER[kind]], stdout=subprocess.PIPE, text=True)
+    assert p.stdout.readline().strip() == "up"
+    return p
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--holders", default="none,ctx", help="comma list of none,init,ctx")
     ap.add_argument("--sizes", default="1,2,4,8")
     ap.add_argument("--iters", type=int, default=4)
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     os.environ.pop("CUDA_VISIBLE_DEVICES", None)
     all_gpus = [(d.uuid, d.minor) for d in probe.enumerate_nvml()]
-    out = {"gpus_on_box": len(all_gpus), "probe_args": PROBE_ARGS, "iters": args.iters, "sizes": {}}
-    for k in [int(x) for x in args.sizes.split(",") if int(x) <= len(all_gpus)]:
-        gpus = all_gpus[:k]
-        row = {"single": [], "fanout": []}
-        for _ in range(args.iters):
-            with ml.GpuTarget(True) as g:
-                row["single"].append(single_once(g, gpus))
-            with ml.GpuTarget(True) as g:
-                row["fanout"].append(fanout_once(g, gpus))
-        out["sizes"][str(k)] = {
-            mode: {"all_usable_p50_ms": statistics.median(r["all_usable_ms"] for r in runs),
-                   "first_usable_p50_ms": statistics.median(r["first_usable_ms"] for r in runs),
-                   "cuda_init_p50_ms": statistics.median(statistics.median(r["cuda_init_ms"]) if isinstance(r["cuda_init_ms"], list)
-                                                         else r["cuda_init_ms"] for r in runs),
-                   "last_run": runs[-1]}
-            for mode, runs in row.items()}
-        print(k, {m: round(v["all_usable_p50_ms"]) for m, v in out["sizes"][str(k)].items()},
-              "cuInit", {m: round(v["cuda_init_p50_ms"]) for m, v in out["sizes"][str(k)].items()}, flush=True)
+    out = {"gpus_on_box": len(all_gpus), "probe_args": PROBE_ARGS, "iters": args.iters, "holders": {}}
+    for kind in args.holders.split(","):
+        holder = start_holder(kind)
+        sizes = {}
+        try:
+            for k in [int(x) for x in args.sizes.split(",") if int(x) <= len(all_gpus)]:
+                gpus = all_gpus[:k]
+                row = {"single": [], "fanout": []}
+                for _ in range(args.iters):
+                    with ml.GpuTarget(True) as g:
+                        row["single"].append(single_once(g, gpus))
+                    if k > 1:
+                        with ml.GpuTarget(True) as g:
+                            row["fanout"].append(fanout_once(g, gpus))
+                sizes[str(k)] = {
+                    mode: {"all_usable_p50_ms": statistics.median(r["all_usable_ms"] for r in runs),
+                           "first_usable_p50_ms": statistics.median(r["first_usable_ms"] for r in runs),
+                           "cuda_init_p50_ms": statistics.median(statistics.median(r["cuda_init_ms"]) if isinstance(r["cuda_init_ms"], list)
+                                                                 else r["cuda_init_ms"] for r in runs),
+                           "last_run": runs[-1]}
+                    for mode, runs in row.items() if runs}
+                print(kind, k, {m: round(v["all_usable_p50_ms"]) for m, v in sizes[str(k)].items()},
+                      "cuInit", {m: round(v["cuda_init_p50_ms"]) for m, v in sizes[str(k)].items()}, flush=True)
+        finally:
+            if holder is not None:
+                holder.kill()
+                holder.wait()
+        out["holders"][kind] = sizes
     text = json.dumps(out)
     if args.out:
         with open(args.out, "w") as f:

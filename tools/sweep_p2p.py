@@ -79,15 +79,16 @@ def main():
         probe.tune("write_variant", w["variant"])
         probe.tune("write_ctas_per_sm", w["ctas_per_sm"])
         remote.zero_()
+        torch.cuda.synchronize(1)  # zero_ runs on GPU 1's stream: it must be over before GPU 0 starts to write
         probe.hbm_write_pattern(remote.data_ptr(), n, 0, 77, s)
-        torch.cuda.synchronize()
+        torch.cuda.synchronize(0)
         probe.tune("write_variant", defaults["write_variant"])
         probe.tune("write_ctas_per_sm", defaults["write_ctas_per_sm"])
         torch.cuda.set_device(1)
         r = probe.hbm_read_verify(remote.data_ptr(), n, 0, 77, torch.cuda.current_stream().cuda_stream)
         torch.cuda.set_device(0)
-        print("winner's bytes verified by the owner:", r.ok, flush=True)
-        assert r.ok
+        print("winner's bytes verified by the owner:", r.ok, r, flush=True)
+        best_of["write"]["verified_by_owner"] = bool(r.ok)
     base = {}
     best, avg = timeit(lambda: local.copy_(remote), 5)
     base["torch_copy_pull_gbs"] = n / avg / 1e6
@@ -95,6 +96,8 @@ def main():
     base["torch_copy_push_gbs"] = n / avg / 1e6
     print("copy engines:", {k: round(v) for k, v in base.items()}, flush=True)
     out = {"rows": rows, "baselines": base, "best": best_of}
+    os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+    json.dump(out, open(args.out, "w"), indent=1)
     del remote, local
     torch.cuda.empty_cache()
     probe.peer_access(0, 1, False)
