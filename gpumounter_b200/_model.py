@@ -32,7 +32,7 @@ class gmp_mount_env(ctypes.Structure):
                 ("cgroup2_root", ctypes.c_char_p), ("extensions", ctypes.c_uint32), ("probe_timeout_ms", ctypes.c_uint32)]
 
 
-EXT_CRI_RUNTIMES, EXT_CGROUP_V2 = 1, 2  # GMP_EXT_*: off by default (section 7 of the header)
+EXT_CRI_RUNTIMES, EXT_CGROUP_V2, EXT_PROBE_KEEP_PRIVILEGES = 1, 2, 4  # GMP_EXT_*: off by default (section 7 of the header)
 
 
 class gmp_ns_config(ctypes.Structure):

@@ -743,7 +743,13 @@ enum {
     GMP_EXT_CRI_RUNTIMES = 1u << 0,
     /* Unified hierarchy: the pod's cgroup lives under gmp_mount_env.cgroup2_root ("/sys/fs/cgroup") and device
      * access is decided by BPF_PROG_TYPE_CGROUP_DEVICE programs, not devices.allow / devices.deny files. */
-    GMP_EXT_CGROUP_V2    = 1u << 1
+    GMP_EXT_CGROUP_V2    = 1u << 1,
+    /* gmp_probe_in_pod: run the probe with the WORKER's credentials (root, every capability), as round 1 did.  Off by
+     * default: the probe then runs as the user and group of the pod's first process, with an empty capability bounding,
+     * permitted and effective set, no_new_privs set, and in the pod's net / ipc / uts namespaces as well as its mount
+     * namespace - what it loads from the pod's root (ld.so, libc, libcuda.so.1) is the tenant's to choose, so it must
+     * not run with more than the tenant already has. */
+    GMP_EXT_PROBE_KEEP_PRIVILEGES = 1u << 2
 };
 
 /* Which hierarchy decides device access on this node: *version = 1 when <devices_root> (default

@@ -4,6 +4,7 @@ CPU only; needs root, unshare and nsenter (skipped otherwise)."""
 
 import os
 import subprocess
+import time
 
 import pytest
 
@@ -442,3 +443,58 @@ def test_pod_like_target_has_its_own_dev_and_only_mounted_gpus_open(fake_nvml):
         with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
             f.write(f"{t.pid}\n")
         t.stop()
+
+
+def test_in_pod_probe_runs_with_the_pod_users_identity_and_no_capabilities(fake_nvml, tmp_path):
+    """What gmp_probe_in_pod execs resolves its loader and libraries from the POD's root, so it must not hold more than the
+    tenant does: identity of the pod's first process, empty capability sets (bounding included), no_new_privs - and the
+    worker that spawned it keeps all of its own.  GMP_EXT_PROBE_KEEP_PRIVILEGES is the explicit opt-out."""
+    from gpumounter_b200._model import EXT_PROBE_KEEP_PRIVILEGES, MountEnv as Env
+
+    fake_nvml()
+    fake_probe = tmp_path / "who-am-i"
+    fake_probe.write_text("#!/bin/sh\n"
+                          "s() { grep \"^$1:\" /proc/self/status | tr -s '\\t ' ' ' | cut -d' ' -f2; }\n"
+                          "printf '{\"status\":0,\"uid\":%s,\"gid\":%s,\"eff\":\"%s\",\"prm\":\"%s\",\"bnd\":\"%s\",\"nnp\":%s,\"groups\":\"%s\"}\\n' "
+                          "\"$(s Uid)\" \"$(s Gid)\" \"$(s CapEff)\" \"$(s CapPrm)\" \"$(s CapBnd)\" \"$(s NoNewPrivs)\" "
+                          "\"$(grep '^Groups:' /proc/self/status | cut -f2- | tr -d '\\n')\"\n")
+    fake_probe.chmod(0o755)
+
+    def caps_of_self():
+        return {k: v for k, v in (line.split(":\t") for line in open("/proc/self/status").read().splitlines()
+                                  if line.startswith(("CapEff", "CapPrm", "CapBnd", "Uid", "NoNewPrivs")))}
+
+    mine = caps_of_self()
+    with harness.Target() as t:
+        gpus = [device.New(3, FAKE_UUIDS[0])]
+        util.MountGPUs(product_pod(), gpus, env_of(t))
+        # a pod whose first process runs as an ordinary user: the probe runs as that user
+        member = subprocess.Popen(["setpriv", "--reuid", "12345", "--regid", "23456", "--clear-groups", "sleep", "600"])
+        try:
+            with open(os.path.join(t.cgroup_dir, "cgroup.procs"), "w") as f:  # scratch cgroup file: make it the FIRST pid
+                f.write(f"{member.pid}\n{t.pid}\n")
+            for _ in range(100):  # setpriv has exec'ed sleep once the uid shows
+                if f"Uid:\t12345" in open(f"/proc/{member.pid}/status").read():
+                    break
+                time.sleep(0.01)
+            rc, rep = util.ProbeInPod(product_pod(), gpus, [], env_of(t), probe_exe=str(fake_probe))
+            assert rc == 0
+            assert (rep["uid"], rep["gid"], rep["groups"].strip()) == (12345, 23456, "")
+            assert int(rep["eff"], 16) == int(rep["prm"], 16) == int(rep["bnd"], 16) == 0 and rep["nnp"] == 1
+        finally:
+            member.kill()
+            member.wait()
+        # first process is root (the usual container): still root by name, but without a single capability
+        with open(os.path.join(t.cgroup_dir, "cgroup.procs"), "w") as f:
+            f.write(f"{t.pid}\n")
+        rc, rep = util.ProbeInPod(product_pod(), gpus, [], env_of(t), probe_exe=str(fake_probe))
+        assert rc == 0 and rep["uid"] == 0
+        assert int(rep["eff"], 16) == int(rep["prm"], 16) == int(rep["bnd"], 16) == 0 and rep["nnp"] == 1
+        # the worker itself is untouched by what its helper did to itself (raw system calls, not glibc's setxid broadcast)
+        assert caps_of_self() == mine
+        # opt-out: round 1's behaviour
+        e = env_of(t)
+        keep = Env(devices_root=e.devices_root, dev_prefix=e.dev_prefix, cgroup_driver=e.cgroup_driver,
+                   extensions=EXT_PROBE_KEEP_PRIVILEGES)
+        rc, rep = util.ProbeInPod(product_pod(), gpus, [], keep, probe_exe=str(fake_probe))
+        assert rc == 0 and int(rep["eff"], 16) == int(mine["CapEff"], 16) and rep["nnp"] == 0

@@ -46,7 +46,9 @@ BOOT = ("import os, sys\n"
         "os.execv(sys.argv[3], sys.argv[3:])\n")
 
 
-def fanout_once(g, gpus):
+def fanout_once(g, gpus, narrow=True):
+    """narrow: each process in a child cgroup that opens only its own GPU; else every process sees all k mounted GPUs
+    (cuInit attaches all of them) and is told which one to probe (--host-view: more visible than named is fine)."""
     t = g.t
     recs = [device.New(m, u) for u, m in gpus]
     pod, env = ml.product_pod(), g.env()
@@ -55,11 +57,13 @@ def fanout_once(g, gpus):
     try:
         t0 = time.monotonic_ns()
         util.MountGPUs(pod, recs, env)
-        dirs = [child_cgroup(t, i, m, [mm for _, mm in gpus]) for i, (_, m) in enumerate(gpus)]
+        if narrow:
+            dirs = [child_cgroup(t, i, m, [mm for _, mm in gpus]) for i, (_, m) in enumerate(gpus)]
         procs = []
-        for d, (u, m) in zip(dirs, gpus):
+        for i, (u, m) in enumerate(gpus):
+            d = dirs[i] if narrow else t.cgroup_dir
             argv = [sys.executable, "-c", BOOT, os.path.join(d, "cgroup.procs"), f"/proc/{t.pid}/ns/mnt", exe,
-                    "--uuid", f"{u}:{m}"] + PROBE_ARGS
+                    "--uuid", f"{u}:{m}"] + PROBE_ARGS + ([] if narrow else ["--host-view"])
             procs.append(subprocess.Popen(argv, stdout=subprocess.PIPE, text=True))
         reps = [json.loads(p.communicate(timeout=120)[0].strip().splitlines()[-1]) for p in procs]
         util.UnmountGPUs(pod, recs, False, env)
@@ -132,13 +136,15 @@ def main():
         try:
             for k in [int(x) for x in args.sizes.split(",") if int(x) <= len(all_gpus)]:
                 gpus = all_gpus[:k]
-                row = {"single": [], "fanout": []}
+                row = {"single": [], "fanout": [], "fanout_shared": []}
                 for _ in range(args.iters):
                     with ml.GpuTarget(True) as g:
                         row["single"].append(single_once(g, gpus))
                     if k > 1:
                         with ml.GpuTarget(True) as g:
                             row["fanout"].append(fanout_once(g, gpus))
+                        with ml.GpuTarget(True) as g:
+                            row["fanout_shared"].append(fanout_once(g, gpus, narrow=False))
                 sizes[str(k)] = {
                     mode: {"all_usable_p50_ms": statistics.median(r["all_usable_ms"] for r in runs),
                            "first_usable_p50_ms": statistics.median(r["first_usable_ms"] for r in runs),
