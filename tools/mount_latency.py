@@ -383,7 +383,9 @@ def churn_real(rounds, hbm_bytes=256 << 20, nodes_only=False, pod_like=None):
     free0 = device_free_bytes()
     fds0 = open_fds()
     usable_s, gone_s, steps = [], [], 0
-    with GpuTarget(pod_like) as g:
+    # a resident worker keeps NVML attached (gmp_nvml_hold): the busy check of every unmount is then a query, not a
+    # cold nvmlInit_v2 (~140 ms on an 8-GPU host)
+    with GpuTarget(pod_like) as g, util.NvmlAttached():
         t = g.t
         pod, env = product_pod(), g.env()
         devices_list0 = t.read("devices.list")
