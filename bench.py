@@ -203,7 +203,8 @@ def p2p_section(uuids, bytes_per_pair: int, iters: int):
             return {"ok": False, "unavailable": f"probe exit {r.returncode}: {rep.get('detail')}"}
         out = ml.p2p_summary(rep["p2p"])
         out.update(iters=iters, status=rep["status"], detail=rep.get("detail", ""), ms_total=rep["p2p"]["ms_total"],
-                   store_kernel="k_hbm_write_pattern_bulk (pattern staged in shared memory, pushed by the bulk-copy engine)",
+                   store_kernel="k_hbm_write_pattern on a peer pointer (32-byte vector stores; 713 GB/s is the fabric's ceiling for "
+                                "128-byte write requests, profiles/r02_p2p_ncu.md); all-to-all: k_peer_alltoall_write, one launch per sender",
                    nvlink5_nominal_gbs_per_direction=900.0)
         out["ok"] = bool(rep["status"] == 0 and out["matrix_match_nvml"] and out["mismatch_lanes"] == 0)
         return out

@@ -1,27 +1,24 @@
 #!/bin/bash
-# One call on an N-GPU box: topology, P2P tests, cold probe of all GPUs, the scaling bench at 1/2/4/N, mount-to-usable.
-N=${1:-8}
+# The 8-GPU call of round 2 (charged x8: keep it short).  Order: what can fail first.
+#   gpurun --gpus 8 --timeout 900 -- 'bash tools/run_8gpu.sh'
 mkdir -p gpurun_out
+N=$(nvidia-smi -L | wc -l)
 nvidia-smi topo -m > gpurun_out/topo_${N}gpu.txt 2>&1
-python -m pytest tests/test_probe_gpu.py -m gpu -x -q 2>&1 | tail -4
-python tools/time_probe.py --bytes 1G --iters 1 --dma-bytes 16M --p2p-bytes 1G --p2p-iters 2 --lib-baselines > gpurun_out/probe_${N}gpu.json
-python -c "
-import json; d=json.load(open('gpurun_out/probe_${N}gpu.json')); print({k:d[k] for k in ('wall_s','status','n_gpus','ms')}); p=d.get('p2p',{});
-print('match',p.get('matrix_match'),'alltoall',p.get('alltoall_gbs'),'bidir',p.get('bidir_gbs'),'links',p.get('nvlink_active'))
-for row in p.get('write_gbs',[]): print('W',[round(x) for x in row])
-for row in p.get('read_gbs',[]): print('R',[round(x) for x in row])
-for row in p.get('memcpy_peer_gbs',[]): print('M',[round(x) for x in row])
-"
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 tools/nccl_crosscheck.py 2>/dev/null | tail -1 | tee gpurun_out/nccl_${N}gpu.json
-for g in 1 2 4 $N; do
-  [ $g -gt $N ] && continue
-  if [ $g -eq 1 ]; then
-    python bench.py --steps 10 --warmup 3 --mount-iters 12 2>gpurun_out/scale_${g}.err | tail -1 > gpurun_out/scale_${g}.json
-  else
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 2951$g bench.py --gpus $g --steps 10 --warmup 3 --mount-iters 12 2>gpurun_out/scale_${g}.err | tail -1 > gpurun_out/scale_${g}.json
-  fi
-  python -c "
-import json; d=json.load(open('gpurun_out/scale_${g}.json')); m=d.get('mount',{}); u=m.get('mount_to_usable',{})
-print('N=${g}', 'value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms/call', round(d['e2e']['ms_per_call'],1), 'mount ref/native p50 ms', m.get('reference_fork_exec_mount_ms',{}).get('p50'), m.get('native_mount_ms',{}).get('p50'), 'to-usable p50/p99 s', u.get('p50_s'), u.get('p99_s'), 'p2p', json.dumps(u.get('p2p'))[:400], m.get('unavailable'))
-"
-done
+timeout 200 python tools/ctx_timeline.py --holders init --sizes 4,8 --iters 3 --out gpurun_out/ctx_timeline_${N}gpu.json | head -4
+timeout 300 python -m pytest tests -m gpu -q -rs -k "p2p or pod or nvml" > gpurun_out/pytest_gpu_${N}.log 2>&1; tail -5 gpurun_out/pytest_gpu_${N}.log
+timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 10 --warmup 3 --mount-iters 6 2> gpurun_out/bench${N}.err | tail -1 > gpurun_out/bench_${N}gpu.json; echo "bench rc=${PIPESTATUS[0]}"
+python - <<PY
+import json
+try:
+    d = json.load(open("gpurun_out/bench_${N}gpu.json"))
+    print("value", round(d["value"]), "e2e", round(d["e2e"]["value"]), "ms/call", round(d["e2e"]["ms_per_call"], 2), "cold", round(d["e2e"]["cold_call"]["ms_per_call"], 2))
+    p = d.get("p2p", {})
+    print("p2p ok", p.get("ok"), {k: p.get(k) for k in ("store_gbs", "load_gbs", "memcpy_peer_gbs", "bidir_gbs_per_gpu_min", "alltoall_gbs_per_gpu", "matrix_match_nvml", "mismatch_lanes", "unavailable")})
+    m = d.get("mount", {}); u = m.get("mount_to_usable", {})
+    print("mount_ok", d.get("mount_ok"), m.get("unavailable"), "cold in-pod", u.get("target"), "p50", u.get("p50_s"), "first", u.get("first_gpu_usable_p50_s"), u.get("median_phases_ms"))
+    print("timeline", u.get("context_timeline_last_ms"))
+    r = m.get("mount_to_usable_resident_worker", {}); print("resident", r.get("p50_s"), r.get("median_phases_ms"))
+except Exception as e:
+    print("bench summary failed:", e); print(open("gpurun_out/bench${N}.err").read()[-3000:])
+PY
+timeout 300 python tools/mount_latency.py --skip-mount-bench --churn-rounds 0 --churn-real-rounds 3 --churn-nodes-rounds 100 --out gpurun_out/churn_real_${N}gpu.json > gpurun_out/churn.log 2>&1; tail -c 1800 gpurun_out/churn.log
