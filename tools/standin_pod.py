@@ -231,6 +231,12 @@ class Target:
                 p.wait(timeout=5)
             except Exception:
                 pass
+            for pipe in (p.stdin, p.stdout, p.stderr):  # or the descriptors live on until the Popen object is collected
+                try:
+                    if pipe is not None:
+                        pipe.close()
+                except Exception:
+                    pass
         if self.real_cgroup:
             self._remove_cgroup_dirs()
         shutil.rmtree(self.base, ignore_errors=True)
