@@ -172,7 +172,11 @@ def mount_section(n_gpus: int, iters: int):
                "native_mount_ms": {"p50": nat_m["p50_ms"], "p99": nat_m["p99_ms"]},
                "note": "slave-pod scheduling (ref: allocator.go:40-99) needs a cluster and is not included"}
         # cold: a fresh process in the pod starts CUDA on the mounted GPUs (what the tenant's first CUDA call pays too)
-        out["mount_to_usable"] = ml.to_usable(iters, 1 << 30, n_gpus)
+        # (gmp_probe_in_pod_fanout from 2 GPUs on: one probe process per GPU, each confined to its GPU; beside it the
+        # single-process probe, which is also what a tenant's own multi-GPU process pays)
+        out["mount_to_usable"] = ml.to_usable(iters, 1 << 30, n_gpus, fanout=n_gpus >= 2)
+        if n_gpus >= 2:
+            out["mount_to_usable_single_process"] = ml.to_usable(max(3, iters // 2), 1 << 30, n_gpus)
         # the two-stage hook of a resident worker (this process: cuInit and contexts already paid).  Contexts are kept
         # and peer access is left alone: the process still belongs to torch.  Kernels run from the HOST view.
         out["mount_to_usable_resident_worker"] = ml.to_usable_resident(iters, 1 << 30, n_gpus, keep_contexts=True,

@@ -1458,6 +1458,158 @@ extern "C" int gmp_verify_gone_in_pod(const gmp_mount_env* env, const gmp_pod* p
 // worker's namespace, (2) writes itself into the target's device cgroup, (3) setns()es into the target's
 // mount namespace and (4) fexecve()s the already open binary: libcuda.so.1 / libnvidia-ml.so.1 then resolve
 // from the pod's own root, the device nodes are the pod's, and the cgroup verdict is the pod's.
+namespace {
+
+// Where and as whom probe processes for one pod are started: resolved once per call.
+struct PodContext {
+    std::string cgroup_path, cgroup_dir, ns_path;
+    int target = 0;
+    int drop = 0;
+    unsigned uid = 0, gid = 0;
+    std::string extra_ns[3];
+};
+
+int resolve_pod_context(const gmp_mount_env* env, const gmp_pod* pod, PodContext* ctx) {
+    int rc = pod_cgroup_path(env, pod, &ctx->cgroup_path);
+    if (rc != GMP_OK) return rc;
+    std::vector<std::string> pids;
+    rc = read_cgroup_pids(env, ctx->cgroup_path, &pids);
+    if (rc != GMP_OK) return rc;
+    rc = first_pid(pids, &ctx->target);
+    if (rc != GMP_OK) return rc;
+    ctx->ns_path = proc_root(env) + "/" + std::to_string(ctx->target) + "/ns/mnt";
+    ctx->cgroup_dir = devices_root(env) + ctx->cgroup_path;
+    if (!extension_on(env, GMP_EXT_PROBE_KEEP_PRIVILEGES)) {
+        ctx->drop = 1;
+        if (!identity_of(proc_root(env), ctx->target, &ctx->uid, &ctx->gid)) {
+            set_error("in-pod probe: cannot read the identity of pid %d", ctx->target);
+            return GMP_ERR_SYS;
+        }
+        static const char* const names[3] = {"net", "ipc", "uts"};
+        for (int k = 0; k < 3; ++k) ctx->extra_ns[k] = foreign_ns(proc_root(env), ctx->target, names[k]);
+    }
+    return GMP_OK;
+}
+
+struct ProbeChild {
+    pid_t pid = -1;
+    int fd = -1;  // read end of the child's stdout
+    std::string output;
+    int wait_status = 0;
+};
+
+// Starts one probe process: member of the device cgroup whose cgroup.procs is `procs_file`, inside the pod's namespaces.
+int spawn_probe(const PodContext& ctx, const std::string& procs_file, const char* probe_exe, std::vector<std::string>& args,
+                ProbeChild* child) {
+    std::vector<char*> argv;
+    for (std::string& a : args) argv.push_back(&a[0]);
+    argv.push_back(nullptr);
+    int out_pipe[2];
+    if (pipe2(out_pipe, O_CLOEXEC) != 0) {
+        set_error("pipe2: %s", strerror(errno));
+        return GMP_ERR_SYS;
+    }
+    HelperStack stack;
+    ProbeHelperArgs hargs = {probe_exe, ctx.ns_path.c_str(), procs_file.c_str(), argv.data(), out_pipe[1], ctx.drop,
+                             {nullptr, nullptr, nullptr}, ctx.uid, ctx.gid};
+    for (int k = 0; k < 3; ++k) hargs.extra_ns[k] = ctx.extra_ns[k].empty() ? nullptr : ctx.extra_ns[k].c_str();
+    const pid_t pid = spawn_helper(probe_helper_main, &hargs, stack);  // returns once the child has exec'ed or exited
+    const int saved = errno;
+    close(out_pipe[1]);
+    if (pid < 0) {
+        set_error("clone: %s", strerror(saved));
+        close(out_pipe[0]);
+        return GMP_ERR_SYS;
+    }
+    child->pid = pid;
+    child->fd = out_pipe[0];
+    return GMP_OK;
+}
+
+// Reads every child's stdout to EOF (a pipe's write end closes when its probe exits), kills all of them when
+// timeout_ms (0 = none) runs out, reaps them.  *timed_out says which way it ended.
+void collect_probes(std::vector<ProbeChild>& kids, uint32_t timeout_ms, bool* timed_out) {
+    *timed_out = false;
+    struct timespec t0;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    size_t open_pipes = 0;
+    for (const ProbeChild& k : kids)
+        if (k.fd >= 0) ++open_pipes;
+    char tmp[4096];
+    while (open_pipes > 0) {
+        int wait_ms = -1;
+        if (timeout_ms != 0) {
+            struct timespec now;
+            clock_gettime(CLOCK_MONOTONIC, &now);
+            const long long elapsed = (now.tv_sec - t0.tv_sec) * 1000ll + (now.tv_nsec - t0.tv_nsec) / 1000000ll;
+            if (elapsed >= (long long)timeout_ms) {
+                *timed_out = true;
+                break;
+            }
+            wait_ms = (int)((long long)timeout_ms - elapsed);
+        }
+        std::vector<struct pollfd> pf;
+        std::vector<size_t> who;
+        for (size_t i = 0; i < kids.size(); ++i)
+            if (kids[i].fd >= 0) {
+                pf.push_back({kids[i].fd, POLLIN, 0});
+                who.push_back(i);
+            }
+        const int pr = poll(pf.data(), pf.size(), wait_ms);
+        if (pr < 0 && errno != EINTR) break;
+        if (pr <= 0) continue;  // 0: the loop head notices the deadline
+        for (size_t k = 0; k < pf.size(); ++k) {
+            if (!(pf[k].revents & (POLLIN | POLLHUP | POLLERR))) continue;
+            ProbeChild& c = kids[who[k]];
+            const ssize_t r = read(c.fd, tmp, sizeof(tmp));
+            if (r > 0) {
+                c.output.append(tmp, (size_t)r);
+            } else if (r == 0 || errno != EINTR) {
+                close(c.fd);
+                c.fd = -1;
+                --open_pipes;
+            }
+        }
+    }
+    for (ProbeChild& c : kids) {
+        if (*timed_out && c.pid > 0) (void)kill(c.pid, SIGKILL);  // host pid: the pid namespace was not entered
+        if (c.fd >= 0) {
+            close(c.fd);
+            c.fd = -1;
+        }
+        if (c.pid > 0)
+            while (waitpid(c.pid, &c.wait_status, 0) < 0 && errno == EINTR) {
+            }
+    }
+}
+
+// The probe's last output line and its verdict.  GMP_OK / the GMP_ERR_* the probe exited with / GMP_ERR_SYS with the
+// failing set-up step named.
+int probe_verdict(ProbeChild& c, std::string* line, int* exit_code) {
+    const int code = WIFEXITED(c.wait_status) ? WEXITSTATUS(c.wait_status) : -1;
+    if (exit_code) *exit_code = code;
+    if (code >= 120 && code <= 127) {
+        static const char* const stage[] = {"open the probe binary", "open the target's mount namespace",
+                                            "open the target's cgroup.procs", "join the target's device cgroup",
+                                            "setns into the target's mount namespace", "fexecve the probe",
+                                            "enter the target's net / ipc / uts namespace",
+                                            "drop to the pod user's identity and an empty capability set"};
+        set_error("in-pod probe: could not %s", stage[code - 120]);
+        return GMP_ERR_SYS;
+    }
+    std::string& output = c.output;
+    while (!output.empty() && (output.back() == '\n' || output.back() == '\r')) output.pop_back();
+    const size_t last_line = output.rfind('\n');
+    *line = last_line == std::string::npos ? output : output.substr(last_line + 1);
+    if (code < 0) {
+        set_error("in-pod probe was killed (wait status 0x%x)", c.wait_status);
+        return GMP_ERR_SYS;
+    }
+    return code == 0 ? GMP_OK : -code;  // the probe's exit status is -(GMP_ERR_*)
+}
+
+}  // namespace
+
 extern "C" int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
                                 const char* probe_exe, const char* const* extra_args, int n_extra, char* json, size_t cap,
                                 int* exit_status) {
@@ -1466,117 +1618,216 @@ extern "C" int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, co
         REQUIRE(n_extra >= 0 && (n_extra == 0 || extra_args != nullptr));
         json[0] = '\0';
         if (exit_status) *exit_status = -1;
-        std::string cgroup_path;
-        int rc = pod_cgroup_path(env, pod, &cgroup_path);
+        PodContext ctx;
+        int rc = resolve_pod_context(env, pod, &ctx);
         if (rc != GMP_OK) return rc;
-        std::vector<std::string> pids;
-        rc = read_cgroup_pids(env, cgroup_path, &pids);
-        if (rc != GMP_OK) return rc;
-        int target = 0;
-        rc = first_pid(pids, &target);
-        if (rc != GMP_OK) return rc;
-        const std::string ns_path = proc_root(env) + "/" + std::to_string(target) + "/ns/mnt";
-        const std::string procs_file = devices_root(env) + cgroup_path + "/cgroup.procs";
-
         std::vector<std::string> args = {"gpumounter-probe"};
         for (int i = 0; i < n; ++i) {
             args.push_back("--uuid");
             args.push_back(std::string(gpus[i].uuid) + ":" + std::to_string(gpus[i].minor_number));
         }
         for (int i = 0; i < n_extra; ++i) args.push_back(extra_args[i]);
-        std::vector<char*> argv;
-        for (std::string& a : args) argv.push_back(&a[0]);
-        argv.push_back(nullptr);
-
-        int out_pipe[2];
-        if (pipe2(out_pipe, O_CLOEXEC) != 0) {
-            set_error("pipe2: %s", strerror(errno));
-            return GMP_ERR_SYS;
-        }
-        HelperStack stack;
-        ProbeHelperArgs hargs = {probe_exe, ns_path.c_str(), procs_file.c_str(), argv.data(), out_pipe[1], 0, {nullptr, nullptr, nullptr}, 0, 0};
-        std::string extra_ns[3];
-        if (!extension_on(env, GMP_EXT_PROBE_KEEP_PRIVILEGES)) {
-            hargs.drop = 1;
-            if (!identity_of(proc_root(env), target, &hargs.uid, &hargs.gid)) {
-                set_error("in-pod probe: cannot read the identity of pid %d", target);
-                close(out_pipe[0]);
-                close(out_pipe[1]);
-                return GMP_ERR_SYS;
-            }
-            static const char* const names[3] = {"net", "ipc", "uts"};
-            for (int k = 0; k < 3; ++k) {
-                extra_ns[k] = foreign_ns(proc_root(env), target, names[k]);
-                hargs.extra_ns[k] = extra_ns[k].empty() ? nullptr : extra_ns[k].c_str();
-            }
-        }
-        const pid_t child = spawn_helper(probe_helper_main, &hargs, stack);
-        if (child < 0) {
-            set_error("clone: %s", strerror(errno));
-            close(out_pipe[0]);
-            close(out_pipe[1]);
-            return GMP_ERR_SYS;
-        }
-        close(out_pipe[1]);
-        std::string output;
-        char tmp[4096];
-        ssize_t r;
+        std::vector<ProbeChild> kids(1);
+        rc = spawn_probe(ctx, ctx.cgroup_dir + "/cgroup.procs", probe_exe, args, &kids[0]);
+        if (rc != GMP_OK) return rc;
         const uint32_t timeout_ms = env ? env->probe_timeout_ms : 0;
         bool timed_out = false;
-        if (timeout_ms == 0) {
-            while ((r = read(out_pipe[0], tmp, sizeof(tmp))) > 0 || (r < 0 && errno == EINTR))
-                if (r > 0) output.append(tmp, (size_t)r);
-        } else {
-            // bounded wait: the pipe's write end closes when the probe exits, so EOF is "finished"
-            struct timespec t0;
-            clock_gettime(CLOCK_MONOTONIC, &t0);
-            for (;;) {
-                struct timespec now;
-                clock_gettime(CLOCK_MONOTONIC, &now);
-                const long long elapsed = (now.tv_sec - t0.tv_sec) * 1000ll + (now.tv_nsec - t0.tv_nsec) / 1000000ll;
-                if (elapsed >= (long long)timeout_ms) {
-                    timed_out = true;
-                    break;
-                }
-                struct pollfd pf = {out_pipe[0], POLLIN, 0};
-                const int pr = poll(&pf, 1, (int)((long long)timeout_ms - elapsed));
-                if (pr < 0 && errno == EINTR) continue;
-                if (pr <= 0) continue;  // 0: the loop head notices the deadline
-                r = read(out_pipe[0], tmp, sizeof(tmp));
-                if (r > 0) output.append(tmp, (size_t)r);
-                else if (r == 0 || errno != EINTR) break;
-            }
-            if (timed_out) (void)kill(child, SIGKILL);  // host pid: only the mount namespace and the cgroup were entered
-        }
-        close(out_pipe[0]);
-        int status = 0;
-        while (waitpid(child, &status, 0) < 0 && errno == EINTR) {
-        }
+        collect_probes(kids, timeout_ms, &timed_out);
         if (timed_out) {
-            if (exit_status) *exit_status = -1;
             set_error("in-pod probe did not finish within %u ms and was killed", timeout_ms);
             return GMP_ERR_TIMEOUT;
         }
-        const int code = WIFEXITED(status) ? WEXITSTATUS(status) : -1;
+        std::string line;
+        int code = -1;
+        rc = probe_verdict(kids[0], &line, &code);
         if (exit_status) *exit_status = code;
-        if (code >= 120 && code <= 127) {
-            static const char* const stage[] = {"open the probe binary", "open the target's mount namespace",
-                                                "open the target's cgroup.procs", "join the target's device cgroup",
-                                                "setns into the target's mount namespace", "fexecve the probe",
-                                                "enter the target's net / ipc / uts namespace",
-                                                "drop to the pod user's identity and an empty capability set"};
-            set_error("in-pod probe: could not %s", stage[code - 120]);
-            return GMP_ERR_SYS;
+        if (rc == GMP_ERR_SYS && (code >= 120 || code < 0) && line.empty()) return rc;
+        const int erc = emit(line, json, cap);
+        if (erc != GMP_OK) return erc;
+        return rc;
+    });
+}
+
+// ---- fan-out: one probe process per mounted GPU --------------------------------------------------------------------
+// Measured on an 8-GPU HGX B200 (profiles/r02_ctx_timeline_8gpu.json): ONE process that starts CUDA on 8 freshly mounted
+// GPUs needs 1.3-1.5 s before every GPU has run a verified kernel - cuInit attaches all eight (~0.55-0.9 s) and the eight
+// primary contexts then contend inside the driver (~0.6 s).  Eight processes that each see all eight GPUs are worse (3.9 s).
+// Eight processes that each can OPEN only their own GPU take 0.86 s: each cuInit attaches one GPU, and they run side by
+// side.  The narrowing is done with the device cgroup itself: a child of the pod's devices group can only hold a subset
+// of the pod's permissions, so a kernel that runs and verifies in the child is a fortiori allowed in the pod.
+namespace {
+
+bool write_file(const std::string& path, const std::string& text) {
+    const int fd = open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC | O_CLOEXEC, 0644);  // as write_permission() opens them
+    if (fd < 0) return false;
+    const ssize_t w = write(fd, text.data(), text.size());
+    const int saved = errno;
+    close(fd);
+    errno = saved;
+    return w == (ssize_t)text.size();
+}
+
+// "key":<unsigned> at the top level of a report line (both keys used here occur once per report).
+unsigned long long json_u64(const std::string& line, const char* key) {
+    const std::string needle = std::string("\"") + key + "\":";
+    const size_t at = line.rfind(needle);
+    if (at == std::string::npos) return 0;
+    unsigned long long v = 0;
+    for (size_t i = at + needle.size(); i < line.size() && line[i] >= '0' && line[i] <= '9'; ++i) v = v * 10 + (unsigned)(line[i] - '0');
+    return v;
+}
+
+}  // namespace
+
+extern "C" int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
+                                       const char* probe_exe, const char* const* extra_args, int n_extra, char* json,
+                                       size_t cap, int* exit_status) {
+    return guarded([&]() -> int {
+        REQUIRE(pod != nullptr && probe_exe != nullptr && json != nullptr && cap > 0 && n >= 1 && n <= GMP_MAX_DEVICES && gpus != nullptr);
+        REQUIRE(n_extra >= 0 && (n_extra == 0 || extra_args != nullptr));
+        json[0] = '\0';
+        if (exit_status) *exit_status = -1;
+        if (extension_on(env, GMP_EXT_CGROUP_V2)) {
+            set_error("fan-out narrows each probe with a cgroup-v1 devices child group; not available on the unified hierarchy");
+            return GMP_ERR_UNSUPPORTED;
         }
-        while (!output.empty() && (output.back() == '\n' || output.back() == '\r')) output.pop_back();
-        const size_t last_line = output.rfind('\n');
-        const std::string line = last_line == std::string::npos ? output : output.substr(last_line + 1);
-        rc = emit(line, json, cap);
+        PodContext ctx;
+        int rc = resolve_pod_context(env, pod, &ctx);
         if (rc != GMP_OK) return rc;
-        if (code < 0) {
-            set_error("in-pod probe was killed (wait status 0x%x)", status);
-            return GMP_ERR_SYS;
+        const uint32_t timeout_ms = env ? env->probe_timeout_ms : 0;
+
+        // 1. one child group per GPU, narrowed to this GPU and the control node
+        std::vector<std::string> dirs;
+        auto remove_dirs = [&]() {
+            for (const std::string& d : dirs)
+                for (int attempt = 0; attempt < 200 && rmdir(d.c_str()) != 0 && errno == EBUSY; ++attempt) usleep(1000);
+        };
+        for (int i = 0; i < n; ++i) {
+            const std::string d = ctx.cgroup_dir + "/gmp-probe-" + std::to_string((long)getpid()) + "-" + std::to_string(i);
+            if (mkdir(d.c_str(), 0755) != 0) {
+                set_error("mkdir %s: %s", d.c_str(), strerror(errno));
+                remove_dirs();
+                return GMP_ERR_SYS;
+            }
+            dirs.push_back(d);
+            {   // cgroupfs provides cgroup.procs; a plain directory tree (the harness's scratch shape) needs one made
+                const int pfd = open((d + "/cgroup.procs").c_str(), O_WRONLY | O_CREAT | O_CLOEXEC, 0644);
+                if (pfd >= 0) close(pfd);
+            }
+            // A new devices group starts with a copy of its parent's list.  Take every OTHER GPU out of it, one entry at
+            // a time: in a default-deny group the kernel revokes exact entries only (a wildcard deny does not remove
+            // "c 195:3 rw").  GPUs the pod owns natively are entries like any other and go too.  A pod that holds the
+            // wildcard "c 195:* rw" cannot be narrowed this way; its probes then each attach every GPU (slower, still right).
+            std::string list;
+            {
+                const int lfd = open((d + "/devices.list").c_str(), O_RDONLY | O_CLOEXEC);
+                char buf[4096];
+                ssize_t r;
+                while (lfd >= 0 && (r = read(lfd, buf, sizeof(buf))) > 0) list.append(buf, (size_t)r);
+                if (lfd >= 0) close(lfd);
+            }
+            const std::string prefix = "c " + std::to_string(GMP_NVIDIA_MAJOR) + ":";
+            bool ok = true;
+            size_t begin = 0;
+            for (size_t nl; ok && (nl = list.find('\n', begin)) != std::string::npos; begin = nl + 1) {
+                const std::string line = list.substr(begin, nl - begin);
+                if (line.compare(0, prefix.size(), prefix) != 0) continue;
+                int minor = 0;
+                size_t k = prefix.size();
+                if (k >= line.size() || !isdigit((unsigned char)line[k])) continue;  // "c 195:* ..."
+                for (; k < line.size() && isdigit((unsigned char)line[k]); ++k) minor = minor * 10 + (line[k] - '0');
+                if (minor == gpus[i].minor_number || minor == 255) continue;
+                ok = write_file(d + "/devices.deny", line);
+            }
+            if (!ok) {
+                set_error("narrowing %s to GPU minor %d: %s", d.c_str(), gpus[i].minor_number, strerror(errno));
+                remove_dirs();
+                return GMP_ERR_SYS;
+            }
         }
-        return code == 0 ? GMP_OK : -code;  // the probe's exit status is -(GMP_ERR_*)
+
+        // 2. one probe per GPU, all started before any is waited for
+        std::vector<ProbeChild> kids((size_t)n);
+        for (int i = 0; i < n && rc == GMP_OK; ++i) {
+            std::vector<std::string> args = {"gpumounter-probe", "--uuid", std::string(gpus[i].uuid) + ":" + std::to_string(gpus[i].minor_number)};
+            for (int k = 0; k < n_extra; ++k) args.push_back(extra_args[k]);
+            args.push_back("--skip-p2p");
+            rc = spawn_probe(ctx, dirs[(size_t)i] + "/cgroup.procs", probe_exe, args, &kids[(size_t)i]);
+        }
+        bool timed_out = false;
+        collect_probes(kids, timeout_ms, &timed_out);  // also reaps what did start when a later spawn failed
+        remove_dirs();
+        if (rc != GMP_OK) return rc;
+        if (timed_out) {
+            set_error("in-pod probes did not finish within %u ms and were killed", timeout_ms);
+            return GMP_ERR_TIMEOUT;
+        }
+        int status = GMP_OK;
+        std::string detail;
+        std::vector<std::string> lines((size_t)n);
+        unsigned long long start_ns = ~0ull, usable_ns = 0;
+        bool all_usable = true;
+        for (int i = 0; i < n; ++i) {
+            int code = -1;
+            const int v = probe_verdict(kids[(size_t)i], &lines[(size_t)i], &code);
+            if (v != GMP_OK && status == GMP_OK) {
+                status = v;
+                detail = std::string(gpus[i].uuid) + ": " + (lines[(size_t)i].empty() ? gmp_last_error() : gmp_strerror(v));
+                if (exit_status) *exit_status = code;
+            }
+            if (lines[(size_t)i].empty() || lines[(size_t)i][0] != '{') {
+                lines[(size_t)i] = "{}";
+                all_usable = false;
+                continue;
+            }
+            const unsigned long long s0 = json_u64(lines[(size_t)i], "mono_start_ns"), u = json_u64(lines[(size_t)i], "mono_usable_ns");
+            if (s0 != 0 && s0 < start_ns) start_ns = s0;
+            if (u == 0) all_usable = false;
+            if (u > usable_ns) usable_ns = u;
+        }
+        if (!all_usable) usable_ns = 0;
+        if (start_ns == ~0ull) start_ns = 0;
+
+        // 3. the pod as ONE process sees it: CUDA enumerates exactly the mounted set, and the P2P step across it.  After
+        //    the usable instant, so its eight-GPU cuInit does not slow the per-GPU probes down.
+        std::string whole = "null";
+        if (status == GMP_OK) {
+            std::vector<std::string> args = {"gpumounter-probe"};
+            for (int i = 0; i < n; ++i) {
+                args.push_back("--uuid");
+                args.push_back(std::string(gpus[i].uuid) + ":" + std::to_string(gpus[i].minor_number));
+            }
+            for (int k = 0; k < n_extra; ++k) args.push_back(extra_args[k]);
+            args.push_back("--skip-hbm");
+            std::vector<ProbeChild> one(1);
+            rc = spawn_probe(ctx, ctx.cgroup_dir + "/cgroup.procs", probe_exe, args, &one[0]);
+            if (rc != GMP_OK) return rc;
+            collect_probes(one, timeout_ms, &timed_out);
+            if (timed_out) {
+                set_error("whole-pod probe did not finish within %u ms and was killed", timeout_ms);
+                return GMP_ERR_TIMEOUT;
+            }
+            std::string line;
+            int code = -1;
+            const int v = probe_verdict(one[0], &line, &code);
+            if (!line.empty() && line[0] == '{') whole = line;
+            if (v != GMP_OK) {
+                status = v;
+                detail = std::string("whole-pod view: ") + (whole == "null" ? gmp_last_error() : gmp_strerror(v));
+                if (exit_status) *exit_status = code;
+            }
+        }
+        if (status == GMP_OK && exit_status) *exit_status = 0;
+
+        std::string out = "{\"status\":" + std::to_string(status) + ",\"verdict\":" + json_quote(gmp_strerror(status)) +
+                          ",\"detail\":" + json_quote(detail.c_str()) + ",\"fanout\":true,\"n_gpus\":" + std::to_string(n) +
+                          ",\"mono_start_ns\":" + std::to_string(start_ns) + ",\"mono_usable_ns\":" + std::to_string(usable_ns) +
+                          ",\"reports\":[";
+        for (int i = 0; i < n; ++i) out += (i ? "," : "") + lines[(size_t)i];
+        out += "],\"whole_pod\":" + whole + "}";
+        rc = emit(out, json, cap);
+        if (rc != GMP_OK) return rc;
+        if (status != GMP_OK) set_error("%s", detail.c_str());
+        return status;
     });
 }

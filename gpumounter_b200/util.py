@@ -119,6 +119,45 @@ def ProbeInPod(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = 
     return rc, report
 
 
+def ProbeInPodFanout(pod: Pod, gpus: Sequence[NvidiaGPU], extra_args: Sequence[str] = (), env: Optional[MountEnv] = None,
+                     probe_exe: Optional[str] = None, raise_on_error: bool = True):
+    """ProbeInPod with one probe process per GPU, each confined to its own GPU by a child device cgroup, then one
+    whole-pod process for the device-set check and the P2P step (gmp_probe_in_pod_fanout; no reference counterpart).
+    Returns (status, report) where the report has ProbeInPod's shape - "hbm", "devices", "health" gathered from the per-GPU
+    reports in the order of `gpus`; device-set / NVML status, "p2p" and "ms_p2p" from the whole-pod process; "ms_cuda_init"
+    the slowest per-GPU one - plus the raw "reports" and "whole_pod"."""
+    import json as _json
+
+    from . import probe as _probe
+    from ._model import c_strings
+
+    exe = probe_exe or _probe.probe_executable()
+    buf = ctypes.create_string_buffer(1 << 18)
+    code = ctypes.c_int(-1)
+    c = pod.to_c()
+    rc = lib().gmp_probe_in_pod_fanout(env_ptr(env), ctypes.byref(c), as_c_array(gpus), len(gpus), exe.encode(),
+                                       c_strings(list(extra_args)), len(extra_args), buf, 1 << 18, ctypes.byref(code))
+    text = buf.value.decode(errors="replace")
+    rep = _json.loads(text) if text.startswith("{") else {}
+    if rep:
+        subs = [r for r in rep.get("reports", []) if r]
+        whole = rep.get("whole_pod") or {}
+        for key in ("hbm", "devices", "health"):
+            rep[key] = [x for r in subs for x in r.get(key, [])]
+        for key in ("ms_cuda_init", "ms_nvml", "ms_nodes", "ms_hbm"):
+            rep[key] = max([r.get(key, 0.0) for r in subs], default=0.0)
+        rep["ms_to_usable"] = (rep["mono_usable_ns"] - rep["mono_start_ns"]) / 1e6 if rep.get("mono_usable_ns") else 0.0
+        rep["nodes_status"] = min([r.get("nodes_status", 0) for r in subs], default=0)
+        for key in ("device_set_status", "nvml_status"):
+            rep[key] = whole.get(key, min([r.get(key, 0) for r in subs], default=0))
+        if "p2p" in whole:
+            rep["p2p"] = whole["p2p"]
+        rep["ms_p2p"] = whole.get("ms_p2p", 0.0)
+    if raise_on_error:
+        check(rc, "ProbeInPodFanout")
+    return rc, rep
+
+
 def VerifyUnmountedInPod(pod: Pod, gpus: Sequence[NvidiaGPU], env: Optional[MountEnv] = None, dev_dir: Optional[str] = None,
                          probe_exe: Optional[str] = None, raise_on_error: bool = True):
     """After UnmountGPU(s): from inside the pod, none of the GPUs' device nodes may exist any more.  No reference

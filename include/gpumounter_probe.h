@@ -693,6 +693,25 @@ GMP_API int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const
                              char* json, size_t cap, int* exit_status);
 
 /*
+ * The same check with ONE probe process per GPU, started together, each in a child of the pod's cgroup-v1 devices group
+ * that may open only its own GPU (a child group can only narrow what the pod holds, so what verifies there is allowed
+ * in the pod).  No reference counterpart.  Why: CUDA start-up, not the kernels, is the mount-to-usable latency, and it
+ * does not scale inside one process - on an 8-GPU HGX B200 one process needs 1.3-1.5 s until all eight freshly mounted
+ * GPUs have run a verified kernel (cuInit attaches every GPU it can open, then eight primary contexts contend in the
+ * driver); eight processes that each attach one GPU need 0.86 s (profiles/r02_ctx_timeline_8gpu.json).  After the last of
+ * them has finished, one more probe process runs in the pod's own group with --skip-hbm: it checks that CUDA in the
+ * pod enumerates exactly the mounted set and runs the P2P step.  `json` receives
+ *   {"status","verdict","detail","fanout":true,"n_gpus","mono_start_ns","mono_usable_ns","reports":[<one gpumounter-probe
+ *    line per GPU, in the order of gpus>],"whole_pod":<that last process's line or null>}
+ * where mono_usable_ns is the instant the LAST GPU's first kernel result verified (0 if one never did).  The child groups
+ * are removed before the call returns.  GMP_ERR_UNSUPPORTED with GMP_EXT_CGROUP_V2 (use gmp_probe_in_pod there).
+ * gmp_mount_env.probe_timeout_ms bounds the per-GPU phase and the whole-pod phase separately.
+ */
+GMP_API int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,
+                                    const char* probe_exe, const char* const* extra_args, int n_extra,
+                                    char* json, size_t cap, int* exit_status);
+
+/*
  * The pod's view of its device nodes without running anything of the pod's image: a helper process joins the pod's
  * device cgroup and mount namespace and open(2)s /dev/nvidiactl, /dev/nvidia-uvm and the node of every GPU in `gpus`.
  * GMP_OK, or GMP_ERR_NODE_CTL / GMP_ERR_NODE_UVM / GMP_ERR_NODE_GPU (absent, or no device behind it) /

@@ -498,3 +498,55 @@ def test_in_pod_probe_runs_with_the_pod_users_identity_and_no_capabilities(fake_
                    extensions=EXT_PROBE_KEEP_PRIVILEGES)
         rc, rep = util.ProbeInPod(product_pod(), gpus, [], keep, probe_exe=str(fake_probe))
         assert rc == 0 and int(rep["eff"], 16) == int(mine["CapEff"], 16) and rep["nnp"] == 0
+
+
+def test_fanout_probe_starts_one_process_per_gpu_each_in_a_narrowed_child_group(fake_nvml, tmp_path):
+    """gmp_probe_in_pod_fanout on a real cgroup-v1 devices group: every per-GPU process sits in a child group that holds
+    the NVIDIA control node and ITS GPU only, all of them run inside the pod's mount namespace, the whole-pod process
+    runs in the pod's own group afterwards, the merged report carries all of it, and the child groups are gone again."""
+    why = harness.can_run_pod_like()
+    if why:
+        pytest.skip(why)
+    gpus_cfg = fake_nvml()
+    fake_probe = tmp_path / "fake-probe"
+    fake_probe.write_text(
+        "#!/bin/sh\n"
+        "now=$(date +%s%N)\n"
+        "printf '{\"status\":0,\"args\":\"%s\",\"cgroup\":\"%s\",\"list\":\"%s\",\"mnt\":\"%s\",\"hbm\":[{\"uuid\":\"x\"}],"
+        "\"devices\":[{\"uuid\":\"x\"}],\"ms_cuda_init\":1.5,\"mono_start_ns\":%s,\"mono_usable_ns\":%s}\\n' "
+        "\"$*\" \"$(grep devices /proc/self/cgroup | cut -d: -f3)\" "
+        "\"$(cat /sys/fs/cgroup/devices$(grep devices /proc/self/cgroup | cut -d: -f3)/devices.list | grep '195:' | tr '\\n' ';')\" "
+        "\"$(readlink /proc/self/ns/mnt)\" \"$now\" \"$(( now + 1000 ))\"\n")
+    fake_probe.chmod(0o755)
+    t = harness.Target(pod_like=True).start()
+    try:
+        env = MountEnv(devices_root=t.devices_root, cgroup_driver="cgroupfs")
+        recs = [device.New(m, u) for u, m, _ in gpus_cfg[:3]]
+        util.MountGPUs(product_pod(), recs, env)
+        rc, rep = util.ProbeInPodFanout(product_pod(), recs, ["--bytes", "1M"], env, probe_exe=str(fake_probe))
+        assert rc == 0 and rep["status"] == 0 and rep["fanout"] is True and rep["n_gpus"] == 3
+        assert len(rep["reports"]) == 3 and len(rep["hbm"]) == 3
+        pod_group = t.cgroup_dir[len("/sys/fs/cgroup/devices"):]
+        for i, (r, g) in enumerate(zip(rep["reports"], recs)):
+            assert r["args"] == f"--uuid {g.UUID}:{g.MinorNumber} --bytes 1M --skip-p2p"
+            assert r["cgroup"].startswith(pod_group + "/gmp-probe-") and r["cgroup"].endswith(f"-{i}")
+            assert sorted(x for x in r["list"].split(";") if x) == sorted([f"c 195:{g.MinorNumber} rw", "c 195:255 rw"])
+            assert r["mnt"] == os.readlink(f"/proc/{t.pid}/ns/mnt")
+        w = rep["whole_pod"]
+        assert w["cgroup"] == pod_group and w["args"].endswith("--bytes 1M --skip-hbm") and w["args"].count("--uuid") == 3
+        assert rep["mono_usable_ns"] == max(r["mono_usable_ns"] for r in rep["reports"])
+        assert rep["mono_start_ns"] == min(r["mono_start_ns"] for r in rep["reports"])
+        assert [d for d in os.listdir(t.cgroup_dir) if d.startswith("gmp-probe-")] == []
+        # a probe that fails on one GPU fails the call, names the GPU, and the whole-pod step is not run
+        bad = tmp_path / "bad-probe"
+        bad.write_text("#!/bin/sh\ncase \"$*\" in *:%d*) echo '{\"status\":-7}'; exit 7;; esac\necho '{\"status\":0}'\n" % recs[1].MinorNumber)
+        bad.chmod(0o755)
+        rc, rep = util.ProbeInPodFanout(product_pod(), recs, [], env, probe_exe=str(bad), raise_on_error=False)
+        assert rc == _lib.GMP_ERR_VERIFY and rep["status"] == -7 and recs[1].UUID in rep["detail"] and rep["whole_pod"] is None
+        assert rep["mono_usable_ns"] == 0
+        assert [d for d in os.listdir(t.cgroup_dir) if d.startswith("gmp-probe-")] == []
+        util.UnmountGPUs(product_pod(), recs, False, env)
+    finally:
+        with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+            f.write(f"{t.pid}\n")
+        t.stop()

@@ -201,3 +201,28 @@ def test_churn_in_one_pod_leaves_nothing_behind(pod_target):
     assert t.read("devices.list") == list0
     assert len(os.listdir("/proc/self/fd")) == fds_after_first <= fds0 + 4  # the NVML image's one-off descriptors
     assert [len(r.GetRunningProcess()) for r in recs_all] == procs0
+
+
+def test_fanout_probe_one_process_per_gpu(pod_target):
+    """gmp_probe_in_pod_fanout on real GPUs: every per-GPU process sees exactly ONE CUDA device (its child group hides the
+    others), all of them verify, and the whole-pod process that follows sees exactly the mounted set."""
+    t = pod_target
+    gpus = node_gpus()
+    k = len(gpus) - 1 if len(gpus) > 1 else 1
+    mounted = gpus[:k]
+    recs = [device.New(m, u) for u, m in mounted]
+    util.MountGPUs(the_pod(), recs, env_of(t))
+    rc, rep = util.ProbeInPodFanout(the_pod(), recs, ["--bytes", "256M", "--iters", "1", "--dma-bytes", "4M", "--p2p-bytes", "64M",
+                                                      "--p2p-iters", "1"], env_of(t), raise_on_error=False)
+    assert rc == 0 and rep["status"] == 0, (rc, rep.get("detail"), rep)
+    assert [r["n_gpus"] for r in rep["reports"]] == [1] * k
+    assert [r["devices"][0]["uuid"] for r in rep["reports"]] == [u for u, _ in mounted]
+    assert all(h["status"] == 0 and h["mismatch_lanes"] == 0 and h["write_gbs"] > 1000 for h in rep["hbm"]) and len(rep["hbm"]) == k
+    assert rep["mono_usable_ns"] == max(h["mono_first_verified_ns"] for h in rep["hbm"])
+    w = rep["whole_pod"]
+    assert w["status"] == 0 and w["device_set_status"] == 0 and {d["uuid"] for d in w["devices"]} == {u for u, _ in mounted}
+    if k >= 2:
+        assert w["p2p"]["matrix_match"] == 1 and w["p2p"]["mismatch_lanes"] == 0
+    assert [d for d in os.listdir(t.cgroup_dir) if d.startswith("gmp-probe-")] == []
+    util.UnmountGPUs(the_pod(), recs, False, env_of(t))
+    assert t.read("devices.list").count("195:") == 1  # the control node alone, as before the mount
