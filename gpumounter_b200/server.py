@@ -15,6 +15,7 @@ Differences from the reference, all deliberate and none visible on the wire:
 
 from __future__ import annotations
 
+import threading
 import time
 from concurrent import futures
 from dataclasses import dataclass
@@ -89,11 +90,22 @@ class GPUMountImpl:
 
     def __init__(self, cluster: Cluster, gpus: Optional[Sequence[device.NvidiaGPU]] = None, env: Optional[MountEnv] = None,
                  probe_hook: Optional[ProbeHook] = None, poll_interval_s: float = 0.002, poll_timeout_s: Optional[float] = None,
-                 extended_response: bool = False):
+                 extended_response: bool = False, fail_on_probe_error: bool = False, revoke_on_mount_failure: bool = True):
         self.cluster = cluster
         # additive wire surface: answer AddGPU with the probe verdict in NEW field numbers (2..4);
         # a peer built from the reference's api.proto skips them as unknown fields and sees the same enum in field 1
         self.extended_response = extended_response
+        # Policy for the post-mount probe (no reference counterpart).  False: a failing probe is reported (probe_status in the
+        # extended response, last_probe_report) and AddGPU still answers Success, as the reference would have.  True: the
+        # GPUs are unmounted again, the slave pods deleted and the RPC fails with ServiceInternalError.
+        self.fail_on_probe_error = fail_on_probe_error
+        # The batched mount grants ALL n devices.allow lines before the first mknod; if it fails part-way the reference's
+        # rollback (delete the slave pods, server.go:86-91) would hand GPUs back to the scheduler that the pod can still
+        # open.  True: permissions and nodes are revoked before the slave pods go.  False: exactly the reference's rollback.
+        self.revoke_on_mount_failure = revoke_on_mount_failure
+        # gRPC serves RPCs concurrently and UpdateGPUStatus rewrites the shared GPU list in place (the reference has the same
+        # race, collector.go:113-135,140-144): every refresh-then-query pair runs under this lock
+        self._status_lock = threading.Lock()
         self.env = env
         self.probe_hook = probe_hook
         self.poll_interval_s = poll_interval_s
@@ -108,19 +120,22 @@ class GPUMountImpl:
 
     # ---- collector / allocator calls that need the kubelet ---------------------------------------------------
     def GetPodGPUResources(self, podName: str, namespace: str) -> List[device.NvidiaGPU]:  # ref: collector.go:149-163
-        self.allocator.UpdateGPUStatus(self.cluster.list_pod_resources())
-        return self.allocator.GetPodGPUResources(podName, namespace)
+        with self._status_lock:
+            self.allocator.UpdateGPUStatus(self.cluster.list_pod_resources())
+            return self.allocator.GetPodGPUResources(podName, namespace)
 
     def GetMountType(self, pod: Pod) -> str:  # ref: allocator.go:158-187
-        try:
-            self.allocator.UpdateGPUStatus(self.cluster.list_pod_resources())
-        except (ClusterError, ProbeError):
-            return util.UnknownMount  # allocator.go:161-165
-        return self.allocator.GetMountType(pod.name, pod.namespace)
+        with self._status_lock:
+            try:
+                self.allocator.UpdateGPUStatus(self.cluster.list_pod_resources())
+            except (ClusterError, ProbeError):
+                return util.UnknownMount  # allocator.go:161-165
+            return self.allocator.GetMountType(pod.name, pod.namespace)
 
     def GetRemoveGPU(self, ownerPod: Pod, uuids: Sequence[str]) -> List[device.NvidiaGPU]:  # ref: allocator.go:101-126
-        self.allocator.UpdateGPUStatus(self.cluster.list_pod_resources())
-        return self.allocator.GetRemoveGPU(ownerPod.name, ownerPod.namespace, list(uuids))
+        with self._status_lock:
+            self.allocator.UpdateGPUStatus(self.cluster.list_pod_resources())
+            return self.allocator.GetRemoveGPU(ownerPod.name, ownerPod.namespace, list(uuids))
 
     # ---- slave pods (ref: allocator.go:40-99, 128-156, 236-317) ------------------------------------------------
     def _poll(self, step: Callable[[], Optional[str]], podNames: Sequence[str] = ()) -> str:
@@ -231,19 +246,40 @@ class GPUMountImpl:
             if str(e) == InsufficientGPU:
                 return api.AddGPUResponse(add_gpu_result=api.AddGPUResult_InsufficientGPU)  # server.go:69-71
             raise RpcError(ServiceInternalError)  # server.go:72-77
-        try:
-            util.MountGPUs(targetPod, gpuResources, self.env)  # the loop of server.go:80-95, batched
-        except ProbeError:
-            for freeGPU in gpuResources:  # server.go:86-91
+        def free_slave_pods():  # server.go:86-91
+            for freeGPU in gpuResources:
                 try:
                     self.cluster.delete_pod(GPUPoolNamespace, freeGPU.PodName, grace_period_seconds=0)
                 except (ClusterError, NotFound):
                     pass
+
+        def revoke_all():
+            for g in gpuResources:  # one by one: some have a node, all have a devices.allow line, any step may fail
+                try:
+                    util.UnmountGPU(targetPod, g, True, self.env)
+                except ProbeError:
+                    pass
+
+        try:
+            util.MountGPUs(targetPod, gpuResources, self.env)  # the loop of server.go:80-95, batched
+        except ProbeError:
+            if self.revoke_on_mount_failure:
+                revoke_all()
+            free_slave_pods()
             raise RpcError(ServiceInternalError)
         status, report = None, None
         if self.probe_hook is not None:  # new: prove the mounted GPUs usable from inside the pod
-            status, report = self.probe_hook(targetPod, gpuResources)
-            self.last_probe_report = dict(report, status=status)
+            try:
+                status, report = self.probe_hook(targetPod, gpuResources)
+            except ProbeError as e:  # a hook that raises (GMP_ERR_TIMEOUT included) is a failed probe, not a crashed RPC
+                status, report = e.code, {"detail": e.detail}
+            except Exception as e:  # noqa: BLE001 - whatever the hook does, AddGPU keeps its contract
+                status, report = -9, {"detail": f"{type(e).__name__}: {e}"}
+            self.last_probe_report = dict(report or {}, status=status)
+            if status not in (None, 0) and self.fail_on_probe_error:
+                revoke_all()
+                free_slave_pods()
+                raise RpcError(ServiceInternalError)
         if self.extended_response:
             import json as _json
 

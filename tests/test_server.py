@@ -4,6 +4,8 @@ target, in process and through a real gRPC channel on the reference's method pat
 import grpc
 import pytest
 
+from gpumounter_b200 import ProbeError
+
 from gpumounter_b200 import api, device, server
 from gpumounter_b200._model import MountEnv, Pod
 from tests import harness
@@ -150,6 +152,75 @@ def test_mount_failure_rolls_back_slave_pods_but_not_nodes(world):
         impl.AddGPU(add(n=1))
     assert len(cluster.alloc) == 1 and cluster.deleted[-1][1] == 0                           # server.go:86-91
     assert "nvidia3" in t.nodes()                                                            # earlier mount untouched
+
+
+def test_partial_mount_failure_revokes_what_was_granted_before_the_gpus_are_freed(world):
+    """The batched mount writes ALL n devices.allow lines before the first mknod.  When it fails part-way the rollback
+    must not hand GPUs back to the scheduler that this pod can still open: lines revoked, nodes made so far removed.
+    revoke_on_mount_failure=False is the reference's rollback to the letter (slave pods only, server.go:86-91)."""
+    import os
+
+    impl, cluster, t, _, _ = world
+    # three GPUs asked; the SECOND one's node exists already, so mknod fails after the first node was made
+    os.mknod(f"/proc/{t.pid}/root{t.devdir}/nvidia2", 0o020666, os.makedev(195, 2))
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):
+        impl.AddGPU(add(n=3))
+    assert not cluster.alloc and t.nodes() == []                       # nothing left mounted, nothing left allocated
+    assert (t.read("devices.deny") or "").strip() != ""                # the grants were taken back
+    impl.revoke_on_mount_failure = False
+    for minor in range(8):                                             # whichever GPUs come next, their first mknod fails
+        os.mknod(f"/proc/{t.pid}/root{t.devdir}/nvidia{minor}", 0o020666, os.makedev(195, minor))
+    deny_before = t.read("devices.deny")
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):
+        impl.AddGPU(add(n=3))
+    assert not cluster.alloc and t.read("devices.deny") == deny_before  # the reference's rollback: slave pods only
+
+
+def test_probe_verdict_policy(world):
+    """A failing or raising probe hook never escapes as a crashed RPC; with fail_on_probe_error it undoes the mount."""
+    impl, cluster, t, _, _ = world
+
+    def failing_hook(pod, gpus):
+        return -7, {"detail": "mismatch"}
+
+    def raising_hook(pod, gpus):
+        raise ProbeError(-27, "in-pod probe did not finish", "ProbeInPod")
+
+    impl.probe_hook = failing_hook
+    assert impl.AddGPU(add(n=1)).add_gpu_result == api.AddGPUResult_Success      # default policy: reported, not enforced
+    assert impl.last_probe_report["status"] == -7 and len(t.nodes()) == 1
+    impl.probe_hook = raising_hook
+    assert impl.AddGPU(add(n=1)).add_gpu_result == api.AddGPUResult_Success
+    assert impl.last_probe_report["status"] == -27 and "did not finish" in impl.last_probe_report["detail"]
+    assert len(t.nodes()) == 2 and len(cluster.alloc) == 2
+    impl.fail_on_probe_error = True
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):
+        impl.AddGPU(add(n=2))
+    assert len(t.nodes()) == 2 and len(cluster.alloc) == 2                       # the two new GPUs are gone again, the old stay
+
+
+def test_status_refresh_and_query_are_one_critical_section(world):
+    """Concurrent handlers (gRPC serves them from a thread pool) never see the GPU list half reset."""
+    import threading
+
+    impl, cluster, t, _, _ = world
+    assert impl.AddGPU(add(n=2)).add_gpu_result == api.AddGPUResult_Success
+    wrong, stop = [], threading.Event()
+
+    def reader():
+        while not stop.is_set():
+            if impl.GetMountType(target_pod()) != "single-mount" or len(impl.GetPodGPUResources("gpu-pod", "default")) != 2:
+                wrong.append(1)
+
+    threads = [threading.Thread(target=reader) for _ in range(4)]
+    for th in threads:
+        th.start()
+    for _ in range(300):
+        impl.GetRemoveGPU(target_pod(), [])
+    stop.set()
+    for th in threads:
+        th.join()
+    assert not wrong
 
 
 def remove(uuids, force=False):
