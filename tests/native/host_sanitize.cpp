@@ -25,6 +25,7 @@ void set_error(const char* fmt, ...) {
 void clear_error() { g_err[0] = '\0'; }
 }  // namespace gmp
 extern "C" const char* gmp_last_error(void) { return gmp::g_err; }
+extern "C" const char* gmp_strerror(int) { return "error"; }  // lives in gmp_core.cu, which this host-only build leaves out
 
 #define CHECK(cond)                                                         \
     do {                                                                    \
