@@ -278,3 +278,35 @@ def test_repeated_one_shot_probes_leave_nothing_behind():
     assert out.returncode == 0, out.stderr[-2000:]
     base, kept = (int(x) for x in out.stdout.split()[-2:])
     assert abs(base - kept) <= 64 << 20, (base, kept)   # nothing accumulates over a dozen calls (allocator granularity aside)
+
+
+def test_probe_hbm_retained_buffers_are_reused_and_released(cuda):
+    """GMP_HBM_F_RETAIN (a resident worker probing again and again): the second call allocates nothing, answers the same
+    bit-exact checksums, and the memory comes back on gmp_probe_hbm_release() - or on the next call without the flag."""
+    torch = cuda
+    uuid = probe.enumerate_cuda()[0].uuid
+    nbytes = (512 << 20) + 16
+    flags = probe.HBM_F_KEEP_DEVICE | probe.HBM_F_RETAIN
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    r1 = probe.probe_hbm(uuid, nbytes=nbytes, iters=1, seed=41, dma_bytes=4 << 20, flags=flags)
+    free1, _ = torch.cuda.mem_get_info()
+    assert r1.status == 0 and free0 - free1 >= 2 * nbytes                       # both buffers are still there
+    r2 = probe.probe_hbm(uuid, nbytes=nbytes, iters=1, seed=41, dma_bytes=4 << 20, flags=flags)
+    free2, _ = torch.cuda.mem_get_info()
+    assert r2.status == 0 and free2 == free1                                    # nothing allocated, nothing freed
+    assert (r2.xor64, r2.sum64) == (r1.xor64, r1.sum64) == gmo.pattern_checksum(nbytes, probe.PAT_SPLITMIX, 41)
+    assert r2.ns_alloc < 1_000_000 and r2.ns_teardown < 1_000_000 and r2.ns_alloc < r1.ns_alloc
+    assert r2.h2d_bytes == 4 << 20 and r2.mismatch_lanes == 0
+    # a smaller request fits in what is retained; a larger one grows it
+    r3 = probe.probe_hbm(uuid, nbytes=nbytes // 2, iters=1, seed=42, dma_bytes=0, flags=flags)
+    assert r3.status == 0 and torch.cuda.mem_get_info()[0] == free1
+    assert (r3.xor64, r3.sum64) == gmo.pattern_checksum(nbytes // 2, probe.PAT_SPLITMIX, 42)
+    probe.probe_hbm_release(uuid)
+    assert torch.cuda.mem_get_info()[0] >= free0 - (8 << 20)                    # given back (modulo allocator granularity)
+    # a call WITHOUT the flag gives back what earlier RETAIN calls left
+    probe.probe_hbm(uuid, nbytes=nbytes, iters=1, dma_bytes=0, flags=flags)
+    assert free0 - torch.cuda.mem_get_info()[0] >= 2 * nbytes
+    r4 = probe.probe_hbm(uuid, nbytes=64 << 20, iters=1, dma_bytes=0, flags=probe.HBM_F_KEEP_DEVICE)
+    assert r4.status == 0 and torch.cuda.mem_get_info()[0] >= free0 - (8 << 20)
+    probe.probe_hbm_release()                                                   # nothing left: still GMP_OK
