@@ -446,7 +446,7 @@ def main():
                         "frac_of_datasheet_8tbs": gbs[k] / 8000.0,  # secondary denominator, not the graded one
                         "share_of_step": avg[k] / sum(avg.values())} for k in avg},
         "kernels_over": "slowest rank's average per kernel" if world > 1 else "this GPU",
-        "roofline": {"bound": "hbm", "kernel": "k_hbm_copy", "achieved": gbs["copy"], "peak": peak, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "k_hbm_copy_bulk (gmp_hbm_copy: TMA bulk copy, the step's dominant kernel)", "achieved": gbs["copy"], "peak": peak, "unit": "GB/s",
                      "frac": gbs["copy"] / peak, "traffic": None, "traffic_source": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": 2 * nbytes},
         "e2e": e2e,

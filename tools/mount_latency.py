@@ -401,8 +401,9 @@ def churn_real(rounds, hbm_bytes=256 << 20, nodes_only=False, pod_like=None):
                     assert rc == 0, (rc, failed, probe.lib().gmp_last_error())
                     usable_s.append((time.monotonic_ns() - t0) / 1e9)
                 else:
-                    rc, rep = util.ProbeInPod(pod, recs, g.probe_args() + ["--bytes", str(hbm_bytes), "--iters", "1",
-                                                                           "--dma-bytes", "1M", "--skip-p2p"], env, raise_on_error=False)
+                    hook = util.ProbeInPodFanout if (k >= 2 and g.pod_like) else util.ProbeInPod  # the product's hook
+                    rc, rep = hook(pod, recs, g.probe_args() + ["--bytes", str(hbm_bytes), "--iters", "1",
+                                                                "--dma-bytes", "1M", "--skip-p2p"], env, raise_on_error=False)
                     assert rc == 0 and rep.get("status") == 0, (rc, rep, probe.lib().gmp_last_error())
                     usable_s.append((rep["mono_usable_ns"] - t0) / 1e9)
                 g.unrestrict_cuda()
@@ -419,7 +420,8 @@ def churn_real(rounds, hbm_bytes=256 << 20, nodes_only=False, pod_like=None):
     leaked_procs = [len(r.GetRunningProcess()) - b for r, b in zip(recs_all, baseline)]
     free1 = device_free_bytes()
     return {"gpus": n, "rounds": rounds, "steps": steps, "hbm_bytes_per_gpu": hbm_bytes, "target": label, "total_s": total_s,
-            "per_step_check": "device nodes opened from inside the pod (no CUDA)" if nodes_only else "cold in-pod HBM probe",
+            "per_step_check": "device nodes opened from inside the pod (no CUDA)" if nodes_only
+            else "cold in-pod HBM probe (one process per GPU from 2 GPUs on, then the whole-pod device-set check)",
             "mount_to_usable": {"p50_s": statistics.median(usable_s), "p99_s": pct(usable_s, 0.99), "max_s": max(usable_s)},
             "unmount_to_verified_gone": {"p50_ms": 1e3 * statistics.median(gone_s), "p99_ms": 1e3 * pct(gone_s, 0.99)},
             "leaked_fds": open_fds() - fds0, "leaked_gpu_processes": leaked_procs,

@@ -4,7 +4,6 @@
 mkdir -p gpurun_out
 N=$(nvidia-smi -L | wc -l)
 nvidia-smi topo -m > gpurun_out/topo_${N}gpu.txt 2>&1
-timeout 200 python tools/ctx_timeline.py --holders init --sizes 4,8 --iters 3 --out gpurun_out/ctx_timeline_${N}gpu.json | head -4
 timeout 300 python -m pytest tests -m gpu -q -rs -k "p2p or pod or nvml" > gpurun_out/pytest_gpu_${N}.log 2>&1; tail -5 gpurun_out/pytest_gpu_${N}.log
 timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 10 --warmup 3 --mount-iters 6 2> gpurun_out/bench${N}.err | tail -1 > gpurun_out/bench_${N}gpu.json; echo "bench rc=${PIPESTATUS[0]}"
 python - <<PY
@@ -21,4 +20,14 @@ try:
 except Exception as e:
     print("bench summary failed:", e); print(open("gpurun_out/bench${N}.err").read()[-3000:])
 PY
-timeout 300 python tools/mount_latency.py --skip-mount-bench --churn-rounds 0 --churn-real-rounds 3 --churn-nodes-rounds 100 --out gpurun_out/churn_real_${N}gpu.json > gpurun_out/churn.log 2>&1; tail -c 1800 gpurun_out/churn.log
+timeout 400 python tools/mount_latency.py --skip-mount-bench --churn-rounds 0 --churn-real-rounds 10 --churn-nodes-rounds 100 --usable-iters 5 --fanout --out gpurun_out/churn_real_${N}gpu.json > gpurun_out/churn.log 2>&1
+python - <<PY
+import json
+d = json.load(open("gpurun_out/churn_real_${N}gpu.json"))
+for k in ("mount_to_usable", "mount_to_usable_fanout"):
+    for n, v in d.get(k, {}).items():
+        print(k, n, "p50", round(v["p50_s"], 3), "p99", round(v["p99_s"], 3), "first", round(v["first_gpu_usable_p50_s"], 3), "cuInit", round(v["cuda_init_ms"]))
+for k in ("churn_real", "churn_real_nodes_only"):
+    c = d.get(k, {}); print(k, {x: c.get(x) for x in ("steps", "total_s", "mount_to_usable", "unmount_to_verified_gone", "leaked_fds", "leaked_gpu_processes", "devices_list_back_to_baseline", "device_free_bytes_delta", "zombies")})
+PY
+tail -c 600 gpurun_out/churn.log | grep -i -A5 "error\|Traceback" | head -20
