@@ -20,7 +20,7 @@ try:
 except Exception as e:
     print("bench summary failed:", e); print(open("gpurun_out/bench${N}.err").read()[-3000:])
 PY
-timeout 400 python tools/mount_latency.py --skip-mount-bench --churn-rounds 0 --churn-real-rounds 10 --churn-nodes-rounds 100 --usable-iters 5 --fanout --out gpurun_out/churn_real_${N}gpu.json > gpurun_out/churn.log 2>&1
+timeout 520 python tools/mount_latency.py --skip-mount-bench --churn-rounds 0 --churn-real-rounds 6 --churn-nodes-rounds 100 --usable-iters 5 --fanout --out gpurun_out/churn_real_${N}gpu.json > gpurun_out/churn.log 2>&1
 python - <<PY
 import json
 d = json.load(open("gpurun_out/churn_real_${N}gpu.json"))
