@@ -76,3 +76,30 @@ def test_verify_slow_path_is_out_of_line(sass):
     for k, body in fn.items():
         if "k_hbm_read_verify" in k and "segments" not in k:
             assert "CALL.REL.NOINC" in body and "RET.REL.NODEC" in body, f"{k}: the __noinline__ slow path was inlined"
+
+
+def test_peer_kernels(sass):
+    """The all-to-all push writes with the same 256-bit streaming stores as the write kernel and indexes its per-peer
+    arguments from the constant bank (no local-memory copy of the argument struct); the bulk-engine pattern write
+    stages through shared memory and never stores to global from a register."""
+    _, fn = sass
+    a2a = [k for k in fn if "k_peer_alltoall_write" in k]
+    assert len(a2a) == 1
+    body = fn[a2a[0]]
+    assert "STG.E.EF.ENL2.256" in body and not re.search(r"\b(LDL|STL)\b", body) and "LDC" in body
+    bulk = [k for k in fn if "k_hbm_write_pattern_bulk" in k]
+    assert bulk
+    for k in bulk:
+        assert "STS.128" in fn[k] and "UBLKCP.G.S" in fn[k] and "STG" not in fn[k], k
+
+
+def test_allocation_free_verify_writes_its_slot_with_plain_stores(sass):
+    """One CTA per segment, the segment's verdict stored into its own slot: no atomics in the streaming kernel (the one
+    fold CTA afterwards is where the four atomics are)."""
+    _, fn = sass
+    seg = [k for k in fn if "k_hbm_read_verify_segments" in k]
+    assert len(seg) == 5
+    for k in seg:
+        assert "LDG.E.128" in fn[k] and not re.search(r"\b(ATOMG|RED)\b", fn[k]), k
+    fold = [k for k in fn if "k_noalloc_fold" in k]
+    assert len(fold) == 1 and re.search(r"\b(ATOMG|RED)", fn[fold[0]])

@@ -46,7 +46,7 @@ BOOT = ("import os, sys\n"
         "os.execv(sys.argv[3], sys.argv[3:])\n")
 
 
-def fanout_once(g, gpus, narrow=True):
+def fanout_once(g, gpus, narrow=True, only_first=False, stagger_ms=0.0):
     """narrow: each process in a child cgroup that opens only its own GPU; else every process sees all k mounted GPUs
     (cuInit attaches all of them) and is told which one to probe (--host-view: more visible than named is fine)."""
     t = g.t
@@ -60,11 +60,13 @@ def fanout_once(g, gpus, narrow=True):
         if narrow:
             dirs = [child_cgroup(t, i, m, [mm for _, mm in gpus]) for i, (_, m) in enumerate(gpus)]
         procs = []
-        for i, (u, m) in enumerate(gpus):
+        for i, (u, m) in enumerate(gpus[:1] if only_first else gpus):  # only_first: ONE narrowed process, alone
             d = dirs[i] if narrow else t.cgroup_dir
             argv = [sys.executable, "-c", BOOT, os.path.join(d, "cgroup.procs"), f"/proc/{t.pid}/ns/mnt", exe,
                     "--uuid", f"{u}:{m}"] + PROBE_ARGS + ([] if narrow else ["--host-view"])
             procs.append(subprocess.Popen(argv, stdout=subprocess.PIPE, text=True))
+            if stagger_ms:  # per-GPU attach work is serialised node-wide: let each start-up finish its own before the next begins
+                time.sleep(stagger_ms / 1e3)
         reps = [json.loads(p.communicate(timeout=120)[0].strip().splitlines()[-1]) for p in procs]
         util.UnmountGPUs(pod, recs, False, env)
     finally:
@@ -125,6 +127,7 @@ def main():
     ap.add_argument("--holders", default="none,ctx", help="comma list of none,init,ctx")
     ap.add_argument("--sizes", default="1,2,4,8")
     ap.add_argument("--iters", type=int, default=4)
+    ap.add_argument("--staggers", default="", help="comma list of ms between the starts of the narrowed per-GPU processes")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     os.environ.pop("CUDA_VISIBLE_DEVICES", None)
@@ -136,7 +139,7 @@ def main():
         try:
             for k in [int(x) for x in args.sizes.split(",") if int(x) <= len(all_gpus)]:
                 gpus = all_gpus[:k]
-                row = {"single": [], "fanout": [], "fanout_shared": []}
+                row = {"single": [], "fanout": [], "fanout_shared": [], "one_narrowed_alone": []}
                 for _ in range(args.iters):
                     with ml.GpuTarget(True) as g:
                         row["single"].append(single_once(g, gpus))
@@ -145,6 +148,12 @@ def main():
                             row["fanout"].append(fanout_once(g, gpus))
                         with ml.GpuTarget(True) as g:
                             row["fanout_shared"].append(fanout_once(g, gpus, narrow=False))
+                        for st in [float(x) for x in args.staggers.split(",") if x]:
+                            with ml.GpuTarget(True) as g:
+                                row.setdefault(f"fanout_stagger_{st:g}ms", []).append(fanout_once(g, gpus, stagger_ms=st))
+                        # does a node that EXISTS but is refused cost cuInit time, or is it the k start-ups sharing a lock?
+                        with ml.GpuTarget(True) as g:
+                            row["one_narrowed_alone"].append(fanout_once(g, gpus, only_first=True))
                 sizes[str(k)] = {
                     mode: {"all_usable_p50_ms": statistics.median(r["all_usable_ms"] for r in runs),
                            "first_usable_p50_ms": statistics.median(r["first_usable_ms"] for r in runs),
