@@ -550,3 +550,30 @@ def test_fanout_probe_starts_one_process_per_gpu_each_in_a_narrowed_child_group(
         with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
             f.write(f"{t.pid}\n")
         t.stop()
+
+
+def test_fanout_probe_deadline_kills_every_child_and_removes_the_child_groups(fake_nvml, tmp_path):
+    """A GPU that hangs must not hang AddGPU: probe_timeout_ms bounds the per-GPU phase, every probe process is killed,
+    reaped, and the child groups are removed."""
+    why = harness.can_run_pod_like()
+    if why:
+        pytest.skip(why)
+    gpus_cfg = fake_nvml()
+    slow = tmp_path / "slow-probe"
+    slow.write_text("#!/bin/sh\nexec sleep 30\n")
+    slow.chmod(0o755)
+    t = harness.Target(pod_like=True).start()
+    try:
+        env = MountEnv(devices_root=t.devices_root, cgroup_driver="cgroupfs", probe_timeout_ms=300)
+        recs = [device.New(m, u) for u, m, _ in gpus_cfg[:2]]
+        util.MountGPUs(product_pod(), recs, env)
+        t0 = time.monotonic()
+        rc, rep = util.ProbeInPodFanout(product_pod(), recs, [], env, probe_exe=str(slow), raise_on_error=False)
+        assert rc == _lib.GMP_ERR_TIMEOUT and time.monotonic() - t0 < 5
+        assert [d for d in os.listdir(t.cgroup_dir) if d.startswith("gmp-probe-")] == []
+        assert t.read("cgroup.procs").split() == [str(t.pid)]          # nobody of ours is left in the pod's group
+        util.UnmountGPUs(product_pod(), recs, False, env)
+    finally:
+        with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
+            f.write(f"{t.pid}\n")
+        t.stop()
