@@ -324,6 +324,28 @@ class GPUMountImpl:
         return api.RemoveGPUResponse(remove_gpu_result=api.RemoveGPUResult_Success)
 
 
+def in_pod_probe_hook(env: Optional[MountEnv] = None, probe_args: Sequence[str] = ("--bytes", "1G", "--iters", "1"),
+                      nodes_first: bool = True) -> "ProbeHook":
+    """The product's post-mount hook (insertion point ref: server.go:97-98), for
+    GPUMountImpl(probe_hook=...).  Stage 1 (nothing of the pod executed): the device nodes open from inside the pod's
+    device cgroup and mount namespace.  Stage 2: gpumounter-probe inside the pod - one process per GPU from two GPUs on
+    (gmp_probe_in_pod_fanout, cgroup v1), one process otherwise.  Returns (status, report); never raises."""
+    from ._model import EXT_CGROUP_V2
+
+    def hook(pod: Pod, gpus: Sequence[device.NvidiaGPU]):
+        if nodes_first:
+            rc, failed = util.CheckNodesInPod(pod, gpus, env, raise_on_error=False)
+            if rc != 0:
+                from ._lib import lib
+
+                return rc, {"stage": "nodes", "failed_index": failed, "detail": lib().gmp_last_error().decode(errors="replace")}
+        v2 = env is not None and bool(env.extensions & EXT_CGROUP_V2)
+        fn = util.ProbeInPodFanout if (len(gpus) >= 2 and not v2) else util.ProbeInPod
+        return fn(pod, gpus, list(probe_args), env, raise_on_error=False)
+
+    return hook
+
+
 def serve(impl: GPUMountImpl, address: str = f"[::]:{api.WORKER_PORT}", max_workers: int = 8):
     """Both services on one insecure port, as ref: cmd/GPUMounter-worker/main.go:24-33.  Returns the started grpc.Server."""
     import grpc

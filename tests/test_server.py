@@ -199,6 +199,20 @@ def test_probe_verdict_policy(world):
     assert len(t.nodes()) == 2 and len(cluster.alloc) == 2                       # the two new GPUs are gone again, the old stay
 
 
+def test_the_products_hook_reports_the_pods_view_and_never_raises(world):
+    """server.in_pod_probe_hook on a box without a driver: stage 1 (nodes opened from inside the pod) already fails, with the
+    node named; the verdict travels in last_probe_report, and with fail_on_probe_error the mount is undone."""
+    impl, cluster, t, _, _ = world
+    impl.probe_hook = server.in_pod_probe_hook(impl.env)
+    assert impl.AddGPU(add(n=1)).add_gpu_result == api.AddGPUResult_Success
+    rep = impl.last_probe_report
+    assert rep["status"] == -18 and rep["stage"] == "nodes" and "nvidiactl" in rep["detail"]      # GMP_ERR_NODE_CTL
+    impl.fail_on_probe_error = True
+    with pytest.raises(server.RpcError, match="^Service Internal Error $"):
+        impl.AddGPU(add(n=1))
+    assert len(t.nodes()) == 1 and len(cluster.alloc) == 1
+
+
 def test_status_refresh_and_query_are_one_critical_section(world):
     """Concurrent handlers (gRPC serves them from a thread pool) never see the GPU list half reset."""
     import threading
