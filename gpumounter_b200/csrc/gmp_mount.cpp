@@ -1750,7 +1750,14 @@ extern "C" int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* 
         std::vector<ProbeChild> kids((size_t)n);
         for (int i = 0; i < n && rc == GMP_OK; ++i) {
             std::vector<std::string> args = {"gpumounter-probe", "--uuid", std::string(gpus[i].uuid) + ":" + std::to_string(gpus[i].minor_number)};
-            for (int k = 0; k < n_extra; ++k) args.push_back(extra_args[k]);
+            for (int k = 0; k < n_extra; ++k) {
+                // a narrowed child sees its own GPU and nothing else: what the pod held before is the whole-pod step's to check
+                if (strcmp(extra_args[k], "--also-mounted") == 0) {
+                    ++k;
+                    continue;
+                }
+                args.push_back(extra_args[k]);
+            }
             args.push_back("--skip-p2p");
             rc = spawn_probe(ctx, dirs[(size_t)i] + "/cgroup.procs", probe_exe, args, &kids[(size_t)i]);
         }

@@ -184,8 +184,20 @@ int probe_all_impl(const gmp_device* expected, int n_expected, const gmp_probe_o
 
     // 1. device nodes and the driver library, as seen from this process's namespaces
     uint64_t t0 = now_ns();
+    if (o.n_also_visible < 0 || o.n_also_visible > GMP_MAX_DEVICES || (o.n_also_visible > 0 && o.also_visible == nullptr)) {
+        set_error("bad also_visible list");
+        return GMP_ERR_INVALID;
+    }
     if (!(o.flags & GMP_PROBE_F_SKIP_NODES)) {
         out->nodes_status = check_nodes(expected, n_expected, o.dev_dir);
+        if (out->nodes_status == GMP_OK && o.n_also_visible > 0) {
+            // the GPUs the pod held before this mount: their nodes must still open as well (control nodes checked above)
+            const std::string dir = (o.dev_dir && o.dev_dir[0]) ? o.dev_dir : "/dev";
+            for (int i = 0; i < o.n_also_visible && out->nodes_status == GMP_OK; ++i)
+                if (o.also_visible[i].minor != UINT32_MAX)
+                    out->nodes_status = check_node(dir + "/nvidia" + std::to_string(o.also_visible[i].minor), GMP_ERR_NODE_GPU,
+                                                   GMP_ERR_NODE_DENIED);
+        }
         first_failure(out, out->nodes_status);
     }
     out->ns_nodes = now_ns() - t0;
@@ -269,8 +281,14 @@ int probe_all_impl(const gmp_device* expected, int n_expected, const gmp_probe_o
                 if (out->devices[i].pci_bus_id[0] == '\0') memcpy(out->devices[i].pci_bus_id, cuda[c].pci_bus_id, GMP_PCI_LEN);
             }
         }
-        if (out->device_set_status == GMP_OK && n_cuda != n_expected && !(o.flags & GMP_PROBE_F_HOST_VIEW)) {
-            set_error("CUDA sees %d devices, %d were mounted", n_cuda, n_expected);
+        for (int i = 0; i < o.n_also_visible && out->device_set_status == GMP_OK; ++i)
+            if (find_uuid(cuda, n_cuda, o.also_visible[i].uuid) < 0) {
+                set_error("%s, which the pod held before this mount, is not visible to CUDA (%d visible)", o.also_visible[i].uuid, n_cuda);
+                out->device_set_status = GMP_ERR_DEVICE_SET;
+            }
+        if (out->device_set_status == GMP_OK && n_cuda != n_expected + o.n_also_visible && !(o.flags & GMP_PROBE_F_HOST_VIEW)) {
+            set_error("CUDA sees %d devices, %d were mounted (%d now + %d held before)", n_cuda, n_expected + o.n_also_visible,
+                      n_expected, o.n_also_visible);
             out->device_set_status = GMP_ERR_DEVICE_SET;
         }
     } else {

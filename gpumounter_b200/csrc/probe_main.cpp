@@ -136,6 +136,7 @@ void usage() {
     fprintf(stderr,
             "usage: gpumounter-probe --gone GPU-...:minor [--gone ...] [--dev-dir DIR]     (after an unmount)\n"
             "       gpumounter-probe [--uuid GPU-...[:minor]]... [--uuids a,b,c] [--bytes N[K|M|G]] [--iters N]\n"
+            "         [--also-mounted GPU-...[:minor]]...  (held by the pod already: must be visible too, not probed)\n"
             "         [--patterns MASK|all] [--dma-bytes N] [--p2p-bytes N] [--p2p-iters N] [--dev-dir DIR]\n"
             "         [--skip-nodes] [--skip-hbm] [--skip-p2p] [--skip-nvml] [--skip-copy] [--matrix-only] [--lib-baselines]\n"
             "         [--min-hbm-gbs N] [--min-p2p-gbs N]  (fail with -25 when a measured rate is lower)\n"
@@ -166,7 +167,7 @@ int main(int argc, char** argv) {
     if (const char* v = getenv("GPUMOUNTER_PROBE_STRICT_HEALTH")) strict_health = parse_u32(v) != 0;
     if (const char* v = getenv("GPUMOUNTER_PROBE_MIN_HBM_GBS")) min_hbm_gbs = (double)parse_u32(v);
     if (const char* v = getenv("GPUMOUNTER_PROBE_MIN_P2P_GBS")) min_p2p_gbs = (double)parse_u32(v);
-    std::vector<gmp_device> expected, gone;
+    std::vector<gmp_device> expected, gone, also;
     std::string dev_dir;
     // environment defaults (the worker's DaemonSet can set them once; command-line flags win)
     if (const char* v = getenv("GPUMOUNTER_PROBE_BYTES")) o.hbm.bytes = parse_size(v);
@@ -190,6 +191,7 @@ int main(int argc, char** argv) {
         };
         if (a == "--uuid") add_device(&expected, need("--uuid"));
         else if (a == "--gone") add_device(&gone, need("--gone"));
+        else if (a == "--also-mounted") add_device(&also, need("--also-mounted"));
         else if (a == "--uuids") {
             std::string all = need("--uuids");
             size_t b = 0;
@@ -251,7 +253,11 @@ int main(int argc, char** argv) {
         fflush(stdout);
         return rc == GMP_OK ? 0 : -rc;
     }
-    if ((int)expected.size() > GMP_MAX_DEVICES) {
+    if (!also.empty()) {
+        o.also_visible = also.data();
+        o.n_also_visible = (int)also.size();
+    }
+    if ((int)expected.size() > GMP_MAX_DEVICES || (int)also.size() > GMP_MAX_DEVICES) {
         fprintf(stderr, "at most %d devices\n", GMP_MAX_DEVICES);
         return 64;
     }

@@ -331,7 +331,8 @@ def nvml_health(uuid: str) -> gmp_gpu_health:
 
 class gmp_probe_opts(ctypes.Structure):
     _fields_ = [("hbm", gmp_hbm_opts), ("p2p", gmp_p2p_opts), ("flags", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
-                ("dev_dir", ctypes.c_char_p)]
+                ("dev_dir", ctypes.c_char_p), ("also_visible", ctypes.POINTER(gmp_device)), ("n_also_visible", ctypes.c_int32),
+                ("reserved2", ctypes.c_int32)]
 
 
 class gmp_report(ctypes.Structure):
@@ -367,7 +368,8 @@ def peer_access(device: int, peer: int, enable: bool = True) -> None:
 
 def probe_all(expected: Sequence[Device] = (), *, hbm_bytes: int = 0, hbm_iters: int = 0, pattern_mask: int = 0,
               dma_bytes: int = UINT64_MAX, p2p_bytes: int = 0, p2p_iters: int = 0, flags: int = 0, hbm_flags: int = 0,
-              p2p_flags: int = 0, dev_dir: Optional[str] = None, raise_on_error: bool = True) -> gmp_report:
+              p2p_flags: int = 0, dev_dir: Optional[str] = None, also_visible: Sequence[Device] = (),
+              raise_on_error: bool = True) -> gmp_report:
     """The whole-pod probe the worker's hook runs after AddGPU's mount loop (ref: server.go:97-98)."""
     f = lib().gmp_probe_all
     f.argtypes = [ctypes.POINTER(gmp_device), ctypes.c_int, ctypes.POINTER(gmp_probe_opts), ctypes.POINTER(gmp_report)]
@@ -376,6 +378,9 @@ def probe_all(expected: Sequence[Device] = (), *, hbm_bytes: int = 0, hbm_iters:
     o.p2p = gmp_p2p_opts(p2p_bytes, p2p_iters, p2p_flags, 0)
     o.flags = flags
     o.dev_dir = dev_dir.encode() if dev_dir else None
+    also = _to_c_devices(also_visible) if also_visible else None  # GPUs the pod already holds: visible, not probed
+    o.also_visible = also
+    o.n_also_visible = len(also_visible)
     r = gmp_report()
     rc = f(_to_c_devices(expected) if expected else None, len(expected), ctypes.byref(o), ctypes.byref(r))
     if raise_on_error and rc < 0:

@@ -82,7 +82,7 @@ class Cluster:
         return False
 
 
-ProbeHook = Callable[[Pod, Sequence[device.NvidiaGPU]], "tuple[int, dict]"]
+ProbeHook = Callable[..., "tuple[int, dict]"]  # (pod, newly mounted GPUs[, GPUs the pod held before]) -> (status, report)
 
 
 class GPUMountImpl:
@@ -270,7 +270,17 @@ class GPUMountImpl:
         status, report = None, None
         if self.probe_hook is not None:  # new: prove the mounted GPUs usable from inside the pod
             try:
-                status, report = self.probe_hook(targetPod, gpuResources)
+                try:  # what the pod held before this call (a hook that takes a third argument is told)
+                    new = {g.UUID for g in gpuResources}
+                    already = [g for g in self.GetPodGPUResources(targetPod.name, targetPod.namespace) if g.UUID not in new]
+                except (ClusterError, ProbeError):
+                    already = []
+                import inspect
+
+                if len(inspect.signature(self.probe_hook).parameters) >= 3:
+                    status, report = self.probe_hook(targetPod, gpuResources, already)
+                else:
+                    status, report = self.probe_hook(targetPod, gpuResources)
             except ProbeError as e:  # a hook that raises (GMP_ERR_TIMEOUT included) is a failed probe, not a crashed RPC
                 status, report = e.code, {"detail": e.detail}
             except Exception as e:  # noqa: BLE001 - whatever the hook does, AddGPU keeps its contract
@@ -332,7 +342,12 @@ def in_pod_probe_hook(env: Optional[MountEnv] = None, probe_args: Sequence[str] 
     (gmp_probe_in_pod_fanout, cgroup v1), one process otherwise.  Returns (status, report); never raises."""
     from ._model import EXT_CGROUP_V2
 
-    def hook(pod: Pod, gpus: Sequence[device.NvidiaGPU]):
+    def hook(pod: Pod, gpus: Sequence[device.NvidiaGPU], already: Sequence[device.NvidiaGPU] = ()):
+        # `already`: GPUs the pod held before this AddGPU.  CUDA in the pod must see them too (the visible set has to be
+        # exactly new + old), but they are not probed - the tenant may be using them.
+        args = list(probe_args)
+        for g in already:
+            args += ["--also-mounted", f"{g.UUID}:{g.MinorNumber}"]
         if nodes_first:
             rc, failed = util.CheckNodesInPod(pod, gpus, env, raise_on_error=False)
             if rc != 0:
@@ -341,7 +356,7 @@ def in_pod_probe_hook(env: Optional[MountEnv] = None, probe_args: Sequence[str] 
                 return rc, {"stage": "nodes", "failed_index": failed, "detail": lib().gmp_last_error().decode(errors="replace")}
         v2 = env is not None and bool(env.extensions & EXT_CGROUP_V2)
         fn = util.ProbeInPodFanout if (len(gpus) >= 2 and not v2) else util.ProbeInPod
-        return fn(pod, gpus, list(probe_args), env, raise_on_error=False)
+        return fn(pod, gpus, args, env, raise_on_error=False)
 
     return hook
 

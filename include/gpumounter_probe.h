@@ -464,6 +464,12 @@ typedef struct gmp_probe_opts {
     uint32_t     flags;       /* GMP_PROBE_F_* */
     uint32_t     reserved;
     const char*  dev_dir;     /* where the device nodes are looked up; NULL -> "/dev" */
+    /* GPUs the pod holds ALREADY (earlier AddGPU calls, or natively): they must be visible too - the CUDA-visible set
+     * has to equal expected + also_visible exactly - but they are not probed: they may be running the tenant's work.
+     * gpumounter-probe: --also-mounted UUID[:minor].  NULL / 0: the pod holds nothing but `expected`. */
+    const gmp_device* also_visible;
+    int32_t      n_also_visible;
+    int32_t      reserved2;
 } gmp_probe_opts;
 
 enum {

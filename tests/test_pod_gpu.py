@@ -226,3 +226,29 @@ def test_fanout_probe_one_process_per_gpu(pod_target):
     assert [d for d in os.listdir(t.cgroup_dir) if d.startswith("gmp-probe-")] == []
     util.UnmountGPUs(the_pod(), recs, False, env_of(t))
     assert t.read("devices.list").count("195:") == 1  # the control node alone, as before the mount
+
+
+def test_incremental_mount_expects_what_the_pod_held_before(pod_target):
+    """A second AddGPU into a pod that already has a GPU: CUDA in the pod sees both; the probe of the NEW one names the old
+    one with --also-mounted (visible, not probed).  Without it the set check rightly fails; so does naming a GPU the pod
+    does not hold."""
+    t = pod_target
+    gpus = node_gpus()
+    if len(gpus) < 2:
+        pytest.skip("needs at least 2 GPUs")
+    (u0, m0), (u1, m1) = gpus[0], gpus[1]
+    first, second = device.New(m0, u0), device.New(m1, u1)
+    util.MountGPUs(the_pod(), [first], env_of(t))
+    util.MountGPUs(the_pod(), [second], env_of(t))
+    small = ["--bytes", "64M", "--iters", "1", "--dma-bytes", "1M", "--skip-p2p"]
+    rc, rep = probe_in_pod(t, [second], small + ["--also-mounted", f"{u0}:{m0}"])
+    assert rc == 0 and [h["uuid"] for h in rep["hbm"]] == [u1] and rep["device_set_status"] == 0, (rc, rep)
+    rc, rep = probe_in_pod(t, [second], small)
+    assert rc == _lib.GMP_ERR_DEVICE_SET and "2" in rep["detail"], (rc, rep)
+    if len(gpus) >= 3:
+        rc, rep = probe_in_pod(t, [second], small + ["--also-mounted", f"{gpus[2][0]}:{gpus[2][1]}", "--skip-nodes"])
+        assert rc == _lib.GMP_ERR_DEVICE_SET and gpus[2][0] in rep["detail"], (rc, rep)
+    # the fan-out form: the per-GPU child is narrowed to the new GPU, the whole-pod step checks the full set
+    rc, rep = util.ProbeInPodFanout(the_pod(), [second], small + ["--also-mounted", f"{u0}:{m0}"], env_of(t), raise_on_error=False)
+    assert rc == 0 and rep["reports"][0]["n_gpus"] == 1 and rep["whole_pod"]["device_set_status"] == 0, (rc, rep)
+    util.UnmountGPUs(the_pod(), [first, second], False, env_of(t))

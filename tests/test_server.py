@@ -213,6 +213,22 @@ def test_the_products_hook_reports_the_pods_view_and_never_raises(world):
     assert len(t.nodes()) == 1 and len(cluster.alloc) == 1
 
 
+def test_hook_is_told_what_the_pod_held_before(world):
+    """A second AddGPU mounts one more GPU into a pod that already has two: the in-pod probe must expect CUDA to see all
+    three and probe only the new one."""
+    impl, cluster, t, _, _ = world
+    seen = []
+
+    def hook(pod, gpus, already):
+        seen.append(([g.UUID for g in gpus], sorted(g.UUID for g in already)))
+        return 0, {}
+
+    impl.probe_hook = hook
+    impl.AddGPU(add(n=2))
+    impl.AddGPU(add(n=1))
+    assert seen == [([FAKE_UUIDS[0], FAKE_UUIDS[1]], []), ([FAKE_UUIDS[2]], sorted([FAKE_UUIDS[0], FAKE_UUIDS[1]]))]
+
+
 def test_status_refresh_and_query_are_one_critical_section(world):
     """Concurrent handlers (gRPC serves them from a thread pool) never see the GPU list half reset."""
     import threading
