@@ -30,6 +30,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <new>
 #include <string>
 #include <vector>
@@ -1700,10 +1701,20 @@ extern "C" int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* 
         std::vector<std::string> dirs;
         auto remove_dirs = [&]() {
             for (const std::string& d : dirs)
-                for (int attempt = 0; attempt < 200 && rmdir(d.c_str()) != 0 && errno == EBUSY; ++attempt) usleep(1000);
+                for (int attempt = 0; attempt < 200 && rmdir(d.c_str()) != 0; ++attempt) {
+                    if (errno == EBUSY) {  // cgroupfs: the probe's exit has not been accounted yet
+                        usleep(1000);
+                    } else if (errno == ENOTEMPTY && attempt == 0) {  // a plain directory tree (scratch harness): our own files
+                        for (const char* f : {"/cgroup.procs", "/devices.deny", "/devices.allow"}) (void)unlink((d + f).c_str());
+                    } else {
+                        break;
+                    }
+                }
         };
+        static std::atomic<unsigned> call_counter{0};  // concurrent calls for one pod must not share a child group
+        const unsigned call_id = call_counter.fetch_add(1, std::memory_order_relaxed);
         for (int i = 0; i < n; ++i) {
-            const std::string d = ctx.cgroup_dir + "/gmp-probe-" + std::to_string((long)getpid()) + "-" + std::to_string(i);
+            const std::string d = ctx.cgroup_dir + "/gmp-probe-" + std::to_string((long)getpid()) + "-" + std::to_string(call_id) + "-" + std::to_string(i);
             if (mkdir(d.c_str(), 0755) != 0) {
                 set_error("mkdir %s: %s", d.c_str(), strerror(errno));
                 remove_dirs();

@@ -9,6 +9,7 @@
 
 #include <string>
 #include <thread>
+#include <unistd.h>
 #include <vector>
 
 #include "gpumounter_probe.h"
@@ -163,6 +164,59 @@ static void logic_round(int salt) {
     CHECK(gmp_enumerate_nvml(devs, 2, &n) == GMP_ERR_NVML_NOT_FOUND && n == 0);
 }
 
+// The process-spawning entry points (clone(CLONE_VM|CLONE_VFORK) helpers, privilege drop, pipes, child groups) on a scratch
+// tree whose "pod" is this very process: own pid in cgroup.procs, own mount namespace.  Needs root (setns); skipped otherwise.
+static void in_pod_round() {
+#if defined(__SANITIZE_THREAD__)
+    return;  // TSan's own clone() interceptor aborts on CLONE_VM children (tsan_rtl.cpp FindSlotAndLock): ASan/UBSan cover this part
+#endif
+    if (geteuid() != 0) return;
+    char tmpl[] = "/tmp/gmp_sanitize_XXXXXX";
+    CHECK(mkdtemp(tmpl) != nullptr);
+    const std::string root = tmpl;
+    const std::string uid = "0a1b2c3d-1111-2222-3333-444455556666", cid(64, 'c');
+    const std::string cg = root + "/kubepods/besteffort/pod" + uid + "/" + cid;
+    CHECK(system(("mkdir -p " + cg + " " + root + "/dev").c_str()) == 0);
+    {
+        FILE* f = fopen((cg + "/cgroup.procs").c_str(), "w");
+        CHECK(f != nullptr);
+        fprintf(f, "%d\n", (int)getpid());
+        fclose(f);
+    }
+    const std::string prefix = root + "/dev/nvidia", container = "docker://" + cid;
+    gmp_mount_env env;
+    memset(&env, 0, sizeof(env));
+    env.devices_root = root.c_str();
+    env.dev_prefix = prefix.c_str();
+    env.cgroup_driver = "cgroupfs";
+    env.probe_timeout_ms = 20000;
+    gmp_container_resources none[1] = {{nullptr, nullptr, nullptr, nullptr}};
+    gmp_pod pod = {"gpu-pod", "default", uid.c_str(), "node", container.c_str(), 1, none};
+    gmp_gpu gpus[2];
+    CHECK(gmp_device_new(3, "GPU-aaaaaaaa-0000-0000-0000-000000000003", &gpus[0]) == GMP_OK);
+    CHECK(gmp_device_new(5, "GPU-aaaaaaaa-0000-0000-0000-000000000005", &gpus[1]) == GMP_OK);
+    int done = 0, status = -2, failed = -2;
+    CHECK(gmp_mount_gpus(&env, &pod, gpus, 2, &done) == GMP_OK && done == 2);
+    static char json[1 << 16];
+    const char* extra[] = {"--also-mounted", "GPU-x:9", "--bytes", "1M"};
+    for (uint32_t ext : {0u, (uint32_t)GMP_EXT_PROBE_KEEP_PRIVILEGES}) {
+        env.extensions = ext;
+        // /bin/echo stands in for the probe: its "report" is its own argument list
+        CHECK(gmp_probe_in_pod(&env, &pod, gpus, 2, "/bin/echo", extra, 4, json, sizeof(json), &status) == GMP_OK && status == 0);
+        CHECK(strstr(json, "--uuid GPU-aaaaaaaa-0000-0000-0000-000000000003:3") != nullptr && strstr(json, "--also-mounted GPU-x:9") != nullptr);
+        CHECK(gmp_probe_in_pod(&env, &pod, gpus, 2, "/nonexistent/probe", nullptr, 0, json, sizeof(json), &status) == GMP_ERR_SYS);
+        CHECK(gmp_probe_in_pod(&env, &pod, gpus, 2, "/bin/echo", nullptr, 0, json, 4, &status) == GMP_ERR_BUFFER_TOO_SMALL);
+        const int rc = gmp_probe_in_pod_fanout(&env, &pod, gpus, 2, "/bin/echo", extra, 4, json, sizeof(json), &status);
+        if (rc != GMP_OK) fprintf(stderr, "fan-out: rc=%d %s | %s\n", rc, gmp_last_error(), json);
+        CHECK(rc == GMP_OK && strstr(json, "\"fanout\":true") != nullptr && strstr(json, "\"whole_pod\":null") != nullptr);
+        CHECK(gmp_probe_in_pod_fanout(&env, &pod, gpus, 2, "/nonexistent/probe", nullptr, 0, json, sizeof(json), &status) == GMP_ERR_SYS);
+    }
+    env.extensions = 0;
+    (void)gmp_check_nodes_in_pod(&env, &pod, gpus, 2, &failed);  // scratch nodes have no driver behind them: an error code, no crash
+    CHECK(gmp_verify_gone_in_pod(&env, &pod, gpus, 2, &failed) == GMP_ERR_STILL_MOUNTED && failed == 0);
+    CHECK(system(("rm -rf " + root).c_str()) == 0);
+}
+
 int main() {
     logic_round(0);
     std::vector<std::thread> ts;
@@ -171,6 +225,7 @@ int main() {
             for (int i = 0; i < 50; ++i) logic_round(t);
         });
     for (auto& t : ts) t.join();
+    in_pod_round();
     puts("host sanitize ok");
     return 0;
 }
