@@ -210,6 +210,14 @@ def p2p_section(uuids, bytes_per_pair: int, iters: int):
                    store_kernel="k_hbm_write_pattern on a peer pointer (32-byte vector stores; 713 GB/s is the fabric's ceiling for "
                                 "128-byte write requests, profiles/r02_p2p_ncu.md); all-to-all: k_peer_alltoall_write, one launch per sender",
                    nvlink5_nominal_gbs_per_direction=900.0)
+        # bound: NVLink.  Denominator: the pool's measured peer copy (B200_PROFILING.md: 770 GB/s per direction; nominal 900).
+        # Algorithmic bytes = wire user bytes = bytes_per_pair per ordered pair (profiles/r02_p2p_ncu.md: equal on every path).
+        out["roofline"] = {"bound": "nvlink", "peak": 770.0, "peak_source": "measured peer copy, /opt/skills/guides/B200_PROFILING.md",
+                           "unit": "GB/s", "store": {"achieved": out["store_gbs"]["mean"], "frac": out["store_gbs"]["mean"] / 770.0},
+                           "load_verify": {"achieved": out["load_gbs"]["mean"], "frac": out["load_gbs"]["mean"] / 770.0},
+                           "alltoall_per_gpu": {"achieved": out["alltoall_gbs_per_gpu"], "frac": out["alltoall_gbs_per_gpu"] / 770.0},
+                           "note": "stores are 128-byte NVLink requests with 24 bytes of protocol each: 713 GB/s of user bytes is 849 GB/s "
+                                   "on the wire (profiles/r02_p2p_ncu.md)"}
         out["ok"] = bool(rep["status"] == 0 and out["matrix_match_nvml"] and out["mismatch_lanes"] == 0)
         return out
     except Exception as e:
