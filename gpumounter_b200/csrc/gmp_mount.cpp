@@ -1699,6 +1699,7 @@ extern "C" int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* 
 
         // 1. one child group per GPU, narrowed to this GPU and the control node
         std::vector<std::string> dirs;
+        bool not_narrowed = false;  // the pod holds a wildcard over the NVIDIA major: children see what the pod sees
         auto remove_dirs = [&]() {
             for (const std::string& d : dirs)
                 for (int attempt = 0; attempt < 200 && rmdir(d.c_str()) != 0; ++attempt) {
@@ -1742,6 +1743,12 @@ extern "C" int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* 
             size_t begin = 0;
             for (size_t nl; ok && (nl = list.find('\n', begin)) != std::string::npos; begin = nl + 1) {
                 const std::string line = list.substr(begin, nl - begin);
+                // a wildcard that covers the NVIDIA major with read or write access ("a *:* rwm", "c *:* rw", "c 195:* rw"):
+                // this group cannot be narrowed, its probes will see every GPU the pod sees
+                const bool any_dev = line.compare(0, 6, "a *:* ") == 0 || line.compare(0, 6, "c *:* ") == 0 ||
+                                     line.compare(0, prefix.size() + 2, prefix + "* ") == 0;
+                if (any_dev && line.find_first_of("rw", line.rfind(' ') == std::string::npos ? 0 : line.rfind(' ')) != std::string::npos)
+                    not_narrowed = true;
                 if (line.compare(0, prefix.size(), prefix) != 0) continue;
                 int minor = 0;
                 size_t k = prefix.size();
@@ -1770,6 +1777,7 @@ extern "C" int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* 
                 args.push_back(extra_args[k]);
             }
             args.push_back("--skip-p2p");
+            if (not_narrowed) args.push_back("--host-view");  // more devices visible than named is then expected, not an error
             rc = spawn_probe(ctx, dirs[(size_t)i] + "/cgroup.procs", probe_exe, args, &kids[(size_t)i]);
         }
         bool timed_out = false;

@@ -710,7 +710,9 @@ GMP_API int gmp_probe_in_pod(const gmp_mount_env* env, const gmp_pod* pod, const
  *   {"status","verdict","detail","fanout":true,"n_gpus","mono_start_ns","mono_usable_ns","reports":[<one gpumounter-probe
  *    line per GPU, in the order of gpus>],"whole_pod":<that last process's line or null>}
  * where mono_usable_ns is the instant the LAST GPU's first kernel result verified (0 if one never did).  The child groups
- * are removed before the call returns.  GMP_ERR_UNSUPPORTED with GMP_EXT_CGROUP_V2 (use gmp_probe_in_pod there).
+ * are removed before the call returns.  A pod whose devices group holds a wildcard over the NVIDIA major (a privileged pod:
+ * "a *:* rwm") cannot be narrowed: its per-GPU probes are then started with --host-view and each attaches every GPU the pod
+ * sees (correct, but no faster than one process).  GMP_ERR_UNSUPPORTED with GMP_EXT_CGROUP_V2 (use gmp_probe_in_pod there).
  * gmp_mount_env.probe_timeout_ms bounds the per-GPU phase and the whole-pod phase separately.
  */
 GMP_API int gmp_probe_in_pod_fanout(const gmp_mount_env* env, const gmp_pod* pod, const gmp_gpu* gpus, int n,

@@ -577,3 +577,27 @@ def test_fanout_probe_deadline_kills_every_child_and_removes_the_child_groups(fa
         with open("/sys/fs/cgroup/devices/cgroup.procs", "w") as f:
             f.write(f"{t.pid}\n")
         t.stop()
+
+
+def test_fanout_in_a_pod_that_holds_a_wildcard_cannot_narrow_and_says_so_to_its_probes(fake_nvml, tmp_path):
+    """A privileged pod ("a *:* rwm" in its devices group) cannot be narrowed per GPU: every per-GPU probe will see all of
+    the pod's GPUs, so it is started with --host-view (more devices visible than named is expected there)."""
+    why = harness.can_run_pod_like()
+    if why:
+        pytest.skip(why)
+    gpus_cfg = fake_nvml()
+    echo = tmp_path / "echo-probe"
+    echo.write_text("#!/bin/sh\nprintf '{\"status\":0,\"args\":\"%s\",\"mono_start_ns\":1,\"mono_usable_ns\":2}\\n' \"$*\"\n")
+    echo.chmod(0o755)
+    t = harness.Target(real_cgroup=True).start()   # a real devices group left at the parent's allow-everything
+    try:
+        assert "a *:* rwm" in t.read("devices.list")
+        env = MountEnv(devices_root=t.devices_root, dev_prefix=t.dev_prefix, cgroup_driver="cgroupfs")
+        recs = [device.New(m, u) for u, m, _ in gpus_cfg[:2]]
+        util.MountGPUs(product_pod(), recs, env)
+        rc, rep = util.ProbeInPodFanout(product_pod(), recs, [], env, probe_exe=str(echo))
+        assert rc == 0 and all(r["args"].endswith("--skip-p2p --host-view") for r in rep["reports"])
+        assert "--host-view" not in rep["whole_pod"]["args"]
+        util.UnmountGPUs(product_pod(), recs, False, env)
+    finally:
+        t.stop()
